@@ -1,0 +1,126 @@
+"""Generate ``tests/golden/*.pt`` by running the UNMODIFIED reference (k-flouris/cmf) from
+/root/reference.  Build-container only: the GPU box has no /root/reference, which is why the
+outputs are committed as fixtures.  TEST INFRASTRUCTURE ONLY.
+
+    PYTHONDONTWRITEBYTECODE=1 python oracle/gen_golden.py [case ...]
+
+Import recipe: SURVEY.md Appendix A (vendored gpytorch first, then pyro stubs needed only by
+`cmf/models/components/bijections/sos.py:6-7`).  No reference code is copied: the reference
+modules are imported, loaded with the deterministic weights of ``oracle/detfill.py`` and driven
+through their own public entry points (`config.get_config/get_schema`, `cmf.models.get_density`,
+`cmf.non_square_helpers.get_non_square_train_metrics`).
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import time
+import types
+import warnings
+
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+REF = os.environ.get("CMF_REFERENCE", "/root/reference")
+
+
+def import_reference():
+    warnings.filterwarnings("ignore")
+    sys.setrecursionlimit(3000)
+    sys.dont_write_bytecode = True
+    sys.path.insert(0, os.path.join(REF, "gitmodules", "gpytorch"))
+    from gpytorch.utils import linear_cg  # noqa: F401
+    sys.path.pop(0)
+    for name in ["pyro", "pyro.nn", "pyro.distributions", "pyro.distributions.transforms",
+                 "pyro.distributions.transforms.polynomial"]:
+        mod = types.ModuleType(name)
+        mod.__path__ = []
+        sys.modules[name] = mod
+    sys.modules["pyro.distributions.transforms.polynomial"].Polynomial = object
+    sys.modules["pyro.nn"].AutoRegressiveNN = object
+    sys.path.insert(0, REF)
+    from config import get_config, get_schema, expand_grid
+    from cmf.models import get_density
+    from cmf.non_square_helpers import get_non_square_train_metrics
+    return get_config, get_schema, expand_grid, get_density, get_non_square_train_metrics
+
+
+def jsonable(obj):
+    return json.loads(json.dumps(obj, default=str))
+
+
+def run_case(name, case, api):
+    from cases import make_input, grad_probe
+    from detfill import fill_state_dict
+    get_config, get_schema, expand_grid, get_density, get_train_metrics = api
+
+    ds = case["dataset"]
+    cfg = expand_grid({"model": "non-square", "dataset": ds,
+                       **get_config(ds, "non-square", False), **case["overrides"]})[0]
+    schema = get_schema(cfg)
+    torch.manual_seed(0)
+    x = make_input(case)
+    density = get_density(schema, x)
+    # checkerboard masks are expand()ed buffers (acl.py:73) that load_state_dict cannot write into
+    filled = {k: v for k, v in fill_state_dict(density.state_dict()).items() if not k.endswith(".mask")}
+    missing, unexpected = density.load_state_dict(filled, strict=False)
+    assert not unexpected and all(k.endswith(".mask") for k in missing)
+    density.train()
+
+    # strip DataParallel (CPU: a plain passthrough) and the dequantiser (in-place rand, wrapper.py:27-30)
+    top = density.module if hasattr(density, "module") else density
+    if type(top).__name__ == "DequantizationDensity":
+        top = top.density
+
+    train_metrics = get_train_metrics(cfg)[0]
+    t0 = time.time()
+    loss = train_metrics(top, x.clone(), case["epoch"])["loss"]
+    loss.backward()
+    dt = time.time() - t0
+
+    grads = {}
+    for pname, p in density.named_parameters():
+        if p.grad is not None:
+            key = pname[len("module."):] if pname.startswith("module.") else pname
+            grads[key] = grad_probe(key, p.grad)
+
+    # intermediates, through the head's own methods (no graph needed)
+    head, xin = top, x.clone()
+    while type(head).__name__ != "NonSquareHeadDensity":
+        xin = head.bijection.x_to_z(xin)["z"]
+        head = head.prior
+    out = dict(name=name, case=jsonable({k: v for k, v in case.items()}), config=jsonable(cfg),
+               schema=jsonable(schema), loss=loss.detach().clone(), grads=grads, ref_seconds=dt,
+               x_pre=xin.detach().clone() if xin.numel() <= 4096 else None)
+    with torch.no_grad():
+        prior_dict = head.prior.elbo(xin)
+        z, low_dim_elbo, _ = head._traverse_backward(xin, prior_dict)
+        out.update(z=z.clone(), low_dim_elbo=low_dim_elbo.clone())
+        logdet, recon, gram = head._exact_log_det_jac_and_reconstruction(z)
+        out.update(logdet=logdet.clone(), gram=gram.clone(),
+                   recon_loss=((recon - xin).flatten(1) ** 2).sum(-1, keepdim=True))
+        off = ~torch.eye(gram.shape[1], dtype=torch.bool)
+        out["l1_offdiag"] = gram.masked_select(off).view(gram.shape[0], -1).abs().sum(1, keepdim=True)
+        out["l1_diag"] = torch.diagonal(gram, dim1=-2, dim2=-1).abs().sum(1, keepdim=True)
+    return out
+
+
+def main(argv):
+    from cases import CASES
+    api = import_reference()
+    out_dir = os.path.join(os.path.dirname(HERE), "tests", "golden")
+    os.makedirs(out_dir, exist_ok=True)
+    names = argv or [n for n, c in CASES.items()]
+    for name in names:
+        t0 = time.time()
+        res = run_case(name, CASES[name], api)
+        path = os.path.join(out_dir, name + ".pt")
+        torch.save(res, path)
+        print(f"{name}: loss={float(res['loss']):.6f}  {os.path.getsize(path) / 1024:.1f} KiB  "
+              f"{time.time() - t0:.1f}s", flush=True)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1:])

@@ -1,0 +1,84 @@
+"""Pin the CPU oracle (oracle/cmf_oracle.py) to outputs of the unmodified reference
+(tests/golden/*.pt, written by oracle/gen_golden.py in the build container)."""
+import pytest
+import torch
+
+from conftest import load_golden
+from cases import CASES, make_input, grad_probe
+from detfill import fill_state_dict
+import cmf_oracle as O
+
+FAST = [n for n, c in CASES.items() if not c.get("slow")]
+RTOL = 2e-5   # oracle and reference are the same fp32 torch ops; only op order inside sums differs
+
+
+def build(golden, dtype=torch.float32):
+    case = golden["case"]
+    params = fill_state_dict(O.init_params(golden["schema"], case["x_shape"]))
+    params = {k: (v.to(dtype).requires_grad_(True) if v.is_floating_point() else v) for k, v in params.items()}
+    return O.OracleFlow(golden["schema"], params, case["x_shape"]), params
+
+
+def close(a, b, rtol=RTOL, atol=0.0):
+    a, b = a.detach().double(), b.detach().double()
+    scale = max(float(b.abs().max()), 1e-30)
+    err = float((a - b).abs().max())
+    assert err <= rtol * scale + atol, f"max err {err:.3e} vs scale {scale:.3e}"
+
+
+@pytest.mark.parametrize("name", FAST)
+def test_oracle_matches_reference(name):
+    g = load_golden(name)
+    flow, params = build(g)
+    x = make_input(CASES[name])
+    # parameter inventory == the reference's trainable tensors
+    ref_keys = set(g["grads"])
+    ours = {k for k, v in params.items() if v.is_floating_point()}
+    assert ref_keys <= ours
+    loss = O.train_loss(flow, g["config"], x, g["case"]["epoch"])
+    loss.backward()
+    close(loss, g["loss"])
+    for k, probe in g["grads"].items():
+        mine = grad_probe(k, params[k].grad)
+        tol = 5e-5 * max(probe["norm"], 1e-12)
+        assert abs(mine["norm"] - probe["norm"]) <= tol, k
+        assert abs(mine["dot"] - probe["dot"]) <= 5e-5 * max(probe["norm"], 1e-12) * 8, k
+        close(mine["head"], probe["head"], rtol=1e-4, atol=tol)
+    # untouched parameters must have no gradient in the reference either
+    for k in ours - ref_keys:
+        assert params[k].grad is None or float(params[k].grad.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("name", FAST)
+def test_oracle_intermediates(name):
+    g = load_golden(name)
+    flow, _ = build(g)
+    x = make_input(CASES[name])
+    with torch.no_grad():
+        xin, z, low = flow.encode(x)
+        close(z, g["z"]); close(low, g["low_dim_elbo"])
+        logdet, recon, gram, attempts = flow.exact_log_det(z)
+        assert attempts == 1
+        close(gram, g["gram"]); close(logdet, g["logdet"], atol=1e-5)
+        close(((recon - xin).flatten(1) ** 2).sum(-1, keepdim=True), g["recon_loss"])
+        off = ~torch.eye(flow.d, dtype=torch.bool)
+        close(gram.masked_select(off).view(gram.shape[0], -1).abs().sum(1, keepdim=True), g["l1_offdiag"])
+
+
+@pytest.mark.slow
+def test_oracle_mnist_full_shape():
+    g = load_golden("mnist_gij_d64")
+    flow, params = build(g)
+    x = make_input(CASES["mnist_gij_d64"])
+    with torch.no_grad():
+        xin, z, low = flow.encode(x)
+        close(z, g["z"]); close(low, g["low_dim_elbo"])
+        logdet, recon, gram, _ = flow.exact_log_det(z)
+        close(gram, g["gram"]); close(logdet, g["logdet"], atol=1e-4)
+
+
+def test_schema_walk_rejects_unknown_layer():
+    g = load_golden("sphere_gij_d3")
+    bad = list(g["schema"]) + [{"type": "made"}]
+    with pytest.raises(ValueError):
+        O.OracleFlow(bad, fill_state_dict(O.init_params(g["schema"], (3,))), (3,))
