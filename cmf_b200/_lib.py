@@ -1,0 +1,62 @@
+"""ctypes binding of ``libcmf_b200.so`` -- the C ABI declared in ``include/cmf_b200.h``.
+
+There is no CPU fallback: if the library is missing or a launch fails this raises.  The Python
+layer above only ever passes raw device pointers, sizes and the current CUDA stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libcmf_b200.so")
+ABI_VERSION = 1
+
+_vp, _i, _ll, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/cmf_b200.h one to one
+SIGNATURES = {
+    "cmf_version": (_i, []),
+    "cmf_last_error_string": (C.c_char_p, []),
+    "cmf_coupling_jvp_fwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_coupling_jvp_bwd_workspace": (_sz, [_i, _i, _i, _i]),
+    "cmf_coupling_jvp_bwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                  _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "cmf_gather_rows": (_i, [_ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_gram_fwd": (_i, [_i, _i, _i, _vp, _vp, _i, _vp]),
+    "cmf_gram_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
+    "cmf_chol_logdet_fwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_chol_logdet_bwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+}
+
+_lib = None
+
+
+class CmfB200Error(RuntimeError):
+    pass
+
+
+def load():
+    """Load the shared library once; raise loudly if it is absent (no fallback path exists)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CmfB200Error(
+            f"{LIB_PATH} not found: build it with `python -m cmf_b200.build` "
+            "(nvcc, sm_100a). cmf_b200 has no CPU or eager fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError here == header/library mismatch
+        fn.restype, fn.argtypes = res, args
+    if lib.cmf_version() != ABI_VERSION:
+        raise CmfB200Error(f"libcmf_b200.so ABI {lib.cmf_version()} != expected {ABI_VERSION}")
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        msg = load().cmf_last_error_string().decode(errors="replace")
+        kind = "bad argument" if code < 0 else f"CUDA error {code}"
+        raise CmfB200Error(f"{what}: {kind}: {msg}")

@@ -1,0 +1,402 @@
+// Kernel (a): fused affine-coupling push of the primal and all d tangent columns, and its adjoint.
+//
+// HBM-bound streaming kernels.  Algorithmic traffic per launch (fp32):
+//   fwd: reads z_m,s,t (3M) + V_m,S_dot,T_dot (3Md), writes x_m (M) + V_out (Md)  = 16 M (1+d) B bytes
+//   bwd: reads g_V,V_m,S_dot (3Md) + O(M), writes g_Vin,g_S_dot,g_T_dot (3Md) + O(M) = 24 M (1+d) B bytes
+// Thread mapping: one thread owns one 128-bit vector (4 consecutive compact elements j of one
+// sample) and walks a chunk of tangent columns k, so exp(-s), z_m are computed once and reused
+// from registers for every column; consecutive lanes touch consecutive 16-byte words of every
+// stream (fully coalesced).  The mapped (checkerboard / permuted) variant does the same with
+// 32-bit accesses, reading conditioner outputs through the int32 index map.
+#include "common.cuh"
+
+namespace cmf {
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;
+
+// ------------------------------------------------------------------------------------------------
+// forward, identity map, 128-bit path.  M == Q, M % 4 == 0, all pointers 16B aligned.
+// grid = (ceil(B*M/4 / kThreads), KC)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+coupling_fwd_vec4(int B, int d, int M, int kchunk,
+                  const float* __restrict__ z_m, const float* __restrict__ V_m,
+                  const float* __restrict__ st, const float* __restrict__ ST,
+                  float* __restrict__ x_m, float* __restrict__ V_out) {
+    const int Mv = M >> 2;
+    const long long t = (long long)blockIdx.x * kThreads + threadIdx.x;
+    if (t >= (long long)B * Mv) return;
+    const int b = (int)(t / Mv);
+    const int j = (int)(t % Mv) << 2;
+    const float4 z = ldg4(z_m + (size_t)b * M + j);
+    const float4 s = ldg4(st + (size_t)b * 2 * M + M + j);
+    float4 e;
+    e.x = expf(-s.x); e.y = expf(-s.y); e.z = expf(-s.z); e.w = expf(-s.w);
+    if (blockIdx.y == 0) {
+        const float4 sh = ldg4(st + (size_t)b * 2 * M + j);
+        float4 x;
+        x.x = z.x * e.x - sh.x; x.y = z.y * e.y - sh.y; x.z = z.z * e.z - sh.z; x.w = z.w * e.w - sh.w;
+        *reinterpret_cast<float4*>(x_m + (size_t)b * M + j) = x;
+    }
+    const int k0 = blockIdx.y * kchunk;
+    const int k1 = min(d, k0 + kchunk);
+    const float* vp = V_m + ((size_t)b * d + k0) * M + j;
+    const float* tp = ST + ((size_t)b * d + k0) * 2 * M + j;
+    float* op = V_out + ((size_t)b * d + k0) * M + j;
+    int k = k0;
+    for (; k + kUnroll <= k1; k += kUnroll) {
+        float4 v[kUnroll], sd[kUnroll], td[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            v[u] = ldcs4(vp + (size_t)u * M);
+            td[u] = ldcs4(tp + (size_t)u * 2 * M);
+            sd[u] = ldcs4(tp + (size_t)u * 2 * M + M);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            float4 o;
+            o.x = e.x * (v[u].x - z.x * sd[u].x) - td[u].x;
+            o.y = e.y * (v[u].y - z.y * sd[u].y) - td[u].y;
+            o.z = e.z * (v[u].z - z.z * sd[u].z) - td[u].z;
+            o.w = e.w * (v[u].w - z.w * sd[u].w) - td[u].w;
+            *reinterpret_cast<float4*>(op + (size_t)u * M) = o;
+        }
+        vp += (size_t)kUnroll * M; tp += (size_t)kUnroll * 2 * M; op += (size_t)kUnroll * M;
+    }
+    for (; k < k1; ++k) {
+        const float4 v = ldcs4(vp), td = ldcs4(tp), sd = ldcs4(tp + M);
+        float4 o;
+        o.x = e.x * (v.x - z.x * sd.x) - td.x;
+        o.y = e.y * (v.y - z.y * sd.y) - td.y;
+        o.z = e.z * (v.z - z.z * sd.z) - td.z;
+        o.w = e.w * (v.w - z.w * sd.w) - td.w;
+        *reinterpret_cast<float4*>(op) = o;
+        vp += M; tp += 2 * M; op += M;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward, general: optional index map, any M/Q, 32-bit accesses.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+coupling_fwd_map(int B, int d, int M, int Q, int kchunk,
+                 const float* __restrict__ z_m, const float* __restrict__ V_m,
+                 const float* __restrict__ st, const float* __restrict__ ST,
+                 const int32_t* __restrict__ map,
+                 float* __restrict__ x_m, float* __restrict__ V_out) {
+    const long long t = (long long)blockIdx.x * kThreads + threadIdx.x;
+    if (t >= (long long)B * M) return;
+    const int b = (int)(t / M);
+    const int j = (int)(t % M);
+    const int q = map ? __ldg(map + j) : j;
+    const float z = __ldg(z_m + (size_t)b * M + j);
+    const float e = expf(-__ldg(st + (size_t)b * 2 * Q + Q + q));
+    if (blockIdx.y == 0) x_m[(size_t)b * M + j] = z * e - __ldg(st + (size_t)b * 2 * Q + q);
+    const int k0 = blockIdx.y * kchunk;
+    const int k1 = min(d, k0 + kchunk);
+    const float* vp = V_m + ((size_t)b * d + k0) * M + j;
+    const float* tp = ST + ((size_t)b * d + k0) * 2 * Q + q;
+    float* op = V_out + ((size_t)b * d + k0) * M + j;
+    int k = k0;
+    for (; k + kUnroll <= k1; k += kUnroll) {
+        float v[kUnroll], sd[kUnroll], td[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            v[u] = __ldcs(vp + (size_t)u * M);
+            td[u] = __ldg(tp + (size_t)u * 2 * Q);
+            sd[u] = __ldg(tp + (size_t)u * 2 * Q + Q);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) op[(size_t)u * M] = e * (v[u] - z * sd[u]) - td[u];
+        vp += (size_t)kUnroll * M; tp += (size_t)kUnroll * 2 * Q; op += (size_t)kUnroll * M;
+    }
+    for (; k < k1; ++k) {
+        *op = e * (__ldcs(vp) - z * __ldg(tp + Q)) - __ldg(tp);
+        vp += M; tp += 2 * Q; op += M;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward.  Per (b, j):  A = sum_k S_dot_k * g_k,  C = sum_k V_k * g_k   (g = g_V)
+//   g_Vin_k   = e * g_k          g_S_dot_k = -e * z * g_k        g_T_dot_k = -g_k
+//   g_z = e * (g_x - A)          g_s = -z e g_x - e (C - z A)    g_t = -g_x
+// When the tangent range is split over blockIdx.y (KC > 1) the partial (A, C) go to the workspace
+// [KC][2][B*M] and coupling_bwd_finalize reduces them in a fixed order (deterministic).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void finalize_store(float z, float e, float gx, float A, float C,
+                                               float* g_z, float* g_t, float* g_s) {
+    *g_z = e * (gx - A);
+    *g_s = -z * e * gx - e * (C - z * A);
+    *g_t = -gx;
+}
+
+// identity map, 128-bit path.  grid = (ceil(B*M/4 / kThreads), KC)
+__global__ void __launch_bounds__(kThreads)
+coupling_bwd_vec4(int B, int d, int M, int kchunk,
+                  const float* __restrict__ z_m, const float* __restrict__ V_m,
+                  const float* __restrict__ st, const float* __restrict__ ST,
+                  const float* __restrict__ g_x, const float* __restrict__ g_V,
+                  float* __restrict__ g_z, float* __restrict__ g_Vin,
+                  float* __restrict__ g_st, float* __restrict__ g_ST, float* __restrict__ ws) {
+    const int Mv = M >> 2;
+    const long long t = (long long)blockIdx.x * kThreads + threadIdx.x;
+    if (t >= (long long)B * Mv) return;
+    const int b = (int)(t / Mv);
+    const int j = (int)(t % Mv) << 2;
+    const float4 z = ldg4(z_m + (size_t)b * M + j);
+    const float4 s = ldg4(st + (size_t)b * 2 * M + M + j);
+    float4 e;
+    e.x = expf(-s.x); e.y = expf(-s.y); e.z = expf(-s.z); e.w = expf(-s.w);
+    float4 ez;
+    ez.x = -e.x * z.x; ez.y = -e.y * z.y; ez.z = -e.z * z.z; ez.w = -e.w * z.w;
+    float4 A = make_float4(0.f, 0.f, 0.f, 0.f), C = A;
+    const int k0 = blockIdx.y * kchunk;
+    const int k1 = min(d, k0 + kchunk);
+    const float* gp = g_V + ((size_t)b * d + k0) * M + j;
+    const float* vp = V_m + ((size_t)b * d + k0) * M + j;
+    const float* sp = ST + ((size_t)b * d + k0) * 2 * M + M + j;
+    float* ovp = g_Vin + ((size_t)b * d + k0) * M + j;
+    float* otp = g_ST + ((size_t)b * d + k0) * 2 * M + j;
+    int k = k0;
+    for (; k + kUnroll <= k1; k += kUnroll) {
+        float4 g[kUnroll], v[kUnroll], sd[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            g[u] = ldcs4(gp + (size_t)u * M);
+            v[u] = ldcs4(vp + (size_t)u * M);
+            sd[u] = ldcs4(sp + (size_t)u * 2 * M);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            A.x += sd[u].x * g[u].x; A.y += sd[u].y * g[u].y; A.z += sd[u].z * g[u].z; A.w += sd[u].w * g[u].w;
+            C.x += v[u].x * g[u].x;  C.y += v[u].y * g[u].y;  C.z += v[u].z * g[u].z;  C.w += v[u].w * g[u].w;
+            stcs4(ovp + (size_t)u * M, make_float4(e.x * g[u].x, e.y * g[u].y, e.z * g[u].z, e.w * g[u].w));
+            stcs4(otp + (size_t)u * 2 * M, make_float4(-g[u].x, -g[u].y, -g[u].z, -g[u].w));
+            stcs4(otp + (size_t)u * 2 * M + M, make_float4(ez.x * g[u].x, ez.y * g[u].y, ez.z * g[u].z, ez.w * g[u].w));
+        }
+        gp += (size_t)kUnroll * M; vp += (size_t)kUnroll * M; sp += (size_t)kUnroll * 2 * M;
+        ovp += (size_t)kUnroll * M; otp += (size_t)kUnroll * 2 * M;
+    }
+    for (; k < k1; ++k) {
+        const float4 g = ldcs4(gp), v = ldcs4(vp), sd = ldcs4(sp);
+        A.x += sd.x * g.x; A.y += sd.y * g.y; A.z += sd.z * g.z; A.w += sd.w * g.w;
+        C.x += v.x * g.x;  C.y += v.y * g.y;  C.z += v.z * g.z;  C.w += v.w * g.w;
+        stcs4(ovp, make_float4(e.x * g.x, e.y * g.y, e.z * g.z, e.w * g.w));
+        stcs4(otp, make_float4(-g.x, -g.y, -g.z, -g.w));
+        stcs4(otp + M, make_float4(ez.x * g.x, ez.y * g.y, ez.z * g.z, ez.w * g.w));
+        gp += M; vp += M; sp += 2 * M; ovp += M; otp += 2 * M;
+    }
+    if (gridDim.y == 1) {
+        float4 gx = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (g_x) gx = ldg4(g_x + (size_t)b * M + j);
+        float4 gz, gt, gs;
+        finalize_store(z.x, e.x, gx.x, A.x, C.x, &gz.x, &gt.x, &gs.x);
+        finalize_store(z.y, e.y, gx.y, A.y, C.y, &gz.y, &gt.y, &gs.y);
+        finalize_store(z.z, e.z, gx.z, A.z, C.z, &gz.z, &gt.z, &gs.z);
+        finalize_store(z.w, e.w, gx.w, A.w, C.w, &gz.w, &gt.w, &gs.w);
+        *reinterpret_cast<float4*>(g_z + (size_t)b * M + j) = gz;
+        *reinterpret_cast<float4*>(g_st + (size_t)b * 2 * M + j) = gt;
+        *reinterpret_cast<float4*>(g_st + (size_t)b * 2 * M + M + j) = gs;
+    } else {
+        const size_t BM = (size_t)B * M;
+        float* w = ws + (size_t)blockIdx.y * 2 * BM + (size_t)b * M + j;
+        *reinterpret_cast<float4*>(w) = A;
+        *reinterpret_cast<float4*>(w + BM) = C;
+    }
+}
+
+// general: thread per conditioner position (b, q); dense zero-filled writes of g_st / g_ST.
+__global__ void __launch_bounds__(kThreads)
+coupling_bwd_map(int B, int d, int M, int Q, int kchunk,
+                 const float* __restrict__ z_m, const float* __restrict__ V_m,
+                 const float* __restrict__ st, const float* __restrict__ ST,
+                 const int32_t* __restrict__ inv,
+                 const float* __restrict__ g_x, const float* __restrict__ g_V,
+                 float* __restrict__ g_z, float* __restrict__ g_Vin,
+                 float* __restrict__ g_st, float* __restrict__ g_ST, float* __restrict__ ws) {
+    const long long t = (long long)blockIdx.x * kThreads + threadIdx.x;
+    if (t >= (long long)B * Q) return;
+    const int b = (int)(t / Q);
+    const int q = (int)(t % Q);
+    const int j = inv ? __ldg(inv + q) : q;
+    const int k0 = blockIdx.y * kchunk;
+    const int k1 = min(d, k0 + kchunk);
+    float* otp = g_ST + ((size_t)b * d + k0) * 2 * Q + q;
+    if (j < 0) {  // passthrough position of a checkerboard layer: conditioner output unused
+        for (int k = k0; k < k1; ++k) { otp[0] = 0.f; otp[Q] = 0.f; otp += 2 * Q; }
+        if (blockIdx.y == 0) { g_st[(size_t)b * 2 * Q + q] = 0.f; g_st[(size_t)b * 2 * Q + Q + q] = 0.f; }
+        return;
+    }
+    const float z = __ldg(z_m + (size_t)b * M + j);
+    const float e = expf(-__ldg(st + (size_t)b * 2 * Q + Q + q));
+    const float ez = -e * z;
+    float A = 0.f, C = 0.f;
+    const float* gp = g_V + ((size_t)b * d + k0) * M + j;
+    const float* vp = V_m + ((size_t)b * d + k0) * M + j;
+    const float* sp = ST + ((size_t)b * d + k0) * 2 * Q + Q + q;
+    float* ovp = g_Vin + ((size_t)b * d + k0) * M + j;
+    int k = k0;
+    for (; k + kUnroll <= k1; k += kUnroll) {
+        float g[kUnroll], v[kUnroll], sd[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            g[u] = __ldcs(gp + (size_t)u * M);
+            v[u] = __ldcs(vp + (size_t)u * M);
+            sd[u] = __ldg(sp + (size_t)u * 2 * Q);
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            A += sd[u] * g[u];
+            C += v[u] * g[u];
+            ovp[(size_t)u * M] = e * g[u];
+            otp[(size_t)u * 2 * Q] = -g[u];
+            otp[(size_t)u * 2 * Q + Q] = ez * g[u];
+        }
+        gp += (size_t)kUnroll * M; vp += (size_t)kUnroll * M; sp += (size_t)kUnroll * 2 * Q;
+        ovp += (size_t)kUnroll * M; otp += (size_t)kUnroll * 2 * Q;
+    }
+    for (; k < k1; ++k) {
+        const float g = __ldcs(gp), v = __ldcs(vp), sd = __ldg(sp);
+        A += sd * g; C += v * g;
+        *ovp = e * g; otp[0] = -g; otp[Q] = ez * g;
+        gp += M; vp += M; sp += 2 * Q; ovp += M; otp += 2 * Q;
+    }
+    if (gridDim.y == 1) {
+        const float gx = g_x ? __ldg(g_x + (size_t)b * M + j) : 0.f;
+        finalize_store(z, e, gx, A, C, g_z + (size_t)b * M + j,
+                       g_st + (size_t)b * 2 * Q + q, g_st + (size_t)b * 2 * Q + Q + q);
+    } else {
+        const size_t BM = (size_t)B * M;
+        float* w = ws + (size_t)blockIdx.y * 2 * BM + (size_t)b * M + j;
+        w[0] = A; w[BM] = C;
+    }
+}
+
+// reduce the KC partials (fixed order) and emit the primal adjoints.  thread per (b, j).
+__global__ void __launch_bounds__(kThreads)
+coupling_bwd_finalize(int B, int M, int Q, int KC,
+                      const float* __restrict__ z_m, const float* __restrict__ st,
+                      const int32_t* __restrict__ map, const float* __restrict__ g_x,
+                      const float* __restrict__ ws,
+                      float* __restrict__ g_z, float* __restrict__ g_st) {
+    const long long t = (long long)blockIdx.x * kThreads + threadIdx.x;
+    const size_t BM = (size_t)B * M;
+    if (t >= (long long)BM) return;
+    const int b = (int)(t / M);
+    const int j = (int)(t % M);
+    const int q = map ? __ldg(map + j) : j;
+    float A = 0.f, C = 0.f;
+    for (int c = 0; c < KC; ++c) {
+        A += ws[(size_t)c * 2 * BM + t];
+        C += ws[(size_t)c * 2 * BM + BM + t];
+    }
+    const float z = __ldg(z_m + t);
+    const float e = expf(-__ldg(st + (size_t)b * 2 * Q + Q + q));
+    const float gx = g_x ? __ldg(g_x + t) : 0.f;
+    finalize_store(z, e, gx, A, C, g_z + t, g_st + (size_t)b * 2 * Q + q, g_st + (size_t)b * 2 * Q + Q + q);
+}
+
+// How many tangent chunks to spread over blockIdx.y so the grid fills the machine (>= ~2 waves of
+// 148 SMs x 2048 threads) even at the reference's default batch of 50.
+static int pick_kchunks(long long threads_x, int d) {
+    if (d <= 0) return 1;
+    const long long want = 2LL * kNumSMs * 2048;
+    long long kc = ceil_div(want, threads_x > 0 ? threads_x : 1);
+    const long long kc_max = ceil_div(d, kUnroll);  // at least one unrolled batch per chunk
+    if (kc > kc_max) kc = kc_max;
+    if (kc < 1) kc = 1;
+    return (int)kc;
+}
+
+static bool vec4_ok(int M, int Q, const void* map, std::initializer_list<const void*> ptrs) {
+    if (map != nullptr || M != Q || (M & 3) != 0) return false;
+    for (const void* p : ptrs)
+        if (p != nullptr && !aligned16(p)) return false;
+    return true;
+}
+
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_coupling_jvp_fwd(int B, int d, int M, int Q,
+                                    const float* z_m, const float* V_m,
+                                    const float* st, const float* ST, const int32_t* map,
+                                    float* x_m, float* V_out, cmf_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CMF_REQUIRE(B >= 0 && d >= 0 && M >= 0 && Q >= M, "coupling_fwd: bad sizes B=%d d=%d M=%d Q=%d", B, d, M, Q);
+    CMF_REQUIRE(map != nullptr || M == Q, "coupling_fwd: identity map needs M == Q (M=%d Q=%d)", M, Q);
+    if (B == 0 || M == 0) return 0;
+    CMF_REQUIRE(z_m && st && x_m, "coupling_fwd: null primal pointer");
+    CMF_REQUIRE(d == 0 || (V_m && ST && V_out), "coupling_fwd: null tangent pointer");
+    if (vec4_ok(M, Q, map, {z_m, V_m, st, ST, x_m, V_out})) {
+        const long long tx = (long long)B * (M >> 2);
+        const int KC = pick_kchunks(tx, d);
+        const int kchunk = d > 0 ? (int)ceil_div(ceil_div(d, KC), kUnroll) * kUnroll : 1;
+        dim3 grid((unsigned)ceil_div(tx, kThreads), (unsigned)(d > 0 ? ceil_div(d, kchunk) : 1));
+        coupling_fwd_vec4<<<grid, kThreads, 0, stream>>>(B, d, M, kchunk, z_m, V_m, st, ST, x_m, V_out);
+    } else {
+        const long long tx = (long long)B * M;
+        const int KC = pick_kchunks(tx, d);
+        const int kchunk = d > 0 ? (int)ceil_div(ceil_div(d, KC), kUnroll) * kUnroll : 1;
+        dim3 grid((unsigned)ceil_div(tx, kThreads), (unsigned)(d > 0 ? ceil_div(d, kchunk) : 1));
+        coupling_fwd_map<<<grid, kThreads, 0, stream>>>(B, d, M, Q, kchunk, z_m, V_m, st, ST, map, x_m, V_out);
+    }
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+// The split over tangent chunks must be the same function of (B,d,M,Q) in the workspace query and
+// in the launch; vectorisation (which changes threads_x) depends on pointers, so size for the worst case.
+static int bwd_kchunks(int B, int d, int M, int Q, bool vec) {
+    return pick_kchunks(vec ? (long long)B * (M >> 2) : (long long)B * Q, d);
+}
+
+extern "C" size_t cmf_coupling_jvp_bwd_workspace(int B, int d, int M, int Q) {
+    if (B <= 0 || M <= 0 || d <= 0) return 0;
+    int kc = bwd_kchunks(B, d, M, Q, false);
+    if (M == Q && (M & 3) == 0) kc = max(kc, bwd_kchunks(B, d, M, Q, true));
+    return kc > 1 ? (size_t)kc * 2 * (size_t)B * M * sizeof(float) : 0;
+}
+
+extern "C" int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
+                                    const float* z_m, const float* V_m,
+                                    const float* st, const float* ST,
+                                    const int32_t* map, const int32_t* inv,
+                                    const float* g_x, const float* g_V,
+                                    float* g_z, float* g_Vin, float* g_st, float* g_ST,
+                                    void* workspace, size_t workspace_bytes, cmf_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CMF_REQUIRE(B >= 0 && d >= 0 && M >= 0 && Q >= M, "coupling_bwd: bad sizes B=%d d=%d M=%d Q=%d", B, d, M, Q);
+    CMF_REQUIRE((map == nullptr) == (inv == nullptr), "coupling_bwd: map and inv must be given together");
+    CMF_REQUIRE(map != nullptr || M == Q, "coupling_bwd: identity map needs M == Q (M=%d Q=%d)", M, Q);
+    if (B == 0 || Q == 0) return 0;
+    CMF_REQUIRE(z_m && st && g_z && g_st, "coupling_bwd: null primal pointer");
+    CMF_REQUIRE(d == 0 || (V_m && ST && g_V && g_Vin && g_ST), "coupling_bwd: null tangent pointer");
+    const bool vec = vec4_ok(M, Q, map, {z_m, V_m, st, ST, g_x, g_V, g_z, g_Vin, g_st, g_ST, workspace});
+    const int KC = bwd_kchunks(B, d, M, Q, vec);
+    const int kchunk = d > 0 ? (int)ceil_div(ceil_div(d, KC), kUnroll) * kUnroll : 1;
+    const int ny = d > 0 ? (int)ceil_div(d, kchunk) : 1;
+    if (ny > 1)
+        CMF_REQUIRE(workspace && workspace_bytes >= (size_t)ny * 2 * (size_t)B * M * sizeof(float),
+                    "coupling_bwd: workspace too small (%zu bytes, need %zu)", workspace_bytes,
+                    (size_t)ny * 2 * (size_t)B * M * sizeof(float));
+    float* ws = static_cast<float*>(workspace);
+    if (vec) {
+        dim3 grid((unsigned)ceil_div((long long)B * (M >> 2), kThreads), (unsigned)ny);
+        coupling_bwd_vec4<<<grid, kThreads, 0, stream>>>(B, d, M, kchunk, z_m, V_m, st, ST, g_x, g_V,
+                                                         g_z, g_Vin, g_st, g_ST, ws);
+    } else {
+        dim3 grid((unsigned)ceil_div((long long)B * Q, kThreads), (unsigned)ny);
+        coupling_bwd_map<<<grid, kThreads, 0, stream>>>(B, d, M, Q, kchunk, z_m, V_m, st, ST, inv, g_x, g_V,
+                                                        g_z, g_Vin, g_st, g_ST, ws);
+    }
+    CMF_CHECK_LAUNCH();
+    if (ny > 1) {
+        coupling_bwd_finalize<<<(unsigned)ceil_div((long long)B * M, kThreads), kThreads, 0, stream>>>(
+            B, M, Q, ny, z_m, st, map, g_x, ws, g_z, g_st);
+        CMF_CHECK_LAUNCH();
+    }
+    return 0;
+}

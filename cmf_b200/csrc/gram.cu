@@ -1,0 +1,164 @@
+// Kernel (b), portable-precision path: per-sample metric G = V V^T (V = J^T, shape d x n) and its
+// adjoint g_V = (g_G + g_G^T) V, as classic shared-memory tiled FP32 FMA GEMMs (64x64x16 tiles,
+// 4x4 register micro-tiles).  Used for every d; the tcgen05 3xTF32 kernel (gram_tc.cu) takes over
+// for the tensor-core friendly shapes.  Only the lower-triangular tiles of G are computed and the
+// mirror is written from the same registers (SYRK).
+#include "common.cuh"
+
+namespace cmf {
+
+constexpr int BT = 64;       // tile edge in M and N
+constexpr int BK = 16;       // k-slab
+constexpr int LDS_ = BT + 4; // padded smem row (keeps float4 alignment)
+constexpr int kGemmThreads = 256;
+
+// load a [64 rows x 16 k] slab of a row-major matrix (ld = row stride, k contiguous) transposed
+// into s[k][row]; rows >= nrows / k >= nk read as zero.
+__device__ __forceinline__ void load_slab_T(float (*s)[LDS_], const float* __restrict__ base, int ld,
+                                            int row0, int nrows, int k0, int nk) {
+    const int row = threadIdx.x >> 2;
+    const int kq = (threadIdx.x & 3) << 2;
+    const int r = row0 + row;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int k = k0 + kq + i;
+        s[kq + i][row] = (r < nrows && k < nk) ? __ldg(base + (size_t)r * ld + k) : 0.f;
+    }
+}
+
+__device__ __forceinline__ void fma_tile(float (&acc)[4][4], const float (*As)[LDS_], const float (*Bs)[LDS_],
+                                         int ty, int tx) {
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+        const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+        const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+        const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+}
+
+// grid.x = B * T(T+1)/2 (sample-major; lower-triangular tile pairs)
+__global__ void __launch_bounds__(kGemmThreads)
+gram_fwd_kernel(int d, int n, int ntiles, const float* __restrict__ V, float* __restrict__ G, int accumulate) {
+    __shared__ __align__(16) float As[BK][LDS_];
+    __shared__ __align__(16) float Bs[BK][LDS_];
+    const int b = blockIdx.x / ntiles;
+    int tr = 0, rem = blockIdx.x - b * ntiles;
+    while (rem > tr) { rem -= tr + 1; ++tr; }   // tile id -> (tr, tc), tc <= tr
+    const int tc = rem;
+    const float* Vb = V + (size_t)b * d * n;
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+    float acc[4][4] = {};
+    for (int k0 = 0; k0 < n; k0 += BK) {
+        load_slab_T(As, Vb, n, tr * BT, d, k0, n);
+        load_slab_T(Bs, Vb, n, tc * BT, d, k0, n);
+        __syncthreads();
+        fma_tile(acc, As, Bs, ty, tx);
+        __syncthreads();
+    }
+    float* Gb = G + (size_t)b * d * d;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = tr * BT + ty * 4 + i;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = tc * BT + tx * 4 + j;
+            if (r < d && c < d) {
+                const float v = acc[i][j];
+                if (accumulate) {
+                    Gb[(size_t)r * d + c] += v;
+                    if (tr != tc) Gb[(size_t)c * d + r] += v;
+                } else {
+                    Gb[(size_t)r * d + c] = v;
+                    if (tr != tc) Gb[(size_t)c * d + r] = v;
+                }
+            }
+        }
+    }
+}
+
+// g_V[b] = (g_G[b] + g_G[b]^T) V[b].  grid = (B * ceil(n/64), ceil(d/64))
+__global__ void __launch_bounds__(kGemmThreads)
+gram_bwd_kernel(int d, int n, int nx, const float* __restrict__ V, const float* __restrict__ gG,
+                float* __restrict__ gV) {
+    __shared__ __align__(16) float As[BK][LDS_];
+    __shared__ __align__(16) float Bs[BK][LDS_];
+    const int b = blockIdx.x / nx;
+    const int r0 = blockIdx.y * BT, n0 = (blockIdx.x - b * nx) * BT;
+    const float* Vb = V + (size_t)b * d * n;
+    const float* Sb = gG + (size_t)b * d * d;
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+    float acc[4][4] = {};
+    for (int k0 = 0; k0 < d; k0 += BK) {
+        {   // As[k][m] = S[m][k] + S[k][m]
+            const int row = threadIdx.x >> 2, kq = (threadIdx.x & 3) << 2;
+            const int m = r0 + row;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int k = k0 + kq + i;
+                As[kq + i][row] = (m < d && k < d) ? __ldg(Sb + (size_t)m * d + k) + __ldg(Sb + (size_t)k * d + m) : 0.f;
+            }
+        }
+        {   // Bs[k][nn] = V[k][n0 + nn]
+            const int kk = threadIdx.x >> 4, nq = (threadIdx.x & 15) << 2;
+            const int k = k0 + kk;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int c = n0 + nq + i;
+                Bs[kk][nq + i] = (k < d && c < n) ? __ldg(Vb + (size_t)k * n + c) : 0.f;
+            }
+        }
+        __syncthreads();
+        fma_tile(acc, As, Bs, ty, tx);
+        __syncthreads();
+    }
+    float* Ob = gV + (size_t)b * d * n;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = r0 + ty * 4 + i;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = n0 + tx * 4 + j;
+            if (r < d && c < n) Ob[(size_t)r * n + c] = acc[i][j];
+        }
+    }
+}
+
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_gram_fwd(int B, int d, int n, const float* V, float* G, int accumulate, cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && d >= 0 && n >= 0, "gram_fwd: negative size");
+    if (B == 0 || d == 0) return 0;
+    CMF_REQUIRE(G && (n == 0 || V), "gram_fwd: null pointer");
+    if (n == 0) {
+        if (!accumulate) {
+            cudaError_t e = cudaMemsetAsync(G, 0, (size_t)B * d * d * sizeof(float), (cudaStream_t)stream);
+            if (e != cudaSuccess) { set_error("gram_fwd memset: %s", cudaGetErrorString(e)); return (int)e; }
+        }
+        return 0;
+    }
+    const int T = (int)ceil_div(d, BT);
+    const int ntiles = T * (T + 1) / 2;
+    CMF_REQUIRE((long long)B * ntiles < (1LL << 31), "gram_fwd: grid too large");
+    gram_fwd_kernel<<<(unsigned)(B * ntiles), kGemmThreads, 0, (cudaStream_t)stream>>>(d, n, ntiles, V, G, accumulate);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && d >= 0 && n >= 0, "gram_bwd: negative size");
+    if (B == 0 || d == 0 || n == 0) return 0;
+    CMF_REQUIRE(V && g_G && g_V, "gram_bwd: null pointer");
+    const int nx = (int)ceil_div(n, BT);
+    CMF_REQUIRE((long long)B * nx < (1LL << 31), "gram_bwd: grid too large");
+    dim3 grid((unsigned)(B * nx), (unsigned)ceil_div(d, BT));
+    gram_bwd_kernel<<<grid, kGemmThreads, 0, (cudaStream_t)stream>>>(d, n, nx, V, g_G, g_V);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}

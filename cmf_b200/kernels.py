@@ -1,0 +1,152 @@
+"""Tensor-level launchers over the C ABI (``include/cmf_b200.h``): validate, allocate outputs with
+torch (device memory + stream plumbing only), pass raw pointers.  Every function requires CUDA
+fp32 contiguous tensors and raises otherwise -- there is no CPU path.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+Tensor = torch.Tensor
+
+PENALTY = {"none": 0, "offdiag": 1, "diag": 2}
+
+
+def _ptr(t: Optional[Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _req(t: Tensor, name: str, dtype=torch.float32) -> Tensor:
+    if not t.is_cuda:
+        raise _lib.CmfB200Error(f"{name} must be a CUDA tensor (cmf_b200 has no CPU fallback)")
+    if t.dtype != dtype:
+        raise _lib.CmfB200Error(f"{name} must be {dtype}, got {t.dtype}")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def coupling_jvp_fwd(z_m: Tensor, V_m: Optional[Tensor], st: Tensor, ST: Optional[Tensor],
+                     map_: Optional[Tensor]) -> Tuple[Tensor, Optional[Tensor]]:
+    """z_m (B,M), V_m (B,d,M)|None, st (B,2Q), ST (B,d,2Q)|None, map (M,) int32|None."""
+    lib = _lib.load()
+    z_m, st = _req(z_m, "z_m"), _req(st, "st")
+    B, M = z_m.shape
+    Q = st.shape[1] // 2
+    d = 0 if V_m is None else V_m.shape[1]
+    if d:
+        V_m, ST = _req(V_m, "V_m"), _req(ST, "ST")
+        assert V_m.shape == (B, d, M) and ST.shape == (B, d, 2 * Q), (V_m.shape, ST.shape)
+    if map_ is not None:
+        map_ = _req(map_, "map", torch.int32)
+        assert map_.numel() == M
+    x_m = torch.empty_like(z_m)
+    V_out = torch.empty_like(V_m) if d else None
+    with torch.cuda.device(z_m.device):
+        _lib.check(lib.cmf_coupling_jvp_fwd(B, d, M, Q, _ptr(z_m), _ptr(V_m), _ptr(st), _ptr(ST),
+                                            _ptr(map_), _ptr(x_m), _ptr(V_out), _stream()),
+                   "cmf_coupling_jvp_fwd")
+    return x_m, V_out
+
+
+def coupling_jvp_bwd(z_m, V_m, st, ST, map_, inv, g_x, g_V):
+    """returns (g_z (B,M), g_Vin (B,d,M)|None, g_st (B,2Q), g_ST (B,d,2Q)|None)"""
+    lib = _lib.load()
+    z_m, st = _req(z_m, "z_m"), _req(st, "st")
+    B, M = z_m.shape
+    Q = st.shape[1] // 2
+    d = 0 if V_m is None else V_m.shape[1]
+    if d:
+        V_m, ST, g_V = _req(V_m, "V_m"), _req(ST, "ST"), _req(g_V, "g_V")
+    if g_x is not None:
+        g_x = _req(g_x, "g_x")
+    g_z, g_st = torch.empty_like(z_m), torch.empty_like(st)
+    g_Vin = torch.empty_like(V_m) if d else None
+    g_ST = torch.empty_like(ST) if d else None
+    nbytes = lib.cmf_coupling_jvp_bwd_workspace(B, d, M, Q)
+    ws = torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=z_m.device) if nbytes else None
+    with torch.cuda.device(z_m.device):
+        _lib.check(lib.cmf_coupling_jvp_bwd(B, d, M, Q, _ptr(z_m), _ptr(V_m), _ptr(st), _ptr(ST),
+                                            _ptr(map_), _ptr(inv), _ptr(g_x), _ptr(g_V),
+                                            _ptr(g_z), _ptr(g_Vin), _ptr(g_st), _ptr(g_ST),
+                                            _ptr(ws), nbytes, _stream()),
+                   "cmf_coupling_jvp_bwd")
+    return g_z, g_Vin, g_st, g_ST
+
+
+def gather_rows(in0: Tensor, in1: Optional[Tensor], idx: Tensor) -> Tensor:
+    """out[..., i] = idx[i] < 0 ? 0 : cat(in0, in1, -1)[..., idx[i]]; leading dims are rows."""
+    lib = _lib.load()
+    in0 = _req(in0, "in0")
+    idx = _req(idx, "idx", torch.int32)
+    lead = in0.shape[:-1]
+    n0 = in0.shape[-1]
+    n1 = 0
+    if in1 is not None:
+        in1 = _req(in1, "in1")
+        assert in1.shape[:-1] == lead
+        n1 = in1.shape[-1]
+    rows = 1
+    for s in lead:
+        rows *= s
+    out = torch.empty(*lead, idx.numel(), dtype=torch.float32, device=in0.device)
+    with torch.cuda.device(in0.device):
+        _lib.check(lib.cmf_gather_rows(rows, n0, n1, idx.numel(), _ptr(in0), _ptr(in1), _ptr(idx),
+                                       _ptr(out), _stream()), "cmf_gather_rows")
+    return out
+
+
+def gram_fwd(V: Tensor, G: Optional[Tensor] = None) -> Tensor:
+    """G (B,d,d) (+)= V V^T for V (B,d,n); accumulates into G when given."""
+    lib = _lib.load()
+    V = _req(V, "V")
+    B, d, n = V.shape
+    acc = G is not None
+    if G is None:
+        G = torch.empty(B, d, d, dtype=torch.float32, device=V.device)
+    with torch.cuda.device(V.device):
+        _lib.check(lib.cmf_gram_fwd(B, d, n, _ptr(V), _ptr(G), int(acc), _stream()), "cmf_gram_fwd")
+    return G
+
+
+def gram_bwd(V: Tensor, g_G: Tensor) -> Tensor:
+    lib = _lib.load()
+    V, g_G = _req(V, "V"), _req(g_G, "g_G")
+    B, d, n = V.shape
+    g_V = torch.empty_like(V)
+    with torch.cuda.device(V.device):
+        _lib.check(lib.cmf_gram_bwd(B, d, n, _ptr(V), _ptr(g_G), _ptr(g_V), _stream()), "cmf_gram_bwd")
+    return g_V
+
+
+def chol_logdet_fwd(G: Tensor):
+    """returns (L (B,d,d), logdet (B,), l1_off (B,), l1_diag (B,), info int32[1])"""
+    lib = _lib.load()
+    G = _req(G, "G")
+    B, d, _ = G.shape
+    L = torch.empty_like(G)
+    logdet = torch.empty(B, dtype=torch.float32, device=G.device)
+    l1_off, l1_diag = torch.empty_like(logdet), torch.empty_like(logdet)
+    info = torch.zeros(1, dtype=torch.int32, device=G.device)
+    with torch.cuda.device(G.device):
+        _lib.check(lib.cmf_chol_logdet_fwd(B, d, _ptr(G), _ptr(L), _ptr(logdet), _ptr(l1_off),
+                                           _ptr(l1_diag), _ptr(info), _stream()), "cmf_chol_logdet_fwd")
+    return L, logdet, l1_off, l1_diag, info
+
+
+def chol_logdet_bwd(L: Tensor, G: Tensor, g_logdet: Tensor, g_l1: Optional[Tensor], penalty: str) -> Tensor:
+    lib = _lib.load()
+    L, G, g_logdet = _req(L, "L"), _req(G, "G"), _req(g_logdet, "g_logdet")
+    if g_l1 is not None:
+        g_l1 = _req(g_l1, "g_l1")
+    B, d, _ = G.shape
+    g_G = torch.empty_like(G)
+    with torch.cuda.device(G.device):
+        _lib.check(lib.cmf_chol_logdet_bwd(B, d, _ptr(L), _ptr(G), _ptr(g_logdet), _ptr(g_l1),
+                                           PENALTY[penalty], _ptr(g_G), _stream()), "cmf_chol_logdet_bwd")
+    return g_G

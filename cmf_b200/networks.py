@@ -1,0 +1,184 @@
+"""Conditioner networks of the affine coupling layers, with *tangent-batched* JVPs.
+
+State-dict names and module indices match the reference (`networks.py:116-161,206-224`,
+`couplers.py:27-59`) so reference checkpoints load unchanged.  The JVP rules are the
+reference's (`jvp_layers.py:38-64`, `networks.py:62-79,108-113`): linear/conv tangents drop the
+bias, relu -> (x>0)*v, tanh -> (1-y^2)*v, scaled tanh -> w*v.  The difference is the schedule:
+the reference pushes ONE tangent column per call and recomputes the primal every time
+(`non_square.py:302-306`, d calls per layer); here the primal runs once on (B, ...) and all d
+tangents run as one library call on a (B*d, ...) tensor.  These are cuBLAS / cuDNN library calls
+ and ordinary autograd nodes; the hand-written kernels start where their outputs
+are consumed (``cmf_b200.ops.coupling_jvp``).
+"""
+from __future__ import annotations
+
+from typing import Sequence, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+Tensor = torch.Tensor
+
+
+def _bcast(t: Tensor) -> Tensor:
+    """(B, ...) -> (B, 1, ...) so a primal-derived factor broadcasts over the tangent axis."""
+    return t.unsqueeze(1)
+
+
+class TangentMLP(nn.Sequential):
+    """Linear / activation stack (`networks.py:206-224`); keys ``{2i}.weight``, ``{2i}.bias``."""
+
+    def __init__(self, num_in: int, hidden: Sequence[int], num_out: int, activation: str):
+        act = {"tanh": nn.Tanh, "relu": nn.ReLU}[activation]
+        layers, prev = [], num_in
+        for h in hidden:
+            layers += [nn.Linear(prev, h), act()]
+            prev = h
+        layers.append(nn.Linear(prev, num_out))
+        super().__init__(*layers)
+        self.activation = activation
+
+    def jvp_batched(self, x: Tensor, V: Tensor) -> Tuple[Tensor, Tensor]:
+        """x (B,p), V (B,d,p) -> y (B,o), Y (B,d,o)."""
+        for mod in self:
+            if isinstance(mod, nn.Linear):
+                x, V = mod(x), F.linear(V, mod.weight)
+            elif isinstance(mod, nn.Tanh):
+                x = torch.tanh(x)
+                V = V * _bcast(1 - x * x)
+            elif isinstance(mod, nn.ReLU):
+                V = V * _bcast((x > 0).to(V.dtype))
+                x = torch.relu(x)
+            else:
+                raise ValueError(f"jvp unsupported for module {type(mod).__name__}")
+        return x, V
+
+
+class ResidualBlock(nn.Module):
+    """relu-conv3x3-relu-conv3x3 + skip, no batch norm (`networks.py:35-94` with
+    ``use_batchnorm=False``, the only variant the non-square image config builds)."""
+
+    def __init__(self, channels: int):
+        super().__init__()
+        self.conv1 = nn.Conv2d(channels, channels, 3, padding=1, bias=True)
+        self.conv2 = nn.Conv2d(channels, channels, 3, padding=1, bias=True)
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self.conv2(torch.relu(self.conv1(torch.relu(x)))) + x
+
+    def jvp_batched(self, x: Tensor, V: Tensor, d: int) -> Tuple[Tensor, Tensor]:
+        """x (B,C,H,W), V (B*d,C,H,W)."""
+        h, Hv = x, V
+        for conv in (self.conv1, self.conv2):
+            Hv = _mask_rows(Hv, h > 0, d)
+            h = conv(torch.relu(h))
+            Hv = F.conv2d(Hv, conv.weight, None, padding=1)
+        return h + x, Hv + V
+
+
+def _mask_rows(V: Tensor, keep: Tensor, d: int) -> Tensor:
+    """V (B*d, ...) * keep (B, ...) broadcast over the d tangents of each sample."""
+    B = keep.shape[0]
+    return (V.view(B, d, *V.shape[1:]) * _bcast(keep.to(V.dtype))).view_as(V)
+
+
+class ScaledTanhResNet(nn.Module):
+    """`networks.py:116-161` (get_resnet, no BN) inside `networks.py:96-113` (ScaledTanh2dModule).
+    Keys: ``weights``, ``bias``, ``module.0.weight``, ``module.{i}.conv{1,2}.*``, ``module.{n+2}.*``."""
+
+    def __init__(self, num_in: int, hidden: Sequence[int], num_out: int):
+        super().__init__()
+        hidden = list(hidden)
+        width = hidden[0] if hidden else num_out
+        layers = [nn.Conv2d(num_in, width, 3, padding=1, bias=False)]
+        for width in hidden:
+            layers.append(ResidualBlock(width))
+        layers += [nn.ReLU(), nn.Conv2d(width, num_out, 1, bias=True)]
+        self.module = nn.Sequential(*layers)
+        self.weights = nn.Parameter(torch.ones(num_out, 1, 1))
+        self.bias = nn.Parameter(torch.zeros(num_out, 1, 1))
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self.weights * torch.tanh(self.module(x)) + self.bias
+
+    def jvp_batched(self, x: Tensor, V: Tensor) -> Tuple[Tensor, Tensor]:
+        """x (B,C,H,W), V (B,d,C,H,W) -> y (B,O,H,W), Y (B,d,O,H,W)."""
+        B, d = V.shape[:2]
+        Hv = V.reshape(B * d, *V.shape[2:])
+        h = x
+        for mod in self.module:
+            if isinstance(mod, ResidualBlock):
+                h, Hv = mod.jvp_batched(h, Hv, d)
+            elif isinstance(mod, nn.Conv2d):
+                Hv = F.conv2d(Hv, mod.weight, None, stride=mod.stride, padding=mod.padding)
+                h = mod(h)
+            elif isinstance(mod, nn.ReLU):
+                Hv = _mask_rows(Hv, h > 0, d)
+                h = torch.relu(h)
+            else:
+                raise ValueError(f"jvp unsupported for module {type(mod).__name__}")
+        y = torch.tanh(h)
+        Hv = Hv.view(B, d, *Hv.shape[1:]) * _bcast((1 - y * y) * self.weights)
+        return self.weights * y + self.bias, Hv
+
+
+def make_coupler_net(in_shape, num_out: int, cfg: dict) -> nn.Module:
+    """`factory.py:467-507` for the net types reachable from ``--model non-square``."""
+    if cfg["type"] == "mlp":
+        assert len(in_shape) == 1
+        return TangentMLP(in_shape[0], cfg["hidden_channels"], num_out, cfg["activation"])
+    if cfg["type"] == "resnet":
+        assert len(in_shape) == 3
+        if cfg.get("batchnorm", True):
+            raise ValueError("resnet batchnorm is not on the non-square path "
+                             "(config/images.py:128 sets resnet_batchnorm=False)")
+        return ScaledTanhResNet(in_shape[0], cfg["hidden_channels"], num_out)
+    raise ValueError(f"Invalid net type {cfg['type']} for the non-square JVP path")
+
+
+class ChunkedSharedCoupler(nn.Module):
+    """One net; channel halves of its output are (shift, log-scale) (`couplers.py:27-59`)."""
+
+    def __init__(self, net: nn.Module):
+        super().__init__()
+        self.shift_log_scale_net = net
+
+    def forward(self, x: Tensor):
+        y = self.shift_log_scale_net(x)
+        c = y.shape[1] // 2
+        return {"shift": y[:, :c], "log-scale": y[:, c:]}
+
+    def st_batched(self, x: Tensor, V):
+        """Flat conditioner outputs for the coupling kernel: st (B,2Q) = [shift | log_scale]
+        and, if V (B,d,...) is given, ST (B,d,2Q)."""
+        if V is None:
+            return self.shift_log_scale_net(x).flatten(1), None
+        y, Y = self.shift_log_scale_net.jvp_batched(x, V)
+        return y.flatten(1), Y.flatten(2)
+
+
+class IndependentCoupler(nn.Module):
+    """Separate shift / log-scale nets (`couplers.py:6-24`)."""
+
+    def __init__(self, shift_net: nn.Module, log_scale_net: nn.Module):
+        super().__init__()
+        self.shift_net, self.log_scale_net = shift_net, log_scale_net
+
+    def forward(self, x: Tensor):
+        return {"shift": self.shift_net(x), "log-scale": self.log_scale_net(x)}
+
+    def st_batched(self, x: Tensor, V):
+        if V is None:
+            return torch.cat((self.shift_net(x).flatten(1), self.log_scale_net(x).flatten(1)), 1), None
+        t, T = self.shift_net.jvp_batched(x, V)
+        s, S = self.log_scale_net.jvp_batched(x, V)
+        return torch.cat((t.flatten(1), s.flatten(1)), 1), torch.cat((T.flatten(2), S.flatten(2)), 2)
+
+
+def make_coupler(in_shape, channels_per_output: int, cfg: dict) -> nn.Module:
+    """`factory.py:413-464`."""
+    if cfg["independent_nets"]:
+        return IndependentCoupler(make_coupler_net(in_shape, channels_per_output, cfg["shift_net"]),
+                                  make_coupler_net(in_shape, channels_per_output, cfg["log_scale_net"]))
+    return ChunkedSharedCoupler(make_coupler_net(in_shape, 2 * channels_per_output, cfg["shift_log_scale_net"]))

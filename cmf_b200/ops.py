@@ -1,0 +1,139 @@
+"""``torch.autograd.Function`` ops over the sm_100a kernels (through ``cmf_b200.kernels`` ->
+C ABI).  These are the only places the hot path touches the GPU outside the conditioner
+networks' library calls.
+
+Only first-order adjoints are needed: the reference's "double backward" is one reverse pass over
+a graph whose nodes are JVPs (`trainer.py:216`, `non_square.py:298-311`), and each op here is one
+such node with an explicit adjoint w.r.t. primal *and* tangent inputs.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence, Tuple
+
+import torch
+from torch.autograd import Function
+
+from . import kernels
+
+Tensor = torch.Tensor
+
+
+class NotPositiveDefiniteError(RuntimeError):
+    """Raised where ``torch.linalg.cholesky`` raises in the reference (`non_square.py:282-288`)."""
+
+
+class _CouplingJVP(Function):
+    @staticmethod
+    def forward(ctx, z_m, V_m, st, ST, map_, inv):
+        x_m, V_out = kernels.coupling_jvp_fwd(z_m, V_m, st, ST, map_)
+        ctx.save_for_backward(z_m, V_m, st, ST)
+        ctx.maps = (map_, inv)
+        ctx.set_materialize_grads(False)
+        if V_out is None:
+            ctx.mark_non_differentiable()
+            return x_m, None
+        return x_m, V_out
+
+    @staticmethod
+    def backward(ctx, g_x, g_V):
+        z_m, V_m, st, ST = ctx.saved_tensors
+        map_, inv = ctx.maps
+        if V_m is not None and g_V is None:
+            g_V = torch.zeros_like(V_m)
+        g_z, g_Vin, g_st, g_ST = kernels.coupling_jvp_bwd(z_m, V_m, st, ST, map_, inv, g_x, g_V)
+        return g_z, g_Vin, g_st, g_ST, None, None
+
+
+def coupling_jvp(z_m: Tensor, V_m: Optional[Tensor], st: Tensor, ST: Optional[Tensor],
+                 map_: Optional[Tensor] = None, inv: Optional[Tensor] = None) -> Tuple[Tensor, Optional[Tensor]]:
+    """Affine coupling on the compact transformed half, primal + d tangents (acl.py:53-66,125-146).
+
+    z_m (B,M), V_m (B,d,M) or None (primal only, acl.py:48-51), st (B,2Q) = [shift | log_scale],
+    ST (B,d,2Q) their tangents; ``map_``/``inv`` (int32) relate compact index j to conditioner
+    position q when the conditioner emits more positions than are transformed (checkerboard)."""
+    return _CouplingJVP.apply(z_m, V_m, st, ST, map_, inv)
+
+
+class _GatherRows(Function):
+    @staticmethod
+    def forward(ctx, in0, in1, idx, inv0, inv1):
+        ctx.inv = (inv0, inv1)
+        ctx.has1 = in1 is not None
+        return kernels.gather_rows(in0, in1, idx)
+
+    @staticmethod
+    def backward(ctx, g):
+        inv0, inv1 = ctx.inv
+        g0 = kernels.gather_rows(g, None, inv0) if ctx.needs_input_grad[0] else None
+        g1 = kernels.gather_rows(g, None, inv1) if (ctx.has1 and ctx.needs_input_grad[1]) else None
+        return g0, g1, None, None, None
+
+
+def gather_rows(in0: Tensor, in1: Optional[Tensor], idx: Tensor, inv0: Tensor,
+                inv1: Optional[Tensor] = None) -> Tensor:
+    """out[..., i] = idx[i] < 0 ? 0 : cat(in0, in1)[..., idx[i]].  ``inv0``/``inv1`` are the
+    adjoint maps: for source element s of in0 (in1), the output slot that reads it, or -1."""
+    return _GatherRows.apply(in0, in1, idx, inv0, inv1)
+
+
+class _Gram(Function):
+    @staticmethod
+    def forward(ctx, *blocks):
+        G = None
+        for V in blocks:
+            G = kernels.gram_fwd(V, G)
+        ctx.save_for_backward(*blocks)
+        return G
+
+    @staticmethod
+    def backward(ctx, g_G):
+        g_G = g_G.contiguous()
+        return tuple(kernels.gram_bwd(V, g_G) if need else None
+                     for V, need in zip(ctx.saved_tensors, ctx.needs_input_grad))
+
+
+def gram(blocks: Sequence[Tensor]) -> Tensor:
+    """G = sum_i V_i V_i^T over the compact blocks V_i (B,d,n_i) of J^T (non_square.py:307-308)."""
+    return _Gram.apply(*blocks)
+
+
+class _CholLogdetL1(Function):
+    @staticmethod
+    def forward(ctx, G, penalty):
+        L, logdet, l1_off, l1_diag, info = kernels.chol_logdet_fwd(G)
+        ctx.save_for_backward(L, G)
+        ctx.penalty = penalty
+        l1 = l1_off if penalty == "offdiag" else l1_diag
+        ctx.mark_non_differentiable(info)
+        ctx.set_materialize_grads(False)
+        return logdet.unsqueeze(1), l1.unsqueeze(1), info
+
+    @staticmethod
+    def backward(ctx, g_logdet, g_l1, _g_info):
+        L, G = ctx.saved_tensors
+        B = G.shape[0]
+        if g_logdet is None:
+            g_logdet = torch.zeros(B, dtype=G.dtype, device=G.device)
+        penalty = ctx.penalty if g_l1 is not None else "none"
+        g_G = kernels.chol_logdet_bwd(L, G, g_logdet.reshape(B).contiguous(),
+                                      None if g_l1 is None else g_l1.reshape(B).contiguous(), penalty)
+        return g_G, None
+
+
+def chol_logdet_l1(G: Tensor, penalty: str = "none") -> Tuple[Tensor, Tensor]:
+    """(log det G (B,1), metric penalty (B,1)) for penalty in {"none","offdiag","diag"}.
+
+    Raises :class:`NotPositiveDefiniteError` exactly where the reference's
+    ``torch.linalg.cholesky`` raises, so the caller can replay the ``+eps*I`` retry loop of
+    `non_square.py:280-288`.  Reading ``info`` is the one host sync of the path (the reference
+    syncs at the same place: cuSOLVER's potrf info check)."""
+    if penalty not in kernels.PENALTY:
+        raise ValueError(f"unknown penalty {penalty}")
+    logdet, l1, info = _CholLogdetL1.apply(G, penalty)
+    bad = int(info.item())
+    if bad:
+        raise NotPositiveDefiniteError(
+            f"cmf_chol_logdet_fwd: leading minor not positive for sample {bad - 1}")
+    if penalty == "none":
+        l1 = torch.zeros_like(logdet)
+    return logdet, l1

@@ -1,0 +1,284 @@
+"""Layer program: the z -> x half of the non-square flow compiled once into a list of kernel
+steps (replaces the Python walk of `non_square.py:146-184` that rebuilds ``jvp_stack`` /
+``transform_stack`` every call, and the d-fold loop of `non_square.py:298-311`).
+
+Data layout.  At every point of the flow the logical per-sample tensor (flattened size D) is held
+as a few COMPACT blocks: block i stores ``n_i`` elements whose logical flat positions are the
+static vector ``pos_i``; a block may be a *zero block* (no storage: zero-padding of
+`non_square.py:397-404` and `split.py:50-52`).  The primal of a block is ``x (B, n_i)``, its
+tangents ``V (B, d, n_i)`` -- tangent index next to the batch, so the conditioner call is a free
+``view(B*d, C, H, W)`` and ``G = sum_i V_i V_i^T`` reads both operands K-major from one buffer.
+
+Consequences:
+  * reshapes / squeeze / flatten / split-pad / tail-pad never move data: they only rewrite
+    ``pos_i`` at compile time (`reshaping.py:28-29`, `split.py:26-30`, `non_square.py:406-410`);
+  * a coupling layer reads and writes ONLY the half it transforms (kernel (a) traffic equals the
+    algorithmic 16 M (1+d) bytes/sample forward); the passthrough half is passed on by reference;
+  * when consecutive layers use different partitions (tail permutation -> checkerboard ->
+    split-channel -> checkerboard) blocks are re-grouped by one gather kernel; in the steady state
+    (alternating masks) nothing is copied.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import ops
+from .bijections import AffineCouplingBijection, ReshapingBijection
+from .densities import BijectionDensity, NonSquareTailDensity, SplitDensity
+
+Tensor = torch.Tensor
+
+
+@dataclass
+class SymBlock:
+    slot: Optional[int]          # runtime slot holding (x, V); None for a zero block
+    pos: np.ndarray              # (n,) int64 logical flat positions, in storage order
+
+    @property
+    def zero(self) -> bool:
+        return self.slot is None
+
+
+@dataclass
+class GatherStep:
+    out: int
+    srcs: Tuple[int, ...]        # 1 or 2 source slots
+    idx: np.ndarray              # (n_out,) int32 into cat(srcs) or -1
+    invs: Tuple[np.ndarray, ...]  # per source: (n_src,) int32 output index or -1
+
+
+@dataclass
+class ZerosStep:
+    out: int
+    n: int
+
+
+@dataclass
+class AclStep:
+    bijection: AffineCouplingBijection
+    cond: int                    # slot holding the conditioner input (B, n_in)
+    in_shape: tuple
+    mod: int                     # slot holding the compact half to transform
+    out: int
+    map: Optional[np.ndarray]    # (M,) int32 conditioner position of compact element j (None = identity)
+    inv: Optional[np.ndarray]    # (Q,) int32 compact index of conditioner position q or -1
+    M: int = 0
+    Q: int = 0
+
+
+class LayerProgram:
+    def __init__(self, head_prior):
+        """``head_prior``: the density subtree below the head (``head.prior``)."""
+        self.nodes, self.tail = self._collect(head_prior)
+        self.d = self.tail.latent_dimension
+        self.steps: List[object] = []
+        self._n_slots = 0
+        self._dev_cache: Dict[Tuple[int, str], Tensor] = {}
+        self._compile()
+
+    # ------------------------------------------------------------------ tree walk
+    @staticmethod
+    def _collect(node):
+        """x -> z list of nodes between the head and the tail; ValueError exactly where
+        `non_square.py:160-168` raises."""
+        nodes = []
+        while not isinstance(node, NonSquareTailDensity):
+            if isinstance(node, BijectionDensity):
+                bij = node.bijection
+                if not isinstance(bij, (AffineCouplingBijection, ReshapingBijection)):
+                    raise ValueError(f"Cannot handle bijection of class {type(bij).__name__} on the JVP path")
+                nodes.append(bij)
+                node = node.prior
+            elif isinstance(node, SplitDensity):
+                if not node.non_square:
+                    raise ValueError("Cannot handle a square SplitDensity on the non-square JVP path")
+                nodes.append(node)
+                node = node.density_1
+            else:
+                raise ValueError(f"Cannot handle density of class {type(node).__name__}")
+        return nodes, node
+
+    # ------------------------------------------------------------------ compile
+    def _new_slot(self) -> int:
+        self._n_slots += 1
+        return self._n_slots - 1
+
+    def _compile(self):
+        tail = self.tail
+        D, d = tail.flattened_dims, self.d
+        perm = tail.permutation.detach().cpu().numpy().astype(np.int64)
+        # z_k sits at logical position perm[k]; everything else is zero padding (non_square.py:397-404)
+        blocks = [SymBlock(self._new_slot(), perm[:d].copy())]
+        if D > d:
+            blocks.append(SymBlock(None, np.sort(perm[d:])))
+        for node in reversed(self.nodes):
+            if isinstance(node, ReshapingBijection):
+                probe = torch.arange(D).view(1, *node.z_shape)
+                src = node.reshape_z(probe).flatten().numpy()      # x[p] = z[src[p]]
+                new_pos = np.empty(D, dtype=np.int64)
+                new_pos[src] = np.arange(D)
+                for b in blocks:
+                    b.pos = new_pos[b.pos]
+            elif isinstance(node, SplitDensity):
+                assert node.dim == 1
+                blocks.append(SymBlock(None, np.arange(D, 2 * D, dtype=np.int64)))
+                D *= 2
+            else:
+                blocks = self._compile_acl(node, blocks, D)
+        self.final_blocks = blocks
+        self.D = D
+
+    def _compile_acl(self, bij, blocks: List[SymBlock], D: int) -> List[SymBlock]:
+        keep_pos, mod_pos, in_shape, dense = bij.partition()
+        keep_pos = keep_pos.cpu().numpy().astype(np.int64)
+        mod_pos = mod_pos.cpu().numpy().astype(np.int64)
+        is_mod = np.zeros(D, dtype=bool)
+        is_mod[mod_pos] = True
+        # 1. no block may straddle the partition
+        conformed: List[SymBlock] = []
+        for b in blocks:
+            m = is_mod[b.pos]
+            if m.all() or not m.any():
+                conformed.append(b)
+            elif b.zero:
+                conformed += [SymBlock(None, b.pos[~m]), SymBlock(None, b.pos[m])]
+            else:
+                for sel in (~m, m):
+                    sub = np.nonzero(sel)[0]
+                    inv = np.full(b.pos.size, -1, dtype=np.int32)
+                    inv[sub] = np.arange(sub.size, dtype=np.int32)
+                    out = self._new_slot()
+                    self.steps.append(GatherStep(out, (b.slot,), sub.astype(np.int32), (inv,)))
+                    conformed.append(SymBlock(out, b.pos[sel]))
+        keep_blocks = [b for b in conformed if not is_mod[b.pos[0]]]
+        mod_blocks = [b for b in conformed if is_mod[b.pos[0]]]
+        # 2. conditioner input: dense x_shape tensor with modified positions zeroed, or the compact
+        #    passthrough tensor in natural order
+        if dense:
+            target = np.arange(D, dtype=np.int64)
+            target[is_mod] = -1
+        else:
+            target = keep_pos
+        cond = self._assemble(keep_blocks, target, D)
+        # 3. the compact half to transform, in conditioner-output order
+        mod = self._assemble(mod_blocks, mod_pos, D)
+        # 4. relation between compact index j and conditioner position q
+        if dense:
+            cmap = mod_pos.astype(np.int32)
+            cinv = np.full(D, -1, dtype=np.int32)
+            cinv[mod_pos] = np.arange(mod_pos.size, dtype=np.int32)
+            Q = D
+        else:
+            cmap, cinv, Q = None, None, mod_pos.size
+        out = self._new_slot()
+        self.steps.append(AclStep(bij, cond, tuple(in_shape), mod, out, cmap, cinv, mod_pos.size, Q))
+        return keep_blocks + [SymBlock(out, mod_pos)]
+
+    def _assemble(self, blocks: Sequence[SymBlock], target: np.ndarray, D: int) -> int:
+        """Slot whose element i is the value at logical position target[i] (0 where target[i] < 0
+        or the position belongs to a zero block)."""
+        real = [b for b in blocks if not b.zero]
+        if len(real) == 1 and real[0].pos.size == target.size and np.array_equal(real[0].pos, target):
+            return real[0].slot
+        if not real:
+            out = self._new_slot()
+            self.steps.append(ZerosStep(out, int(target.size)))
+            return out
+        while len(real) > 2:          # concatenate pairwise until two sources remain
+            a, b = real.pop(), real.pop()
+            out = self._new_slot()
+            na, nb = a.pos.size, b.pos.size
+            self.steps.append(GatherStep(out, (a.slot, b.slot), np.arange(na + nb, dtype=np.int32),
+                                         (np.arange(na, dtype=np.int32), np.arange(na, na + nb, dtype=np.int32))))
+            real.append(SymBlock(out, np.concatenate([a.pos, b.pos])))
+        where = np.full(D, -1, dtype=np.int64)   # logical position -> index into cat(real)
+        base = 0
+        for b in real:
+            where[b.pos] = base + np.arange(b.pos.size)
+            base += b.pos.size
+        idx = np.where(target >= 0, where[np.maximum(target, 0)], -1).astype(np.int32)
+        invs, base = [], 0
+        for b in real:
+            inv = np.full(b.pos.size, -1, dtype=np.int32)
+            hit = (idx >= base) & (idx < base + b.pos.size)
+            inv[idx[hit] - base] = np.nonzero(hit)[0].astype(np.int32)
+            invs.append(inv)
+            base += b.pos.size
+        out = self._new_slot()
+        self.steps.append(GatherStep(out, tuple(b.slot for b in real), idx, tuple(invs)))
+        return out
+
+    # ------------------------------------------------------------------ run
+    def _dev(self, arr: Optional[np.ndarray], device, key, dtype=torch.int32) -> Optional[Tensor]:
+        if arr is None:
+            return None
+        k = (key, str(device))
+        t = self._dev_cache.get(k)
+        if t is None:
+            t = torch.as_tensor(arr, dtype=dtype, device=device)
+            self._dev_cache[k] = t
+        return t
+
+    def run(self, z: Tensor, V0: Optional[Tensor]):
+        """Push z (B,d) and tangents V0 (B,m,d) (None = primal only, `non_square.py:313-320`)
+        through the flow.  Returns ``[(pos (n,) int64 device tensor, x (B,n), V (B,m,n)|None)]`` for
+        the non-zero final blocks and the positions of the final zero blocks."""
+        dev = z.device
+        B = z.shape[0]
+        m = None if V0 is None else V0.shape[1]
+        slots: Dict[int, Tuple[Tensor, Optional[Tensor]]] = {0: (z.contiguous(), V0)}
+        for si, step in enumerate(self.steps):
+            if isinstance(step, GatherStep):
+                xs = [slots[s][0] for s in step.srcs]
+                vs = [slots[s][1] for s in step.srcs]
+                idx = self._dev(step.idx, dev, (si, "idx"))
+                invs = [self._dev(a, dev, (si, "inv", i)) for i, a in enumerate(step.invs)]
+                x1 = xs[1] if len(xs) > 1 else None
+                i1 = invs[1] if len(invs) > 1 else None
+                x = ops.gather_rows(xs[0], x1, idx, invs[0], i1)
+                V = None
+                if m is not None:
+                    V = ops.gather_rows(vs[0], vs[1] if len(vs) > 1 else None, idx, invs[0], i1)
+                slots[step.out] = (x, V)
+            elif isinstance(step, ZerosStep):
+                x = torch.zeros(B, step.n, dtype=z.dtype, device=dev)
+                V = None if m is None else torch.zeros(B, m, step.n, dtype=z.dtype, device=dev)
+                slots[step.out] = (x, V)
+            else:
+                xc, Vc = slots[step.cond]
+                x_in = xc.view(B, *step.in_shape)
+                V_in = None if m is None else Vc.view(B, m, *step.in_shape)
+                st, ST = step.bijection.coupler.st_batched(x_in, V_in)
+                z_m, V_m = slots[step.mod]
+                slots[step.out] = ops.coupling_jvp(z_m, V_m, st, ST,
+                                                   self._dev(step.map, dev, (si, "map")),
+                                                   self._dev(step.inv, dev, (si, "cinv")))
+        out, zero_pos = [], []
+        for bi, b in enumerate(self.final_blocks):
+            pos = self._dev(b.pos, dev, ("final", bi), torch.int64)
+            if b.zero:
+                zero_pos.append(pos)
+            else:
+                out.append((pos, *slots[b.slot]))
+        return out, zero_pos
+
+    # ------------------------------------------------------------------ introspection
+    def describe(self) -> List[str]:
+        lines = []
+        for s in self.steps:
+            if isinstance(s, GatherStep):
+                lines.append(f"gather  {s.srcs} -> {s.out}  n_out={s.idx.size}")
+            elif isinstance(s, ZerosStep):
+                lines.append(f"zeros   -> {s.out}  n={s.n}")
+            else:
+                lines.append(f"acl     {type(s.bijection).__name__}: cond={s.cond} mod={s.mod} -> {s.out}  "
+                             f"M={s.M} Q={s.Q} {'mapped' if s.map is not None else 'identity'}")
+        return lines
+
+    def modified_elements(self) -> int:
+        """sum_l M_l, the factor of the kernel-(a) byte model."""
+        return sum(s.M for s in self.steps if isinstance(s, AclStep))

@@ -1,0 +1,101 @@
+/* cmf_b200 -- C ABI of the B200 (sm_100a) kernels behind the non-square log-det hot path of
+ * Canonical Manifold Flows (k-flouris/cmf).
+ *
+ * This header is the drop-in boundary.  Every entry point takes plain device pointers and
+ * sizes (no torch types), launches on the caller's stream, allocates nothing, keeps no state
+ * between calls and never synchronises.  All tensors are dense row-major fp32 unless noted.
+ * Return value: 0 = ok, <0 = bad argument (see cmf_last_error_string), >0 = cudaError_t.
+ *
+ * Which reference code each entry point replaces is cited as path:line relative to the
+ * reference checkout (cmf/... = cmf/models/components/...).
+ *
+ * Layout conventions
+ *   B   samples in the (per-GPU) batch shard
+ *   d   tangent columns carried next to the primal (latent dimension, or Hutchinson probes)
+ *   M   elements of the half a coupling layer transforms, stored COMPACT: z_m (B,M), V_m (B,d,M)
+ *   Q   elements of one conditioner output ("shift" or "log-scale") per sample; the
+ *       conditioner emits (B, 2Q): shift = [0,Q), log-scale = [Q,2Q)  (couplers.py:52-59)
+ *   map (M) int32: position in [0,Q) of compact element j (NULL = identity, requires M == Q)
+ *   inv (Q) int32: compact index of conditioner position q, or -1 (NULL = identity)
+ */
+#ifndef CMF_B200_H
+#define CMF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* cmf_stream_t; /* a cudaStream_t */
+
+#define CMF_B200_ABI_VERSION 1
+
+#define CMF_PENALTY_NONE    0
+#define CMF_PENALTY_OFFDIAG 1 /* sum_{i!=j} |G_ij|  non_square.py:95-100 (g_ij_loss) */
+#define CMF_PENALTY_DIAG    2 /* sum_k |G_kk|       non_square.py:87-92  (g_kk_loss) */
+
+int cmf_version(void);
+const char* cmf_last_error_string(void);
+
+/* (a) Affine coupling, primal + all d tangent columns in one pass.
+ * Replaces acl.py:53-66 (checkerboard _jvp), acl.py:125-146 (channelwise _jvp) called d times
+ * from non_square.py:298-311, and with d == 0 the primal-only acl.py:48-51,113-123 (_z_to_x)
+ * used by flow_forward (non_square.py:313-320).
+ *   e      = exp(-log_scale)
+ *   x_m    = z_m * e - shift
+ *   V_out  = e * (V_m - z_m * log_scale_dot) - shift_dot
+ */
+int cmf_coupling_jvp_fwd(int B, int d, int M, int Q,
+                         const float* z_m, const float* V_m,
+                         const float* st, const float* ST, const int32_t* map,
+                         float* x_m, float* V_out, cmf_stream_t stream);
+
+/* Adjoint of cmf_coupling_jvp_fwd (what autograd derives from the ~10 ATen ops per layer per
+ * column of acl.py:53-66 / :125-146).  g_x may be NULL (treated as zero).  g_st (B,2Q) and
+ * g_ST (B,d,2Q) are written densely (zeros where inv[q] < 0).  workspace must hold
+ * cmf_coupling_jvp_bwd_workspace(B,d,M,Q) bytes (may be 0). */
+size_t cmf_coupling_jvp_bwd_workspace(int B, int d, int M, int Q);
+int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
+                         const float* z_m, const float* V_m,
+                         const float* st, const float* ST, const int32_t* map, const int32_t* inv,
+                         const float* g_x, const float* g_V,
+                         float* g_z, float* g_Vin, float* g_st, float* g_ST,
+                         void* workspace, size_t workspace_bytes, cmf_stream_t stream);
+
+/* Index maps folded into addressing: out[r, i] = idx[i] < 0 ? 0 : cat(in0, in1)[r, idx[i]].
+ * Replaces the zero-pad / permute / squeeze / split copies of non_square.py:397-410,
+ * split.py:26-30,50-52, reshaping.py:28-29,102-114 and the mask*z products of acl.py:54.
+ * in1 may be NULL (n1 = 0).  idx must be injective on its non-negative entries. */
+int cmf_gather_rows(long long rows, int n0, int n1, int n_out,
+                    const float* in0, const float* in1, const int32_t* idx,
+                    float* out, cmf_stream_t stream);
+
+/* (b) Per-sample metric G = J^T J with tangents stored as V (B,d,n) (V = J^T, row k = column k
+ * of J restricted to this block): G[b] (+)= V[b] V[b]^T.  Replaces torch.stack + torch.bmm of
+ * non_square.py:307-308.  accumulate != 0 adds into G (several blocks of one sample). */
+int cmf_gram_fwd(int B, int d, int n, const float* V, float* G, int accumulate, cmf_stream_t stream);
+
+/* Adjoint: g_V[b] = (g_G[b] + g_G[b]^T) V[b]   (B,d,n). */
+int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream);
+
+/* (c) Batched Cholesky log-det + metric penalties.  Replaces torch.linalg.cholesky + diagonal +
+ * log + sum (non_square.py:282,293-294) and masked_select + vector_norm (non_square.py:95-100,
+ * :87-92).  Outputs: L (B,d,d) lower factor (upper triangle zero), logdet (B) = 2 sum log L_kk,
+ * l1_off (B), l1_diag (B).  info (1 int32, device, MUST be zeroed by the caller): set to
+ * 1 + index of a sample whose leading minor is not positive (the RuntimeError of
+ * non_square.py:283-288); the host then adds eps*I and retries like the reference. d <= 128. */
+int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float* logdet,
+                        float* l1_off, float* l1_diag, int32_t* info, cmf_stream_t stream);
+
+/* Adjoint: g_G = g_logdet * G^{-1} + g_l1 * sign(G) (.) mask(penalty)   (B,d,d), with G^{-1}
+ * rebuilt from L in shared memory.  g_l1 may be NULL when penalty == CMF_PENALTY_NONE. */
+int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
+                        const float* g_logdet, const float* g_l1, int penalty,
+                        float* g_G, cmf_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CMF_B200_H */

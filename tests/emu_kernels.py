@@ -1,0 +1,98 @@
+"""Plain-torch stand-ins for ``cmf_b200.kernels`` (TEST INFRASTRUCTURE ONLY).
+
+The product has no CPU path; these emulate each C-ABI launcher's *contract* (same arguments,
+shapes and index-map semantics as include/cmf_b200.h) so the host logic -- layer program,
+autograd wiring, head, sharding -- can be exercised on the GPU-less build container.  They are
+installed by the ``emu`` fixture through monkeypatching and are never importable from cmf_b200.
+"""
+import torch
+
+PENALTY = {"none": 0, "offdiag": 1, "diag": 2}
+
+
+def _maps(M, Q, map_, dev):
+    return torch.arange(M, device=dev) if map_ is None else map_.long()
+
+
+def coupling_jvp_fwd(z_m, V_m, st, ST, map_):
+    B, M = z_m.shape
+    Q = st.shape[1] // 2
+    q = _maps(M, Q, map_, z_m.device)
+    t, s = st[:, :Q][:, q], st[:, Q:][:, q]
+    e = torch.exp(-s)
+    x = z_m * e - t
+    if V_m is None:
+        return x, None
+    T, S = ST[:, :, :Q][:, :, q], ST[:, :, Q:][:, :, q]
+    return x, e.unsqueeze(1) * (V_m - z_m.unsqueeze(1) * S) - T
+
+
+def coupling_jvp_bwd(z_m, V_m, st, ST, map_, inv, g_x, g_V):
+    B, M = z_m.shape
+    Q = st.shape[1] // 2
+    q = _maps(M, Q, map_, z_m.device)
+    s = st[:, Q:][:, q]
+    e = torch.exp(-s)
+    gx = torch.zeros_like(z_m) if g_x is None else g_x
+    g_st = torch.zeros_like(st)
+    if V_m is None:
+        A = C = torch.zeros_like(z_m)
+        g_Vin = g_ST = None
+    else:
+        S = ST[:, :, Q:][:, :, q]
+        A, C = (S * g_V).sum(1), (V_m * g_V).sum(1)
+        g_Vin = e.unsqueeze(1) * g_V
+        g_ST = torch.zeros_like(ST)
+        g_ST[:, :, q] = -g_V
+        g_ST[:, :, Q + q] = -(e * z_m).unsqueeze(1) * g_V
+    g_z = e * (gx - A)
+    g_st[:, q] = -gx
+    g_st[:, Q + q] = -z_m * e * gx - e * (C - z_m * A)
+    return g_z, g_Vin, g_st, g_ST
+
+
+def gather_rows(in0, in1, idx):
+    src = in0 if in1 is None else torch.cat((in0, in1), dim=-1)
+    idx = idx.long()
+    out = src[..., idx.clamp(min=0)]
+    return torch.where(idx >= 0, out, torch.zeros((), dtype=out.dtype))
+
+
+def gram_fwd(V, G=None):
+    g = V @ V.transpose(1, 2)
+    if G is None:
+        return g
+    G += g
+    return G
+
+
+def gram_bwd(V, g_G):
+    return (g_G + g_G.transpose(1, 2)) @ V
+
+
+def chol_logdet_fwd(G):
+    B, d, _ = G.shape
+    L, info_each = torch.linalg.cholesky_ex(G)
+    bad = (info_each != 0).nonzero()
+    info = torch.zeros(1, dtype=torch.int32)
+    if bad.numel():
+        info[0] = int(bad.max()) + 1
+    logdet = 2 * torch.log(torch.diagonal(L, dim1=-2, dim2=-1)).sum(1)
+    diag = torch.diagonal(G, dim1=-2, dim2=-1).abs().sum(1)
+    off = G.abs().sum((1, 2)) - diag
+    return L, logdet, off, diag, info
+
+
+def chol_logdet_bwd(L, G, g_logdet, g_l1, penalty):
+    d = G.shape[1]
+    Ginv = torch.cholesky_inverse(L)
+    out = g_logdet.view(-1, 1, 1) * Ginv
+    if penalty != "none" and g_l1 is not None:
+        eye = torch.eye(d, dtype=torch.bool)
+        mask = ~eye if penalty == "offdiag" else eye
+        out = out + g_l1.view(-1, 1, 1) * torch.sign(G) * mask
+    return out
+
+
+ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_bwd",
+       "chol_logdet_fwd", "chol_logdet_bwd"]

@@ -1,0 +1,93 @@
+"""Host logic on CPU: the layer program, autograd wiring and fused head, with the CUDA launchers
+replaced by torch emulations of their C-ABI contracts (tests/emu_kernels.py).  What is checked
+here is everything ABOVE the kernels; the kernels themselves are checked on the GPU box."""
+import pytest
+import torch
+
+import emu_kernels
+from conftest import load_golden
+from cases import CASES, make_input
+from helpers import build_product, run_loss, check_against_golden, strip_wrappers, find_head, assert_close
+
+FAST = [n for n, c in CASES.items() if not c.get("slow")]
+
+
+@pytest.fixture
+def emu(monkeypatch):
+    import cmf_b200.kernels as K
+    for name in emu_kernels.ALL:
+        monkeypatch.setattr(K, name, getattr(emu_kernels, name))
+    return K
+
+
+@pytest.mark.parametrize("name", FAST)
+def test_fused_head_matches_reference_golden(emu, name):
+    g = load_golden(name)
+    density = build_product(g)
+    loss, grads = run_loss(g, density)
+    check_against_golden(g, loss, grads, rtol=1e-4)
+
+
+@pytest.mark.parametrize("name", ["sphere_gij_d3", "img8_gij_d8", "hepmass_gij_d10_warm"])
+def test_intermediates(emu, name):
+    g = load_golden(name)
+    density = build_product(g)
+    head, _ = find_head(strip_wrappers(density))
+    with torch.no_grad():
+        z = g["z"]
+        gram, recon = head._get_full_jac_transpose_jac(z)
+        assert_close(gram, g["gram"], 2e-5, what="gram")
+        logdet, recon, gram2, l1 = head._exact_log_det_jac_and_reconstruction(z, "offdiag")
+        assert_close(logdet, g["logdet"], 2e-5, atol=1e-5, what="logdet")
+        assert_close(l1, g["l1_offdiag"], 2e-5, what="l1")
+        if g["x_pre"] is not None:
+            rl = ((recon - g["x_pre"]).flatten(1) ** 2).sum(-1, keepdim=True)
+            assert_close(rl, g["recon_loss"], 2e-5, what="recon")
+        # primal-only program == tangent program's primal
+        assert_close(head.flow_forward(z), recon, 1e-6, what="flow_forward")
+
+
+def test_program_structure_mnist(emu):
+    g = load_golden("mnist_gij_d64")
+    density = build_product(g)
+    head, _ = find_head(strip_wrappers(density))
+    prog = head.program
+    assert prog.modified_elements() == 3136          # sum_l M_l
+    assert prog.D == 784 and prog.d == 64
+    kinds = [l.split()[0] for l in prog.describe()]
+    assert kinds.count("acl") == 10
+
+
+def test_jitter_retry(emu, capsys):
+    g = load_golden("sphere_gij_d3")
+    density = build_product(g)
+    head, _ = find_head(strip_wrappers(density))
+    calls = {"n": 0}
+    real = head._get_full_jac_transpose_jac
+
+    def singular(latent, create_graph=True):
+        gram, recon = real(latent, create_graph)
+        calls["n"] += 1
+        return gram * 0.0, recon                 # rank-0 metric: Cholesky must fail until jitter lands
+    head._get_full_jac_transpose_jac = singular
+    logdet, _, gram, _ = head._exact_log_det_jac_and_reconstruction(g["z"], "none")
+    assert head.last_cholesky_attempts == 2
+    assert "WARNING: Numerical non-invertibility" in capsys.readouterr().out
+    assert torch.allclose(torch.diagonal(gram, dim1=-2, dim2=-1), torch.full((64, 3), 1e-6))
+
+
+def test_invalid_method_raises():
+    from cmf_b200.head import FusedNonSquareHeadDensity
+    with pytest.raises(ValueError, match="not a valid Jacobian calculation method"):
+        FusedNonSquareHeadDensity(None, 1, "lu", (3,), "normal")
+    h = FusedNonSquareHeadDensity(None, 1, "hutchinson", (3,), "normal")
+    assert h.log_jacobian_method == "hutch_with_cg"
+
+
+def test_no_cpu_fallback():
+    """Without the emulation the product must refuse CPU tensors loudly."""
+    from cmf_b200._lib import CmfB200Error
+    g = load_golden("sphere_gij_d3")
+    density = build_product(g)
+    with pytest.raises(CmfB200Error):
+        run_loss(g, density)
