@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py -- log-det + g_ij samples/s (784 -> 64, forward+backward) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+
+N > 1 is launched by torchrun (one rank per GPU, NCCL); rank 0 prints ONE JSON line.
+
+A *step* is one pass of the hot path over one batch of synthetic MNIST-shape input
+(BASELINE.json configs[3]: 1x28x28 -> latent 64, ``log_jacobian_method=cholesky``,
+``g_ij_loss=True``): ``loss = train_metrics(density, x, epoch)["loss"]; loss.backward()`` -- the
+call `cmf/trainer.py:213-216` makes -- followed by the flat-bucket gradient all-reduce.
+
+  value      whole-job samples/s with the batch already resident in HBM (Scope B of SURVEY 8d:
+             conditioner networks included)
+  e2e        same step through the public API with HOST input: pinned-host -> device copy of the
+             raw pixel batch, dequantisation, elbo, backward, all-reduce, loss read back
+  scope_a    the replaced kernels alone (coupling fwd/bwd over the 10 layers, Gram fwd/bwd,
+             Cholesky/log-det/penalty fwd/bwd) on synthetic conditioner outputs resident in HBM,
+             against their algorithmic bytes (8.76 MB/sample) -- explains `value`
+  roofline   the dominant hand-written kernel (coupling adjoint), algorithmic bytes / CUDA-event
+             time inside the scope_a region, against the measured HBM copy bandwidth
+  cpu_baseline  the CPU oracle (a port of the reference's algorithm, oracle/cmf_oracle.py) timed
+             on this box's host cores on a bounded sample of the same workload
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch
+
+METRIC = "log-det+g_ij samples/s (784->64, fwd+bwd)"
+WORKLOAD = dict(dataset="mnist", x_shape=(1, 28, 28),
+                overrides=dict(g_ij_loss=True, latent_dimension=64, log_jacobian_method="cholesky",
+                               likelihood_warmup=False))
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=50, help="per-GPU batch (reference default: config/images.py:131)")
+    ap.add_argument("--scope-a-batch", type=int, default=512)
+    ap.add_argument("--cpu-sample", type=int, default=1, help="samples per CPU-baseline step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--only", default=None, choices=[None, "scope_a", "step"],
+                    help="profiling aid: run only the kernels-only region / only the full step (no JSON contract)")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: sample nvidia-smi DURING the timed regions
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"   # B200_PROFILING.md fallback
+
+
+def build_config():
+    from cmf_b200.config import get_config, get_schema
+    cfg = {**get_config(WORKLOAD["dataset"]), **WORKLOAD["overrides"]}
+    return cfg, get_schema(cfg)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the oracle port on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_step_fn(cfg, schema, batch):
+    """Returns (step, cores): one fwd+bwd of the reference algorithm on ``batch`` samples, all host
+    threads.  The only places bench.py executes oracle/ (allowed: cpu_baseline and --impl reference)."""
+    import cmf_oracle as O
+    from detfill import fill_state_dict, det_tensor
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    params = fill_state_dict(O.init_params(schema, WORKLOAD["x_shape"]))
+    params = {k: (v.requires_grad_(True) if v.is_floating_point() else v) for k, v in params.items()}
+    flow = O.OracleFlow(schema, params, WORKLOAD["x_shape"])
+    x = (det_tensor("bench/x", (batch, *WORKLOAD["x_shape"]), 1.0, salt=5) + 1.0) * 127.9 + 0.05
+
+    def step():
+        for v in params.values():
+            if v.is_floating_point():
+                v.grad = None
+        loss = O.train_loss(flow, cfg, x, epoch=0)
+        loss.backward()
+        return float(loss.detach())
+    return step, cores
+
+
+def run_reference_arm(args, cfg, schema):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return                                   # rank 0 alone runs and prints; others exit 0
+    step, cores = cpu_step_fn(cfg, schema, args.cpu_sample)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    val = args.cpu_sample * args.steps / dt
+    sample = f"{args.cpu_sample} MNIST-shape sample(s) per step, d=64, fp32, torch CPU, {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "MNIST-shape 1x28x28 -> d=64, non-square cholesky + g_ij_loss",
+                   "batch": args.cpu_sample, "l2": "n/a (host)"},
+        "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# Scope A: the hand-written kernels alone, against their algorithmic bytes
+# ------------------------------------------------------------------------------------------------
+def scope_a(head, B, steps, warmup, dev):
+    """fwd+bwd of kernels (a),(b),(c) for the layer program of ``head`` on synthetic conditioner
+    outputs resident in HBM.  Returns samples/s, byte model and per-kernel-class CUDA-event times."""
+    from cmf_b200 import kernels as K
+    from cmf_b200.program import AclStep
+    d, D = head.program.d, head.program.D
+    layers = [s for s in head.program.steps if isinstance(s, AclStep)]
+    gen = torch.Generator(device=dev).manual_seed(1)
+    rnd = lambda *s, scale=1.0: (torch.rand(*s, device=dev, generator=gen) * 2 - 1) * scale
+    bufs = []
+    for s in layers:
+        bufs.append(dict(z=rnd(B, s.M), V=rnd(B, d, s.M), st=rnd(B, 2 * s.Q, scale=0.5), ST=rnd(B, d, 2 * s.Q),
+                         gx=rnd(B, s.M), gV=rnd(B, d, s.M),
+                         map=None if s.map is None else torch.as_tensor(s.map, device=dev),
+                         inv=None if s.inv is None else torch.as_tensor(s.inv, device=dev)))
+    Vf = [rnd(B, d, D // 2), rnd(B, d, D - D // 2)]            # final tangent blocks (two halves)
+    eye = torch.eye(d, device=dev) * (0.05 * D)
+    classes = ["coupling_fwd", "coupling_bwd", "gram_fwd", "gram_bwd", "chol_fwd", "chol_bwd"]
+    ev = {c: [] for c in classes}
+
+    def timed(cls, fn, record):
+        if not record:
+            return fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = fn()
+        b.record()
+        ev[cls].append((a, b))
+        return out
+
+    def one(record):
+        for bf in bufs:
+            timed("coupling_fwd", lambda: K.coupling_jvp_fwd(bf["z"], bf["V"], bf["st"], bf["ST"], bf["map"]), record)
+        G = None
+        for V in Vf:
+            G = timed("gram_fwd", lambda: K.gram_fwd(V, G), record)
+        G = G + eye
+        L, logdet, l1o, l1d, info = timed("chol_fwd", lambda: K.chol_logdet_fwd(G), record)
+        gG = timed("chol_bwd", lambda: K.chol_logdet_bwd(L, G, logdet, l1o, "offdiag"), record)
+        for V in Vf:
+            timed("gram_bwd", lambda: K.gram_bwd(V, gG), record)
+        for bf in reversed(bufs):
+            timed("coupling_bwd", lambda: K.coupling_jvp_bwd(bf["z"], bf["V"], bf["st"], bf["ST"], bf["map"],
+                                                            bf["inv"], bf["gx"], bf["gV"]), record)
+
+    for _ in range(warmup):
+        one(False)
+    torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(steps):
+        one(True)
+    t1.record()
+    torch.cuda.synchronize()
+    total_ms = t0.elapsed_time(t1)
+    sumM = sum(s.M for s in layers)
+    bytes_a = 40 * (1 + d) * sumM + 12 * D * d                  # SURVEY 8(d) per-sample byte model
+    per_class = {c: sum(a.elapsed_time(b) for a, b in ev[c]) / steps for c in classes}
+    return dict(samples_per_s=B * steps / (total_ms * 1e-3), ms_per_step=total_ms / steps, batch=B,
+                bytes_per_sample=bytes_a, sum_M=sumM, class_ms=per_class,
+                launches_per_class={c: len(ev[c]) // steps for c in classes})
+
+
+# ------------------------------------------------------------------------------------------------
+# own arm
+# ------------------------------------------------------------------------------------------------
+def run_own_arm(args, cfg, schema):
+    import torch.distributed as dist
+    from cmf_b200 import _lib
+    from cmf_b200.factory import get_density
+    from cmf_b200.non_square_helpers import get_non_square_train_metrics
+    from cmf_b200.parallel import GradientBucket, allreduce_gradients
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py (own arm) needs CUDA: there is no CPU fallback"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    torch.backends.cuda.matmul.allow_tf32 = False      # FP32-accurate conditioners (parity contract)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cudnn.benchmark = True
+    lib = _lib.load()
+
+    torch.manual_seed(0)
+    density = get_density(schema, WORKLOAD["x_shape"])          # reference default init, same on all ranks
+    with torch.no_grad():                                       # "trained-like": 5 % relative perturbation
+        for p in density.parameters():
+            p.add_(0.05 * float(p.std() if p.numel() > 1 else 1.0) * torch.randn_like(p))
+    density = density.to(dev).train()
+    bucket = GradientBucket(density.parameters())
+    train_metrics = get_non_square_train_metrics(cfg)[0]
+    inner = density.module.density                      # below DataParallel wrapper + dequantiser
+    head = inner
+    while type(head).__name__ != "FusedNonSquareHeadDensity":
+        head = head.prior
+
+    B = args.batch
+    torch.manual_seed(1234 + rank)
+    pixels = torch.randint(0, 256, (B, *WORKLOAD["x_shape"])).float()
+    x_dev = (pixels + torch.rand_like(pixels)).to(dev)   # dequantised once, resident in HBM
+    x_host = pixels.pin_memory()
+
+    def step_resident():
+        bucket.zero()
+        loss = train_metrics(inner, x_dev, 0)["loss"]
+        loss.backward()
+        allreduce_gradients(bucket)
+        return loss
+
+    def step_e2e():
+        bucket.zero()
+        x = x_host.to(dev, non_blocking=True)            # H2D of this step's raw input
+        loss = train_metrics(density, x, 0)["loss"]      # public API: wrapper -> dequantise -> ... -> head
+        loss.backward()
+        allreduce_gradients(bucket)
+        return float(loss.detach())                      # D2H read of the step's result
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        n0 = lib.cmf_launch_count()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            fn()
+        b.record()
+        barrier()
+        ms = torch.tensor([a.elapsed_time(b)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) , lib.cmf_launch_count() - n0
+
+    if args.only == "scope_a":
+        print(json.dumps(scope_a(head, args.scope_a_batch, args.steps, args.warmup, dev)), flush=True)
+        return
+    if args.only == "step":
+        ms, launches = timed(step_resident, args.steps, args.warmup)
+        print(json.dumps({"ms_per_step": ms / args.steps, "gpu_launches": launches}), flush=True)
+        return
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms, launches = timed(step_resident, args.steps, args.warmup)
+    ms_e2e, _ = timed(step_e2e, args.steps, 1)
+    value = world * B * args.steps / (ms * 1e-3)
+    e2e = world * B * args.steps / (ms_e2e * 1e-3)
+
+    sa = None
+    if rank == 0:
+        sa = scope_a(head, args.scope_a_batch, max(args.steps, 5), 3, dev)
+    clocks = sampler.stop() if rank == 0 else None
+    peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
+    barrier()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        step, cores = cpu_step_fn(cfg, schema, args.cpu_sample)
+        t0 = time.perf_counter()
+        step()
+        dt = time.perf_counter() - t0
+        cpu = {"value": args.cpu_sample / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+               "sample": f"1 step of {args.cpu_sample} MNIST-shape sample(s), d=64, fp32 fwd+bwd, oracle port of the "
+                         f"reference algorithm on torch CPU with {cores} threads ({dt:.1f} s)"}
+
+    if rank == 0:
+        peaks, peak_kind = measured_peaks()
+        d = head.program.d
+        cb_bytes = 24 * (1 + d) * sa["sum_M"] * sa["batch"]             # coupling adjoint, all 10 launches
+        cb_s = sa["class_ms"]["coupling_bwd"] * 1e-3
+        achieved = cb_bytes / cb_s / 1e9
+        scope_gbs = sa["bytes_per_sample"] * sa["samples_per_s"] / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "MNIST-shape 1x28x28 -> d=64, non-square cholesky + g_ij_loss (BASELINE configs[3])",
+                       "per_gpu_batch": B, "global_batch": B * world, "parallelism": f"dp{world}",
+                       "weights": "reference default init (seed 0) + 5% relative randn perturbation per parameter",
+                       "l2": "working set (saved conditioner activations, tens of GB) >> 126 MB L2; no flush needed",
+                       "tf32": False},
+            "e2e": {"value": e2e, "unit": "samples/s", "h2d_bytes_per_step": int(x_host.numel() * 4) * world,
+                    "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "cholesky_attempts": head.last_cholesky_attempts,
+            "clocks": clocks,
+            "scope_a": {"what": "kernels (a)+(b)+(c) fwd+bwd on synthetic conditioner outputs, C ABI direct",
+                        "samples_per_s": sa["samples_per_s"], "batch": sa["batch"],
+                        "bytes_per_sample": sa["bytes_per_sample"], "achieved_gbs": scope_gbs,
+                        "frac_of_hbm": scope_gbs / peaks["hbm_gbs"], "class_ms_per_step": sa["class_ms"],
+                        "launches_per_step": sa["launches_per_class"]},
+            "roofline": {"kernel": "coupling_bwd_{vec4,map} (10 launches/step)", "bound": "hbm",
+                         "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
+                         "algorithmic_bytes_per_step": cb_bytes},
+            "peak_mem_gib": peak_mem,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    cfg, schema = build_config()
+    if args.impl == "reference":
+        run_reference_arm(args, cfg, schema)
+    else:
+        run_own_arm(args, cfg, schema)
+
+
+if __name__ == "__main__":
+    main()

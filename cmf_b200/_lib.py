@@ -18,6 +18,7 @@ _vp, _i, _ll, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_size_t
 SIGNATURES = {
     "cmf_version": (_i, []),
     "cmf_last_error_string": (C.c_char_p, []),
+    "cmf_launch_count": (C.c_ulonglong, []),
     "cmf_coupling_jvp_fwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cmf_coupling_jvp_bwd_workspace": (_sz, [_i, _i, _i, _i]),
     "cmf_coupling_jvp_bwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,

@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace cmf {
@@ -12,7 +14,10 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 }  // namespace cmf
 
 extern "C" int cmf_version(void) { return CMF_B200_ABI_VERSION; }
 extern "C" const char* cmf_last_error_string(void) { return cmf::g_err; }
+extern "C" unsigned long long cmf_launch_count(void) { return cmf::g_launches.load(); }

@@ -9,6 +9,7 @@
 namespace cmf {
 
 void set_error(const char* fmt, ...);
+void count_launch();
 
 constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 
@@ -22,6 +23,7 @@ constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs
 
 #define CMF_CHECK_LAUNCH()                                                  \
     do {                                                                    \
+        cmf::count_launch();                                                \
         cudaError_t e__ = cudaPeekAtLastError();                            \
         if (e__ != cudaSuccess) {                                           \
             cmf::set_error("%s:%d: %s", __FILE__, __LINE__, cudaGetErrorString(e__)); \

@@ -38,6 +38,9 @@ typedef void* cmf_stream_t; /* a cudaStream_t */
 
 int cmf_version(void);
 const char* cmf_last_error_string(void);
+/* Number of kernel launches issued by this library since it was loaded (all threads); bench.py
+ * reports the difference over its timed region as "gpu_launches". */
+unsigned long long cmf_launch_count(void);
 
 /* (a) Affine coupling, primal + all d tangent columns in one pass.
  * Replaces acl.py:53-66 (checkerboard _jvp), acl.py:125-146 (channelwise _jvp) called d times

@@ -53,7 +53,25 @@ def assert_close(a, b, rtol, atol=0.0, what=""):
     assert err <= rtol * scale + atol, f"{what}: max err {err:.3e} vs scale {scale:.3e} (rtol {rtol})"
 
 
+def reference_rounding_noise(golden):
+    """Worst relative deviation of the reference's own fp32 gradients from an fp64 evaluation of
+    the same algorithm (oracle/add_fp64_probes.py).  ~1e-7 for the well-conditioned flat configs,
+    1.6e-4 for MNIST-shape d=64 where cond(G) ~ 5e3..8e3 amplifies fp32 rounding in G^{-1}."""
+    if "grads_fp64" not in golden:
+        return 0.0
+    worst = 0.0
+    for k, p64 in golden["grads_fp64"].items():
+        if k in golden["grads"]:
+            worst = max(worst, abs(golden["grads"][k]["norm"] - p64["norm"]) / max(p64["norm"], 1e-30))
+    return worst
+
+
 def check_against_golden(golden, loss, grads, rtol):
+    """loss and every parameter gradient within ``rtol`` relative of the reference's -- or within
+    3x the reference's own fp32 rounding error against fp64 when that is larger (an fp32 result
+    cannot be asked to agree with another fp32 result more closely than either agrees with the
+    exact value)."""
+    rtol = max(rtol, 3.0 * reference_rounding_noise(golden))
     assert_close(loss, golden["loss"], rtol, what="loss")
     assert set(golden["grads"]) == set(grads), "parameters receiving gradients differ from the reference"
     for k, probe in golden["grads"].items():

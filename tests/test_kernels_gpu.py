@@ -1,0 +1,170 @@
+"""Each C-ABI kernel against a plain-torch statement of its contract (tests/emu_kernels.py) on the
+same seeded inputs, computed in fp64 on the CPU.  fp32 kernels: rtol 1e-5 unless noted."""
+import pytest
+import torch
+
+import emu_kernels as E
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rand(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed + sum(shape))
+    return (torch.rand(*shape, generator=g, dtype=torch.float64) * 2 - 1) * scale
+
+
+def _close(a, b, rtol=1e-5, atol=1e-6, what=""):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    err = float((a - b).abs().max())
+    scale = float(b.abs().max())
+    assert err <= rtol * scale + atol, f"{what}: err {err:.3e} scale {scale:.3e}"
+
+
+def _checker_maps(M, Q, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    q = torch.randperm(Q, generator=g)[:M].sort().values
+    inv = torch.full((Q,), -1, dtype=torch.int32)
+    inv[q] = torch.arange(M, dtype=torch.int32)
+    return q.int(), inv
+
+
+COUPLING_SHAPES = [  # B, d, M, Q (Q == M -> identity map; else mapped)
+    (3, 5, 8, 8), (50, 64, 392, 392), (7, 64, 196, 392), (2, 3, 1, 1), (5, 0, 12, 12),
+    (4, 6, 3, 3), (9, 10, 11, 21), (2, 130, 64, 64), (1, 1, 4, 4), (6, 2, 2, 5),
+]
+
+
+@pytest.mark.parametrize("B,d,M,Q", COUPLING_SHAPES)
+def test_coupling_fwd_bwd(B, d, M, Q):
+    import cmf_b200.kernels as K
+    z, st = _rand(B, M, seed=1), _rand(B, 2 * Q, seed=2, scale=0.7)
+    V = _rand(B, d, M, seed=3) if d else None
+    ST = _rand(B, d, 2 * Q, seed=4) if d else None
+    map_, inv = (None, None) if M == Q else _checker_maps(M, Q)
+    x_ref, V_ref = E.coupling_jvp_fwd(z, V, st, ST, map_)
+    f = lambda t: None if t is None else t.float().to(DEV)
+    x, Vo = K.coupling_jvp_fwd(f(z), f(V), f(st), f(ST), f(map_) if map_ is None else map_.to(DEV))
+    _close(x, x_ref, what="x_m")
+    if d:
+        _close(Vo, V_ref, what="V_out")
+    gx, gV = _rand(B, M, seed=5), (_rand(B, d, M, seed=6) if d else None)
+    ref = E.coupling_jvp_bwd(z, V, st, ST, map_, inv, gx, gV)
+    got = K.coupling_jvp_bwd(f(z), f(V), f(st), f(ST), None if map_ is None else map_.to(DEV),
+                             None if inv is None else inv.to(DEV), f(gx), f(gV))
+    for name, a, b in zip(("g_z", "g_Vin", "g_st", "g_ST"), got, ref):
+        if b is not None:
+            _close(a, b, rtol=2e-5, atol=2e-6, what=name)
+    # g_x = None is treated as zero
+    ref0 = E.coupling_jvp_bwd(z, V, st, ST, map_, inv, None, gV)
+    got0 = K.coupling_jvp_bwd(f(z), f(V), f(st), f(ST), None if map_ is None else map_.to(DEV),
+                              None if inv is None else inv.to(DEV), None, f(gV))
+    _close(got0[2], ref0[2], rtol=2e-5, atol=2e-6, what="g_st (no g_x)")
+
+
+def test_coupling_unaligned_falls_back_to_scalar_path():
+    import cmf_b200.kernels as K
+    B, d, M = 4, 8, 16
+    z, st, V, ST = _rand(B, M), _rand(B, 2 * M, scale=0.5), _rand(B, d, M), _rand(B, d, 2 * M)
+    x_ref, V_ref = E.coupling_jvp_fwd(z, V, st, ST, None)
+    buf = torch.empty(B * M + 1, device=DEV)
+    z_dev = buf[1:].view(B, M)          # 4-byte aligned only
+    z_dev.copy_(z.float())
+    x, Vo = K.coupling_jvp_fwd(z_dev, V.float().to(DEV), st.float().to(DEV), ST.float().to(DEV), None)
+    _close(x, x_ref); _close(Vo, V_ref)
+
+
+@pytest.mark.parametrize("rows,n0,n1,n_out", [((3,), 5, 0, 9), ((4, 6), 17, 13, 40), ((50, 64), 392, 0, 784), ((2,), 1, 1, 1)])
+def test_gather_rows(rows, n0, n1, n_out):
+    import cmf_b200.kernels as K
+    g = torch.Generator().manual_seed(n_out)
+    a = _rand(*rows, n0)
+    b = _rand(*rows, n1, seed=9) if n1 else None
+    idx = torch.randint(-1, n0 + n1, (n_out,), generator=g).int()
+    ref = E.gather_rows(a, b, idx)
+    got = K.gather_rows(a.float().to(DEV), None if b is None else b.float().to(DEV), idx.to(DEV))
+    assert torch.equal(got.cpu(), ref.float())      # pure data movement: bit exact
+
+
+@pytest.mark.parametrize("B,d,n", [(3, 3, 3), (5, 6, 6), (4, 10, 21), (6, 64, 784), (2, 64, 392), (2, 128, 300),
+                                   (1, 200, 77), (3, 16, 1), (2, 65, 130)])
+def test_gram_fwd_bwd(B, d, n):
+    import cmf_b200.kernels as K
+    V = _rand(B, d, n)
+    Vd = V.float().to(DEV)
+    G = K.gram_fwd(Vd)
+    _close(G, E.gram_fwd(V), rtol=2e-6 * max(1, n ** 0.5), what="G")
+    assert torch.equal(G, G.transpose(1, 2)), "mirror tiles must be bitwise symmetric"
+    V2 = _rand(B, d, max(1, n // 2), seed=5)
+    G2 = K.gram_fwd(V2.float().to(DEV), G.clone())
+    _close(G2, E.gram_fwd(V) + E.gram_fwd(V2), rtol=1e-5, what="G accumulate")
+    gG = _rand(B, d, d, seed=7)
+    _close(K.gram_bwd(Vd, gG.float().to(DEV)), E.gram_bwd(V, gG), rtol=1e-5, what="g_V")
+
+
+def _spd(B, d, seed=0, cond=1e3):
+    A = _rand(B, d, max(d, 4) * 2, seed=seed)
+    G = A @ A.transpose(1, 2) / A.shape[2]
+    scale = torch.logspace(0, -torch.log10(torch.tensor(cond)).item() / 2, d, dtype=torch.float64)
+    return G * scale.view(1, d, 1) * scale.view(1, 1, d) + 1e-6 * torch.eye(d, dtype=torch.float64)
+
+
+@pytest.mark.parametrize("B,d", [(1, 1), (7, 2), (33, 3), (100, 6), (17, 10), (5, 20), (9, 64), (3, 100), (2, 128)])
+def test_chol_logdet_fwd_bwd(B, d):
+    import cmf_b200.kernels as K
+    G = _spd(B, d)
+    L_ref, ld_ref, off_ref, dia_ref, _ = E.chol_logdet_fwd(G)
+    Gd = G.float().to(DEV)
+    L, ld, off, dia, info = K.chol_logdet_fwd(Gd)
+    assert int(info.item()) == 0
+    _close(L, L_ref, rtol=2e-5, what="L")
+    _close(ld, ld_ref, rtol=1e-5, atol=1e-4, what="logdet")
+    _close(off, off_ref, what="l1_off"); _close(dia, dia_ref, what="l1_diag")
+    assert float(L.triu(1).abs().max()) == 0.0
+    gl, g1 = _rand(B, seed=3), _rand(B, seed=4)
+    for pen in ("none", "offdiag", "diag"):
+        ref = E.chol_logdet_bwd(L_ref, G, gl, g1, pen)
+        got = K.chol_logdet_bwd(L, Gd, gl.float().to(DEV), g1.float().to(DEV), pen)
+        # G^{-1} amplifies rounding by cond(G) ~ 1e3
+        _close(got, ref, rtol=5e-4, what=f"g_G[{pen}]")
+
+
+def test_chol_reports_non_positive_definite():
+    import cmf_b200.kernels as K
+    G = _spd(6, 8)
+    G[4] = -G[4]
+    G[1, 3, 3] = float("nan")
+    *_, info = K.chol_logdet_fwd(G.float().to(DEV))
+    assert int(info.item()) == 5          # 1 + largest failing sample index
+    *_, info = K.chol_logdet_fwd(_spd(6, 8).float().to(DEV))
+    assert int(info.item()) == 0
+
+
+def test_chol_d_above_limit_is_rejected():
+    import cmf_b200.kernels as K
+    from cmf_b200._lib import CmfB200Error
+    with pytest.raises(CmfB200Error, match="d <= 128|1 <= d"):
+        K.chol_logdet_fwd(torch.eye(129, device=DEV).repeat(2, 1, 1))
+
+
+def test_ops_autograd_matches_torch_autograd():
+    """The autograd.Function wrappers against torch autograd over the emulation (fp64)."""
+    from cmf_b200 import ops
+    B, d, M = 5, 6, 12
+    leaves64 = [_rand(B, M, seed=1), _rand(B, d, M, seed=2), _rand(B, 2 * M, seed=3, scale=0.5), _rand(B, d, 2 * M, seed=4)]
+    ref_in = [t.clone().requires_grad_(True) for t in leaves64]
+    x_r, V_r = E.coupling_jvp_fwd(*ref_in, None)
+    G_r = V_r @ V_r.transpose(1, 2) + 0.5 * torch.eye(d, dtype=torch.float64)
+    ld_r = torch.logdet(G_r)
+    off = ~torch.eye(d, dtype=torch.bool)
+    loss_r = (ld_r * 0.7).sum() + (G_r.abs() * off).sum() * 0.3 + (x_r ** 2).sum()
+    loss_r.backward()
+    dev_in = [t.float().to(DEV).requires_grad_(True) for t in leaves64]
+    x, V = ops.coupling_jvp(*dev_in)
+    G = ops.gram([V[:, :, :5].contiguous(), V[:, :, 5:].contiguous()]) + 0.5 * torch.eye(d, device=DEV)
+    ld, l1 = ops.chol_logdet_l1(G, "offdiag")
+    loss = (ld * 0.7).sum() + l1.sum() * 0.3 + (x ** 2).sum()
+    loss.backward()
+    _close(loss, loss_r, rtol=1e-5)
+    for a, b in zip(dev_in, ref_in):
+        _close(a.grad, b.grad, rtol=2e-4, atol=1e-5)
