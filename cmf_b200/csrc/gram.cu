@@ -128,14 +128,30 @@ gram_bwd_kernel(int d, int n, int nx, const float* __restrict__ V, const float* 
     }
 }
 
+// tensor-core path (gram_tc.cu)
+bool gram_tc_usable(int B, int d, int n, const float* V, const float* G);
+int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumulate, cudaStream_t stream);
+
 }  // namespace cmf
 
 using namespace cmf;
 
 extern "C" int cmf_gram_fwd(int B, int d, int n, const float* V, float* G, int accumulate, cmf_stream_t stream) {
+    return cmf_gram_fwd_path(B, d, n, V, G, accumulate, CMF_GRAM_AUTO, stream);
+}
+
+extern "C" int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, int accumulate, int path,
+                                 cmf_stream_t stream) {
     CMF_REQUIRE(B >= 0 && d >= 0 && n >= 0, "gram_fwd: negative size");
+    CMF_REQUIRE(path >= CMF_GRAM_AUTO && path <= CMF_GRAM_TC, "gram_fwd: bad path %d", path);
     if (B == 0 || d == 0) return 0;
     CMF_REQUIRE(G && (n == 0 || V), "gram_fwd: null pointer");
+    if (path != CMF_GRAM_FMA && n > 0) {
+        const bool ok = gram_tc_usable(B, d, n, V, G);
+        CMF_REQUIRE(ok || path == CMF_GRAM_AUTO,
+                    "gram_fwd: tensor-core path needs d >= 16, n >= 32, n %% 4 == 0 and 16-byte aligned V (d=%d n=%d)", d, n);
+        if (ok) return gram_tc_fwd_launch(B, d, n, V, G, accumulate, (cudaStream_t)stream);
+    }
     if (n == 0) {
         if (!accumulate) {
             cudaError_t e = cudaMemsetAsync(G, 0, (size_t)B * d * d * sizeof(float), (cudaStream_t)stream);

@@ -101,8 +101,12 @@ def gather_rows(in0: Tensor, in1: Optional[Tensor], idx: Tensor) -> Tensor:
     return out
 
 
-def gram_fwd(V: Tensor, G: Optional[Tensor] = None) -> Tensor:
-    """G (B,d,d) (+)= V V^T for V (B,d,n); accumulates into G when given."""
+GRAM_PATH = {"auto": 0, "fma": 1, "tc": 2}
+
+
+def gram_fwd(V: Tensor, G: Optional[Tensor] = None, path: str = "auto") -> Tensor:
+    """G (B,d,d) (+)= V V^T for V (B,d,n); accumulates into G when given.  ``path``: "auto" |
+    "fma" (FP32 FMA SYRK) | "tc" (tcgen05 3xTF32, raises when the shape does not qualify)."""
     lib = _lib.load()
     V = _req(V, "V")
     B, d, n = V.shape
@@ -110,7 +114,8 @@ def gram_fwd(V: Tensor, G: Optional[Tensor] = None) -> Tensor:
     if G is None:
         G = torch.empty(B, d, d, dtype=torch.float32, device=V.device)
     with torch.cuda.device(V.device):
-        _lib.check(lib.cmf_gram_fwd(B, d, n, _ptr(V), _ptr(G), int(acc), _stream()), "cmf_gram_fwd")
+        _lib.check(lib.cmf_gram_fwd_path(B, d, n, _ptr(V), _ptr(G), int(acc), GRAM_PATH[path], _stream()),
+                   "cmf_gram_fwd")
     return G
 
 

@@ -80,6 +80,17 @@ int cmf_gather_rows(long long rows, int n0, int n1, int n_out,
  * non_square.py:307-308.  accumulate != 0 adds into G (several blocks of one sample). */
 int cmf_gram_fwd(int B, int d, int n, const float* V, float* G, int accumulate, cmf_stream_t stream);
 
+/* Same, with the kernel chosen explicitly (parity tests pin both):
+ *   CMF_GRAM_TC   tcgen05.mma kind::tf32 with TMEM accumulators, FP32-accurate 3xTF32 split, TMA
+ *                 operand staging; needs d >= 16, n >= 32, n % 4 == 0, V 16-byte aligned
+ *   CMF_GRAM_FMA  FP32 FMA SYRK (any shape; the tabular / 2-D configs with d <= 10)
+ *   CMF_GRAM_AUTO TC when its shape constraints hold, else FMA (what cmf_gram_fwd does). */
+#define CMF_GRAM_AUTO 0
+#define CMF_GRAM_FMA  1
+#define CMF_GRAM_TC   2
+int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, int accumulate, int path,
+                      cmf_stream_t stream);
+
 /* Adjoint: g_V[b] = (g_G[b] + g_G[b]^T) V[b]   (B,d,n). */
 int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream);
 

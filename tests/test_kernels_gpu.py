@@ -102,6 +102,50 @@ def test_gram_fwd_bwd(B, d, n):
     _close(K.gram_bwd(Vd, gG.float().to(DEV)), E.gram_bwd(V, gG), rtol=1e-5, what="g_V")
 
 
+TC_SHAPES = [(5, 64, 392), (50, 64, 784), (3, 128, 96), (4, 20, 40), (2, 256, 128), (3, 200, 36),
+             (7, 16, 32), (1, 512, 64), (9, 48, 100), (2, 130, 260)]
+
+
+@pytest.mark.parametrize("B,d,n", TC_SHAPES)
+def test_gram_tc_matches_fp64_and_fma(B, d, n):
+    """tcgen05 3xTF32 Gram (cmf_gram_fwd_path CMF_GRAM_TC) is FP32-accurate: same tolerance as the
+    FMA kernel against the fp64 contract, bitwise symmetric, accumulate mode, ragged tails."""
+    import cmf_b200.kernels as K
+    V = _rand(B, d, n)
+    Vd = V.float().to(DEV)
+    ref = E.gram_fwd(V)
+    G = K.gram_fwd(Vd, path="tc")
+    _close(G, ref, rtol=2e-6 * max(1, n ** 0.5), what="G tc")
+    assert torch.equal(G, G.transpose(1, 2)), "G must be bitwise symmetric"
+    G_fma = K.gram_fwd(Vd, path="fma")
+    _close(G, G_fma, rtol=2e-6 * max(1, n ** 0.5), what="tc vs fma")
+    V2 = _rand(B, d, n, seed=5)
+    G2 = K.gram_fwd(V2.float().to(DEV), G.clone(), path="tc")
+    _close(G2, ref + E.gram_fwd(V2), rtol=1e-5, what="G tc accumulate")
+
+
+def test_gram_tc_badly_scaled_columns():
+    """Trained CMF models drive most G_kk toward zero (SURVEY 7 hard parts): tangent rows scaled by
+    10^-k must keep fp32-level relative accuracy element-wise against |v_i||v_j|."""
+    import cmf_b200.kernels as K
+    B, d, n = 4, 64, 392
+    V = _rand(B, d, n) * (10.0 ** (-torch.arange(d, dtype=torch.float64) / 8.0)).view(1, d, 1)
+    G = K.gram_fwd(V.float().to(DEV), path="tc").double().cpu()
+    ref = E.gram_fwd(V)
+    nrm = V.norm(dim=2)
+    bound = nrm.unsqueeze(2) * nrm.unsqueeze(1)
+    assert float(((G - ref).abs() / bound).max()) < 2e-6
+
+
+def test_gram_tc_rejects_unaligned_shapes():
+    import cmf_b200.kernels as K
+    from cmf_b200 import _lib
+    with pytest.raises(_lib.CmfB200Error):
+        K.gram_fwd(torch.zeros(2, 6, 6, device=DEV), path="tc")
+    with pytest.raises(_lib.CmfB200Error):
+        K.gram_fwd(torch.zeros(2, 64, 30, device=DEV), path="tc")
+
+
 def _spd(B, d, seed=0, cond=1e3):
     A = _rand(B, d, max(d, 4) * 2, seed=seed)
     G = A @ A.transpose(1, 2) / A.shape[2]
