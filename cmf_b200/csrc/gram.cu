@@ -131,6 +131,8 @@ gram_bwd_kernel(int d, int n, int nx, const float* __restrict__ V, const float* 
 // tensor-core path (gram_tc.cu)
 bool gram_tc_usable(int B, int d, int n, const float* V, const float* G);
 int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumulate, cudaStream_t stream);
+bool gram_tc_bwd_usable(int B, int d, int n, const float* V, const float* gG, const float* gV);
+int gram_tc_bwd_launch(int B, int d, int n, const float* V, const float* gG, float* gV, cudaStream_t stream);
 
 }  // namespace cmf
 
@@ -168,9 +170,22 @@ extern "C" int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, 
 }
 
 extern "C" int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream) {
+    return cmf_gram_bwd_path(B, d, n, V, g_G, g_V, CMF_GRAM_AUTO, stream);
+}
+
+extern "C" int cmf_gram_bwd_path(int B, int d, int n, const float* V, const float* g_G, float* g_V, int path,
+                                 cmf_stream_t stream) {
     CMF_REQUIRE(B >= 0 && d >= 0 && n >= 0, "gram_bwd: negative size");
+    CMF_REQUIRE(path >= CMF_GRAM_AUTO && path <= CMF_GRAM_TC, "gram_bwd: bad path %d", path);
     if (B == 0 || d == 0 || n == 0) return 0;
     CMF_REQUIRE(V && g_G && g_V, "gram_bwd: null pointer");
+    if (path != CMF_GRAM_FMA) {
+        const bool ok = gram_tc_bwd_usable(B, d, n, V, g_G, g_V);
+        CMF_REQUIRE(ok || path == CMF_GRAM_AUTO,
+                    "gram_bwd: tensor-core path needs d >= 16, d %% 4 == 0, n >= 32, n %% 4 == 0 and 16-byte aligned V, g_G (d=%d n=%d)", d, n);
+        // at d <= 64 the FP32 FMA kernel is as fast (HBM-bound either way); the tensor core wins above
+        if (ok && (path == CMF_GRAM_TC || d > 64)) return gram_tc_bwd_launch(B, d, n, V, g_G, g_V, (cudaStream_t)stream);
+    }
     const int nx = (int)ceil_div(n, BT);
     CMF_REQUIRE((long long)B * nx < (1LL << 31), "gram_bwd: grid too large");
     dim3 grid((unsigned)(B * nx), (unsigned)ceil_div(d, BT));

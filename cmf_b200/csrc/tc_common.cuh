@@ -152,6 +152,6 @@ typedef CUresult (*cmf_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuin
 cmf_encode_tiled_fn get_encode_tiled();
 // rank-2 fp32 tensor (rows x cols, row stride `ld` floats), box = box_rows x 32 floats, 128B swizzle
 int make_tmap_2d_f32(CUtensorMap* out, const float* base, uint64_t rows, uint64_t cols, uint64_t ld,
-                     uint32_t box_rows);
+                     uint32_t box_rows, int swizzle_atom32);
 
 }  // namespace cmf

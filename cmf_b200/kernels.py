@@ -119,13 +119,14 @@ def gram_fwd(V: Tensor, G: Optional[Tensor] = None, path: str = "auto") -> Tenso
     return G
 
 
-def gram_bwd(V: Tensor, g_G: Tensor) -> Tensor:
+def gram_bwd(V: Tensor, g_G: Tensor, path: str = "auto") -> Tensor:
     lib = _lib.load()
     V, g_G = _req(V, "V"), _req(g_G, "g_G")
     B, d, n = V.shape
     g_V = torch.empty_like(V)
     with torch.cuda.device(V.device):
-        _lib.check(lib.cmf_gram_bwd(B, d, n, _ptr(V), _ptr(g_G), _ptr(g_V), _stream()), "cmf_gram_bwd")
+        _lib.check(lib.cmf_gram_bwd_path(B, d, n, _ptr(V), _ptr(g_G), _ptr(g_V), GRAM_PATH[path], _stream()),
+                   "cmf_gram_bwd")
     return g_V
 
 

@@ -93,6 +93,11 @@ int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, int accumul
 
 /* Adjoint: g_V[b] = (g_G[b] + g_G[b]^T) V[b]   (B,d,n). */
 int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream);
+/* CMF_GRAM_TC here: D[n,j] = sum_k V[k,n] S[k,j] with V as the MN-major tcgen05 operand (TMA,
+ * 32-byte-atom 128B swizzle) and S = g_G + g_G^T staged by TMA; additionally needs d % 4 == 0 and
+ * g_G 16-byte aligned.  AUTO picks it for d > 64. */
+int cmf_gram_bwd_path(int B, int d, int n, const float* V, const float* g_G, float* g_V, int path,
+                      cmf_stream_t stream);
 
 /* (c) Batched Cholesky log-det + metric penalties.  Replaces torch.linalg.cholesky + diagonal +
  * log + sum (non_square.py:282,293-294) and masked_select + vector_norm (non_square.py:95-100,

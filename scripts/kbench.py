@@ -47,8 +47,11 @@ def bench_gram():
             err = float(((G.double() - ref).abs().amax() / ref.abs().amax()))
             t = timeit(lambda: K.gram_fwd(V, path=path))
             report(f"gram_fwd[{path}] B={B} d={d} n={n}", t, 4.0 * B * d * n + 4.0 * B * d * d, 2.0 * B * d * d * n, rel_err=err)
-        t = timeit(lambda: K.gram_bwd(V, gG))
-        report(f"gram_bwd B={B} d={d} n={n}", t, 8.0 * B * d * n, 2.0 * B * d * d * n)
+        refb = torch.bmm(gG.double() + gG.double().transpose(1, 2), V.double())
+        for path in ("fma", "tc"):
+            err = float((K.gram_bwd(V, gG, path=path).double() - refb).abs().amax() / refb.abs().amax())
+            t = timeit(lambda: K.gram_bwd(V, gG, path=path))
+            report(f"gram_bwd[{path}] B={B} d={d} n={n}", t, 8.0 * B * d * n, 2.0 * B * d * d * n, rel_err=err)
         tb = timeit(lambda: torch.bmm(V, V.transpose(1, 2)))
         report(f"torch.bmm fp32 B={B} d={d} n={n}", tb, 4.0 * B * d * n, 2.0 * B * d * d * n)
 

@@ -122,6 +122,17 @@ def test_gram_tc_matches_fp64_and_fma(B, d, n):
     V2 = _rand(B, d, n, seed=5)
     G2 = K.gram_fwd(V2.float().to(DEV), G.clone(), path="tc")
     _close(G2, ref + E.gram_fwd(V2), rtol=1e-5, what="G tc accumulate")
+    gG = _rand(B, d, d, seed=7)
+    g_ref = E.gram_bwd(V, gG)
+    if d % 4:          # the adjoint stages g_G by TMA: row stride must be a multiple of 16 bytes
+        from cmf_b200 import _lib
+        with pytest.raises(_lib.CmfB200Error):
+            K.gram_bwd(Vd, gG.float().to(DEV), path="tc")
+        _close(K.gram_bwd(Vd, gG.float().to(DEV)), g_ref, rtol=1e-5, what="g_V auto")
+        return
+    g_tc = K.gram_bwd(Vd, gG.float().to(DEV), path="tc")
+    _close(g_tc, g_ref, rtol=1e-5, what="g_V tc")
+    _close(g_tc, K.gram_bwd(Vd, gG.float().to(DEV), path="fma"), rtol=1e-5, what="g_V tc vs fma")
 
 
 def test_gram_tc_badly_scaled_columns():
