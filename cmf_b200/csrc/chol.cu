@@ -174,11 +174,19 @@ static int pick_tps(int d) {
 
 using namespace cmf;
 
+// 128 < d <= 1024: panel-blocked kernels working out of global memory (chol_big.cu)
+constexpr int kCholBigMaxD = 1024;
+int chol_big_fwd_launch(int B, int d, const float* G, float* L, float* logdet, float* l1_off, float* l1_diag,
+                        int32_t* info, cudaStream_t stream);
+int chol_big_bwd_launch(int B, int d, const float* L, const float* G, const float* g_logdet, const float* g_l1,
+                        int penalty, float* g_G, cudaStream_t stream);
+
 extern "C" int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float* logdet,
                                    float* l1_off, float* l1_diag, int32_t* info, cmf_stream_t stream) {
-    CMF_REQUIRE(B >= 0 && d >= 1 && d <= kCholMaxD, "chol_fwd: need 1 <= d <= %d (d=%d)", kCholMaxD, d);
+    CMF_REQUIRE(B >= 0 && d >= 1 && d <= kCholBigMaxD, "chol_fwd: need 1 <= d <= %d (d=%d)", kCholBigMaxD, d);
     if (B == 0) return 0;
     CMF_REQUIRE(G && L && logdet && l1_off && l1_diag && info, "chol_fwd: null pointer");
+    if (d > kCholMaxD) return chol_big_fwd_launch(B, d, G, L, logdet, l1_off, l1_diag, info, (cudaStream_t)stream);
     const int tps = pick_tps(d), spb = kCholThreads / tps;
     const size_t smem = ((size_t)spb * d * (d + 1) + kCholThreads + spb) * sizeof(float);
     static bool attr_set = false;
@@ -196,10 +204,11 @@ extern "C" int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float
 extern "C" int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
                                    const float* g_logdet, const float* g_l1, int penalty,
                                    float* g_G, cmf_stream_t stream) {
-    CMF_REQUIRE(B >= 0 && d >= 1 && d <= kCholMaxD, "chol_bwd: need 1 <= d <= %d (d=%d)", kCholMaxD, d);
+    CMF_REQUIRE(B >= 0 && d >= 1 && d <= kCholBigMaxD, "chol_bwd: need 1 <= d <= %d (d=%d)", kCholBigMaxD, d);
     CMF_REQUIRE(penalty >= 0 && penalty <= 2, "chol_bwd: bad penalty %d", penalty);
     if (B == 0) return 0;
     CMF_REQUIRE(L && G && g_logdet && g_G, "chol_bwd: null pointer");
+    if (d > kCholMaxD) return chol_big_bwd_launch(B, d, L, G, g_logdet, g_l1, penalty, g_G, (cudaStream_t)stream);
     const int tps = pick_tps(d), spb = kCholThreads / tps;
     const size_t smem = (size_t)spb * 2 * d * (d + 1) * sizeof(float);
     static bool attr_set = false;

@@ -104,7 +104,9 @@ int cmf_gram_bwd_path(int B, int d, int n, const float* V, const float* g_G, flo
  * :87-92).  Outputs: L (B,d,d) lower factor (upper triangle zero), logdet (B) = 2 sum log L_kk,
  * l1_off (B), l1_diag (B).  info (1 int32, device, MUST be zeroed by the caller): set to
  * 1 + index of a sample whose leading minor is not positive (the RuntimeError of
- * non_square.py:283-288); the host then adds eps*I and retries like the reference. d <= 128. */
+ * non_square.py:283-288); the host then adds eps*I and retries like the reference.
+ * d <= 128: factor held in shared memory (several samples per CTA for small d); 128 < d <= 1024
+ * (CIFAR-shape latent sweep): panel-blocked out of L2, one CTA per sample. */
 int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float* logdet,
                         float* l1_off, float* l1_diag, int32_t* info, cmf_stream_t stream);
 

@@ -73,7 +73,7 @@ def bench_coupling():
 
 
 def bench_chol():
-    for (B, d) in [(512, 64), (50, 64), (256, 128), (5000, 6), (1000, 3)]:
+    for (B, d) in [(512, 64), (50, 64), (256, 128), (64, 256), (64, 512), (8, 512), (5000, 6), (1000, 3)]:
         A = torch.randn(B, d, 2 * d, device=DEV)
         G = torch.bmm(A, A.transpose(1, 2)) + 0.1 * torch.eye(d, device=DEV)
         t = timeit(lambda: K.chol_logdet_fwd(G))

@@ -164,7 +164,8 @@ def _spd(B, d, seed=0, cond=1e3):
     return G * scale.view(1, d, 1) * scale.view(1, 1, d) + 1e-6 * torch.eye(d, dtype=torch.float64)
 
 
-@pytest.mark.parametrize("B,d", [(1, 1), (7, 2), (33, 3), (100, 6), (17, 10), (5, 20), (9, 64), (3, 100), (2, 128)])
+@pytest.mark.parametrize("B,d", [(1, 1), (7, 2), (33, 3), (100, 6), (17, 10), (5, 20), (9, 64), (3, 100), (2, 128),
+                                 (3, 129), (2, 200), (2, 256), (2, 512), (1, 1000)])
 def test_chol_logdet_fwd_bwd(B, d):
     import cmf_b200.kernels as K
     G = _spd(B, d)
@@ -193,13 +194,20 @@ def test_chol_reports_non_positive_definite():
     assert int(info.item()) == 5          # 1 + largest failing sample index
     *_, info = K.chol_logdet_fwd(_spd(6, 8).float().to(DEV))
     assert int(info.item()) == 0
+    # panel-blocked kernel (d > 128): failure in a later panel of sample 2, NaN in sample 0
+    G = _spd(4, 160)
+    G[2, 150, 150] = -1.0
+    G[0, 40, 7] = G[0, 7, 40] = float("nan")
+    _, ld, *_, info = K.chol_logdet_fwd(G.float().to(DEV))
+    assert int(info.item()) == 3
+    assert torch.isnan(ld[2]) and torch.isnan(ld[0]) and torch.isfinite(ld[1]) and torch.isfinite(ld[3])
 
 
 def test_chol_d_above_limit_is_rejected():
     import cmf_b200.kernels as K
     from cmf_b200._lib import CmfB200Error
-    with pytest.raises(CmfB200Error, match="d <= 128|1 <= d"):
-        K.chol_logdet_fwd(torch.eye(129, device=DEV).repeat(2, 1, 1))
+    with pytest.raises(CmfB200Error, match="1 <= d"):
+        K.chol_logdet_fwd(torch.eye(1025, device=DEV).repeat(2, 1, 1))
 
 
 def test_ops_autograd_matches_torch_autograd():
