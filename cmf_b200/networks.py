@@ -102,12 +102,35 @@ class ScaledTanhResNet(nn.Module):
     def forward(self, x: Tensor) -> Tensor:
         return self.weights * torch.tanh(self.module(x)) + self.bias
 
-    def jvp_batched(self, x: Tensor, V: Tensor) -> Tuple[Tensor, Tensor]:
-        """x (B,C,H,W), V (B,d,C,H,W) -> y (B,O,H,W), Y (B,d,O,H,W)."""
+    # -- compact tail ------------------------------------------------------------------------
+    # A checkerboard coupling layer uses the conditioner output at half of the spatial positions
+    # only (`acl.py:53-66`: everything is multiplied by 1 - mask).  The tail of the net
+    # (ReLU -> 1x1 conv -> scaled tanh, `networks.py:156-161,96-113`) acts per position, so it is
+    # evaluated at those positions alone: the hidden activations are gathered once (cmf_gather_rows,
+    # fused with the ReLU mask product the JVP rule needs anyway) and the coupling kernel receives
+    # COMPACT (shift, log-scale) tensors -- no half-used sectors, no zero-filled adjoints.
+    supports_compact_output = True
+
+    def _tail(self):
+        relu, last = self.module[-2], self.module[-1]
+        assert isinstance(relu, nn.ReLU) and isinstance(last, nn.Conv2d) and last.kernel_size == (1, 1)
+        return last
+
+    def forward_compact(self, x: Tensor, pos: Tensor) -> Tensor:
+        """x (B,C,H,W), pos (P,) int64 spatial positions -> y (B,O,P)."""
+        last = self._tail()
+        h = self.module[:-2](x).flatten(2).index_select(2, pos)
+        y = torch.matmul(last.weight.flatten(1), torch.relu(h)) + last.bias.view(1, -1, 1)
+        return self.weights.view(1, -1, 1) * torch.tanh(y) + self.bias.view(1, -1, 1)
+
+    def jvp_batched(self, x: Tensor, V: Tensor, pos=None) -> Tuple[Tensor, Tensor]:
+        """x (B,C,H,W), V (B,d,C,H,W) -> y (B,O,H,W), Y (B,d,O,H,W); with ``pos`` = (idx int32 (P,),
+        inv int32 (H*W,), pos int64 (P,)) the outputs are compact: y (B,O,P), Y (B,d,O,P)."""
         B, d = V.shape[:2]
         Hv = V.reshape(B * d, *V.shape[2:])
         h = x
-        for mod in self.module:
+        body = self.module if pos is None else self.module[:-2]
+        for mod in body:
             if isinstance(mod, ResidualBlock):
                 h, Hv = mod.jvp_batched(h, Hv, d)
             elif isinstance(mod, nn.Conv2d):
@@ -118,6 +141,19 @@ class ScaledTanhResNet(nn.Module):
                 h = torch.relu(h)
             else:
                 raise ValueError(f"jvp unsupported for module {type(mod).__name__}")
+        if pos is not None:
+            from . import ops
+            idx, inv, pos64 = pos
+            last = self._tail()
+            w2 = last.weight.flatten(1)                                  # (O, C)
+            hc = h.flatten(2).index_select(2, pos64)                     # (B, C, P)
+            Hc = ops.gather_rows(Hv.flatten(2), None, idx, inv)          # (B*d, C, P)
+            Hc = Hc.view(B, d, *Hc.shape[1:]) * _bcast((hc > 0).to(Hc.dtype))
+            h = torch.matmul(w2, torch.relu(hc)) + last.bias.view(1, -1, 1)
+            Hv = torch.matmul(w2, Hc)                                    # (B, d, O, P)
+            y = torch.tanh(h)
+            w = self.weights.view(1, -1, 1)
+            return w * y + self.bias.view(1, -1, 1), Hv * _bcast((1 - y * y) * w)
         y = torch.tanh(h)
         Hv = Hv.view(B, d, *Hv.shape[1:]) * _bcast((1 - y * y) * self.weights)
         return self.weights * y + self.bias, Hv
@@ -149,12 +185,19 @@ class ChunkedSharedCoupler(nn.Module):
         c = y.shape[1] // 2
         return {"shift": y[:, :c], "log-scale": y[:, c:]}
 
-    def st_batched(self, x: Tensor, V):
+    @property
+    def supports_compact_output(self) -> bool:
+        return bool(getattr(self.shift_log_scale_net, "supports_compact_output", False))
+
+    def st_batched(self, x: Tensor, V, pos=None):
         """Flat conditioner outputs for the coupling kernel: st (B,2Q) = [shift | log_scale]
-        and, if V (B,d,...) is given, ST (B,d,2Q)."""
+        and, if V (B,d,...) is given, ST (B,d,2Q).  ``pos``: evaluate the net's tail at these
+        spatial positions only (compact outputs, Q = channels * len(pos))."""
+        net = self.shift_log_scale_net
         if V is None:
-            return self.shift_log_scale_net(x).flatten(1), None
-        y, Y = self.shift_log_scale_net.jvp_batched(x, V)
+            y = net(x) if pos is None else net.forward_compact(x, pos[2])
+            return y.flatten(1), None
+        y, Y = net.jvp_batched(x, V) if pos is None else net.jvp_batched(x, V, pos)
         return y.flatten(1), Y.flatten(2)
 
 
@@ -168,7 +211,10 @@ class IndependentCoupler(nn.Module):
     def forward(self, x: Tensor):
         return {"shift": self.shift_net(x), "log-scale": self.log_scale_net(x)}
 
-    def st_batched(self, x: Tensor, V):
+    supports_compact_output = False
+
+    def st_batched(self, x: Tensor, V, pos=None):
+        assert pos is None
         if V is None:
             return torch.cat((self.shift_net(x).flatten(1), self.log_scale_net(x).flatten(1)), 1), None
         t, T = self.shift_net.jvp_batched(x, V)

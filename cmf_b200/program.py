@@ -68,6 +68,8 @@ class AclStep:
     inv: Optional[np.ndarray]    # (Q,) int32 compact index of conditioner position q or -1
     M: int = 0
     Q: int = 0
+    pos: Optional[np.ndarray] = None   # (P,) spatial positions at which the conditioner tail is evaluated
+    hw: int = 0                        # H*W of the conditioner output (compact tail only)
 
 
 class LayerProgram:
@@ -167,7 +169,19 @@ class LayerProgram:
         # 3. the compact half to transform, in conditioner-output order
         mod = self._assemble(mod_blocks, mod_pos, D)
         # 4. relation between compact index j and conditioner position q
-        if dense:
+        pos, hw = None, 0
+        if dense and getattr(bij.coupler, "supports_compact_output", False) and len(in_shape) == 3:
+            # checkerboard with a per-position net tail: the conditioner emits compact outputs at
+            # the modified spatial positions (same set for every channel), in (channel, position)
+            # order == the order of mod_pos
+            C, hw = in_shape[0], in_shape[1] * in_shape[2]
+            sp = np.unique(mod_pos % hw)
+            if sp.size * C == mod_pos.size and np.array_equal(
+                    mod_pos, (np.arange(C)[:, None] * hw + sp[None, :]).reshape(-1)):
+                pos = sp
+        if pos is not None:
+            cmap, cinv, Q = None, None, mod_pos.size
+        elif dense:
             cmap = mod_pos.astype(np.int32)
             cinv = np.full(D, -1, dtype=np.int32)
             cinv[mod_pos] = np.arange(mod_pos.size, dtype=np.int32)
@@ -175,7 +189,7 @@ class LayerProgram:
         else:
             cmap, cinv, Q = None, None, mod_pos.size
         out = self._new_slot()
-        self.steps.append(AclStep(bij, cond, tuple(in_shape), mod, out, cmap, cinv, mod_pos.size, Q))
+        self.steps.append(AclStep(bij, cond, tuple(in_shape), mod, out, cmap, cinv, mod_pos.size, Q, pos, hw))
         return keep_blocks + [SymBlock(out, mod_pos)]
 
     def _assemble(self, blocks: Sequence[SymBlock], target: np.ndarray, D: int) -> int:
@@ -252,7 +266,14 @@ class LayerProgram:
                 xc, Vc = slots[step.cond]
                 x_in = xc.view(B, *step.in_shape)
                 V_in = None if m is None else Vc.view(B, m, *step.in_shape)
-                st, ST = step.bijection.coupler.st_batched(x_in, V_in)
+                pos = None
+                if step.pos is not None:
+                    pinv = np.full(step.hw, -1, dtype=np.int32)
+                    pinv[step.pos] = np.arange(step.pos.size, dtype=np.int32)
+                    pos = (self._dev(step.pos.astype(np.int32), dev, (si, "pidx")),
+                           self._dev(pinv, dev, (si, "pinv")),
+                           self._dev(step.pos, dev, (si, "p64"), torch.int64))
+                st, ST = step.bijection.coupler.st_batched(x_in, V_in, pos)
                 z_m, V_m = slots[step.mod]
                 slots[step.out] = ops.coupling_jvp(z_m, V_m, st, ST,
                                                    self._dev(step.map, dev, (si, "map")),
@@ -276,7 +297,7 @@ class LayerProgram:
                 lines.append(f"zeros   -> {s.out}  n={s.n}")
             else:
                 lines.append(f"acl     {type(s.bijection).__name__}: cond={s.cond} mod={s.mod} -> {s.out}  "
-                             f"M={s.M} Q={s.Q} {'mapped' if s.map is not None else 'identity'}")
+                             f"M={s.M} Q={s.Q} {'mapped' if s.map is not None else ('compact-tail' if s.pos is not None else 'identity')}")
         return lines
 
     def modified_elements(self) -> int:

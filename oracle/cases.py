@@ -51,6 +51,11 @@ CASES = {
     "img8c3_gij_d16": dict(dataset="cifar10", x_shape=(3, 8, 8), batch=4, epoch=60, data="pixels",
                            overrides=dict(g_ij_loss=True, latent_dimension=16, g_hidden_channels=[8, 8],
                                           prior_num_density_layers=2, **COMMON)),
+    # BASELINE.json configs[4] (CIFAR-shape latent sweep) at reduced size: 3x16x16 -> d=160 > 128,
+    # the regime of the panel-blocked Cholesky and the multi-tile tcgen05 Gram
+    "img16c3_gij_d160": dict(dataset="cifar10", x_shape=(3, 16, 16), batch=2, epoch=60, data="pixels",
+                             overrides=dict(g_ij_loss=True, latent_dimension=160, g_hidden_channels=[8, 8],
+                                            prior_num_density_layers=2, **COMMON), slow=True),
     # BASELINE.json configs[3] at full size: MNIST-shape 1x28x28 -> 64, B=2 (slow on CPU)
     "mnist_gij_d64": dict(dataset="mnist", x_shape=(1, 28, 28), batch=2, epoch=60, data="pixels",
                           overrides=dict(g_ij_loss=True, latent_dimension=64, **COMMON), slow=True),
