@@ -171,7 +171,10 @@ class NonSquareTailDensity(Density):
         self.register_buffer("inverse_permutation", torch.argsort(self.permutation))
 
     def _elbo(self, x):
-        low_dim_x = x.flatten(1)[:, self.permutation][:, self.mask]
+        # == x[:, permutation][:, mask] of `non_square.py:383-384` (mask = first latent_dimension
+        # entries); one index_select, no boolean-mask compaction and hence no host sync, so the step
+        # can be captured into a CUDA graph
+        low_dim_x = x.flatten(1).index_select(1, self.permutation[: self.latent_dimension])
         prior_dict = self.prior.elbo(low_dim_x.detach() if self.detach_before_prior else low_dim_x)
         return {"elbo": prior_dict["elbo"], "low-dim-x": low_dim_x, "prior-dict": prior_dict}
 

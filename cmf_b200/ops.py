@@ -22,6 +22,26 @@ class NotPositiveDefiniteError(RuntimeError):
     """Raised where ``torch.linalg.cholesky`` raises in the reference (`non_square.py:282-288`)."""
 
 
+class _DeferredInfo:
+    """While a training step is being captured into / replayed from a CUDA graph the host cannot
+    read the Cholesky ``info`` word (a device->host sync is illegal during capture).  In this mode
+    :func:`chol_logdet_l1` appends the device word to ``pending`` instead; the owner of the graph
+    reads all of them after the replay and falls back to the eager path (which runs the
+    reference's ``+eps*I`` retry loop) if any is non-zero."""
+    active = False
+    pending: list = []
+
+
+class defer_pd_check:
+    def __enter__(self):
+        _DeferredInfo.active, _DeferredInfo.pending = True, []
+        return _DeferredInfo.pending
+
+    def __exit__(self, *exc):
+        _DeferredInfo.active = False
+        return False
+
+
 class _CouplingJVP(Function):
     @staticmethod
     def forward(ctx, z_m, V_m, st, ST, map_, inv):
@@ -130,7 +150,11 @@ def chol_logdet_l1(G: Tensor, penalty: str = "none") -> Tuple[Tensor, Tensor]:
     if penalty not in kernels.PENALTY:
         raise ValueError(f"unknown penalty {penalty}")
     logdet, l1, info = _CholLogdetL1.apply(G, penalty)
-    bad = int(info.item())
+    if _DeferredInfo.active:
+        _DeferredInfo.pending.append(info)
+        bad = 0
+    else:
+        bad = int(info.item())
     if bad:
         raise NotPositiveDefiniteError(
             f"cmf_chol_logdet_fwd: leading minor not positive for sample {bad - 1}")
