@@ -30,6 +30,8 @@ SIGNATURES = {
     "cmf_gram_bwd_path": (_i, [_i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "cmf_chol_logdet_fwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cmf_chol_logdet_bwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "cmf_rqs_coupling_jvp_fwd": (_i, [_i, _i, _i, _i, C.c_float] + [_vp] * 12),
+    "cmf_rqs_coupling_jvp_bwd": (_i, [_i, _i, _i, _i, C.c_float] + [_vp] * 19),
 }
 
 _lib = None

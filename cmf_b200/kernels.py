@@ -156,3 +156,49 @@ def chol_logdet_bwd(L: Tensor, G: Tensor, g_logdet: Tensor, g_l1: Optional[Tenso
         _lib.check(lib.cmf_chol_logdet_bwd(B, d, _ptr(L), _ptr(G), _ptr(g_logdet), _ptr(g_l1),
                                            PENALTY[penalty], _ptr(g_G), _stream()), "cmf_chol_logdet_bwd")
     return g_G
+
+
+def rqs_coupling_jvp_fwd(z_m: Tensor, V_m: Optional[Tensor], cw: Tensor, ch: Tensor, dv: Tensor,
+                         CW: Optional[Tensor], CH: Optional[Tensor], DV: Optional[Tensor], tail_bound: float):
+    """z_m (B,M), V_m (B,d,M)|None, cw/ch/dv (B,M,K+1), CW/CH/DV (B,d,M,K+1)|None ->
+    (x_m (B,M), V_out (B,d,M)|None, bin (B,M) int32)."""
+    lib = _lib.load()
+    z_m, cw, ch, dv = _req(z_m, "z_m"), _req(cw, "cw"), _req(ch, "ch"), _req(dv, "dv")
+    B, M = z_m.shape
+    K = cw.shape[-1] - 1
+    assert cw.shape == ch.shape == dv.shape == (B, M, K + 1), (cw.shape, ch.shape, dv.shape)
+    d = 0 if V_m is None else V_m.shape[1]
+    if d:
+        V_m, CW, CH, DV = _req(V_m, "V_m"), _req(CW, "CW"), _req(CH, "CH"), _req(DV, "DV")
+        assert V_m.shape == (B, d, M) and CW.shape == CH.shape == DV.shape == (B, d, M, K + 1)
+    x_m = torch.empty_like(z_m)
+    V_out = torch.empty_like(V_m) if d else None
+    bins = torch.empty(B, M, dtype=torch.int32, device=z_m.device)
+    with torch.cuda.device(z_m.device):
+        _lib.check(lib.cmf_rqs_coupling_jvp_fwd(B, d, M, K, float(tail_bound), _ptr(z_m), _ptr(V_m), _ptr(cw), _ptr(ch),
+                                                _ptr(dv), _ptr(CW), _ptr(CH), _ptr(DV), _ptr(x_m), _ptr(V_out),
+                                                _ptr(bins), _stream()), "cmf_rqs_coupling_jvp_fwd")
+    return x_m, V_out, bins
+
+
+def rqs_coupling_jvp_bwd(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound, g_x, g_V):
+    """returns (g_z, g_Vin|None, g_cw, g_ch, g_dv, g_CW|None, g_CH|None, g_DV|None)"""
+    lib = _lib.load()
+    z_m, cw, ch, dv = _req(z_m, "z_m"), _req(cw, "cw"), _req(ch, "ch"), _req(dv, "dv")
+    B, M = z_m.shape
+    K = cw.shape[-1] - 1
+    d = 0 if V_m is None else V_m.shape[1]
+    if d:
+        V_m, CW, CH, DV, g_V = _req(V_m, "V_m"), _req(CW, "CW"), _req(CH, "CH"), _req(DV, "DV"), _req(g_V, "g_V")
+    if g_x is not None:
+        g_x = _req(g_x, "g_x")
+    g_z, g_cw, g_ch, g_dv = torch.empty_like(z_m), torch.empty_like(cw), torch.empty_like(ch), torch.empty_like(dv)
+    g_Vin = torch.empty_like(V_m) if d else None
+    g_CW, g_CH, g_DV = (torch.empty_like(CW), torch.empty_like(CH), torch.empty_like(DV)) if d else (None, None, None)
+    with torch.cuda.device(z_m.device):
+        _lib.check(lib.cmf_rqs_coupling_jvp_bwd(B, d, M, K, float(tail_bound), _ptr(z_m), _ptr(V_m), _ptr(cw), _ptr(ch),
+                                                _ptr(dv), _ptr(CW), _ptr(CH), _ptr(DV), _ptr(g_x), _ptr(g_V),
+                                                _ptr(g_z), _ptr(g_Vin), _ptr(g_cw), _ptr(g_ch), _ptr(g_dv),
+                                                _ptr(g_CW), _ptr(g_CH), _ptr(g_DV), _stream()),
+                   "cmf_rqs_coupling_jvp_bwd")
+    return g_z, g_Vin, g_cw, g_ch, g_dv, g_CW, g_CH, g_DV

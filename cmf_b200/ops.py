@@ -161,3 +161,34 @@ def chol_logdet_l1(G: Tensor, penalty: str = "none") -> Tuple[Tensor, Tensor]:
     if penalty == "none":
         l1 = torch.zeros_like(logdet)
     return logdet, l1
+
+
+class _RqsCouplingJVP(Function):
+    @staticmethod
+    def forward(ctx, z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound):
+        x_m, V_out, bins = kernels.rqs_coupling_jvp_fwd(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound)
+        ctx.save_for_backward(z_m, V_m, cw, ch, dv, CW, CH, DV)
+        ctx.tail_bound = tail_bound
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(bins)
+        if V_out is None:
+            return x_m, None, bins
+        return x_m, V_out, bins
+
+    @staticmethod
+    def backward(ctx, g_x, g_V, _g_bins):
+        z_m, V_m, cw, ch, dv, CW, CH, DV = ctx.saved_tensors
+        if V_m is not None and g_V is None:
+            g_V = torch.zeros_like(V_m)
+        out = kernels.rqs_coupling_jvp_bwd(z_m, V_m, cw, ch, dv, CW, CH, DV, ctx.tail_bound, g_x, g_V)
+        return (*out, None)
+
+
+def rqs_coupling_jvp(z_m: Tensor, V_m: Optional[Tensor], cw: Tensor, ch: Tensor, dv: Tensor,
+                     CW: Optional[Tensor], CH: Optional[Tensor], DV: Optional[Tensor], tail_bound: float):
+    """Inverse rational-quadratic spline (z -> x) on the transformed half, primal + d tangents.
+
+    Knot tables from :func:`cmf_b200.splines.knot_tables`.  Returns ``(x_m, V_out, bin)``; ``bin``
+    (int32, -1 outside the interval) is bit-identical to the reference's
+    ``utils.searchsorted(cumheights, inputs)`` (`gitmodules/nsf/utils/torchutils.py:133-138`)."""
+    return _RqsCouplingJVP.apply(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound)

@@ -116,6 +116,30 @@ int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
                         const float* g_logdet, const float* g_l1, int penalty,
                         float* g_G, cmf_stream_t stream);
 
+/* Rational-quadratic spline coupling, inverse direction (z -> x), primal + d tangent columns.
+ * Arithmetic of gitmodules/nsf/nde/transforms/splines/rational_quadratic.py:13-52,96-112 (linear
+ * tails: identity outside [-tail_bound, tail_bound]) and the bin search of
+ * gitmodules/nsf/utils/torchutils.py:133-138, done with __ballot_sync/__popc over the K+1 <= 32
+ * height knots of an element.  The reference's cmf wrapper (bijections/nsf.py:19-42) has no _jvp
+ * (SURVEY D4): the tangent push is new; its oracle is autograd over the nsf arithmetic.
+ *   cw, ch, dv (B,M,K+1): cumulative widths / heights and knot derivatives, built by the host with
+ *   the reference's torch ops (bit-identical knots => bit-identical bins); CW, CH, DV (B,d,M,K+1)
+ *   their tangents.  bin (B,M) int32 (may be NULL): selected bin, -1 outside the interval. */
+int cmf_rqs_coupling_jvp_fwd(int B, int d, int M, int K, float tail_bound,
+                             const float* z_m, const float* V_m,
+                             const float* cw, const float* ch, const float* dv,
+                             const float* CW, const float* CH, const float* DV,
+                             float* x_m, float* V_out, int32_t* bin, cmf_stream_t stream);
+/* Adjoint w.r.t. z, its tangents, the three knot tables and their tangents (dense, zero outside
+ * the two selected knots).  g_x may be NULL. */
+int cmf_rqs_coupling_jvp_bwd(int B, int d, int M, int K, float tail_bound,
+                             const float* z_m, const float* V_m,
+                             const float* cw, const float* ch, const float* dv,
+                             const float* CW, const float* CH, const float* DV,
+                             const float* g_x, const float* g_V,
+                             float* g_z, float* g_Vin, float* g_cw, float* g_ch, float* g_dv,
+                             float* g_CW, float* g_CH, float* g_DV, cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
