@@ -8,6 +8,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from cmf_b200 import kernels as K
+K_ = K
 
 DEV = "cuda"
 PEAKS = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
@@ -85,9 +86,26 @@ def bench_chol():
         report(f"torch.linalg.cholesky B={B} d={d}", t, 8.0 * d * d * B, d ** 3 / 3.0 * B)
 
 
+def bench_rqs():
+    from cmf_b200 import splines
+    for (B, d, M, K, tb) in [(512, 64, 392, 8, 3.0), (64, 16, 392, 8, 3.0), (5000, 6, 3, 8, 3.0)]:
+        z = (torch.rand(B, M, device=DEV) * 2 - 1) * tb * 1.1
+        p = torch.randn(B, M, 3 * K - 1, device=DEV)
+        V = torch.randn(B, d, M, device=DEV)
+        P = torch.randn(B, d, M, 3 * K - 1, device=DEV)
+        cw, ch, dv, CW, CH, DV = [t.contiguous() for t in splines.knot_tables(p, P, K, tb, hidden_features=32)]
+        gx, gV = torch.randn(B, M, device=DEV), torch.randn(B, d, M, device=DEV)
+        tab = 3 * (K + 1) * 4.0
+        t = timeit(lambda: K_.rqs_coupling_jvp_fwd(z, V, cw, ch, dv, CW, CH, DV, tb))
+        report(f"rqs_fwd B={B} d={d} M={M} K={K}", t, B * M * ((4 + tab + 8) + d * (4 + tab + 4)))
+        t = timeit(lambda: K_.rqs_coupling_jvp_bwd(z, V, cw, ch, dv, CW, CH, DV, tb, gx, gV))
+        report(f"rqs_bwd B={B} d={d} M={M} K={K}", t, B * M * ((8 + tab + 4 + tab) + d * (8 + tab + 4 + tab)))
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "all"
     torch.backends.cuda.matmul.allow_tf32 = False
     if what in ("gram", "all"): bench_gram()
     if what in ("coupling", "all"): bench_coupling()
     if what in ("chol", "all"): bench_chol()
+    if what in ("rqs", "all"): bench_rqs()
