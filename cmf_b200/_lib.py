@@ -32,6 +32,9 @@ SIGNATURES = {
     "cmf_chol_logdet_bwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "cmf_rqs_coupling_jvp_fwd": (_i, [_i, _i, _i, _i, C.c_float] + [_vp] * 12),
     "cmf_rqs_coupling_jvp_bwd": (_i, [_i, _i, _i, _i, C.c_float] + [_vp] * 19),
+    "cmf_conv3x3_c64_usable": (_i, [_i, _i, _i]),
+    "cmf_conv3x3_c64_prep": (_i, [_vp, _i, _vp, _vp]),
+    "cmf_conv3x3_c64_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None

@@ -45,7 +45,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: cannot build libcmf_b200.so")
     os.makedirs(os.path.dirname(LIB), exist_ok=True)
-    cmd = [nvcc, *NVCC_FLAGS, *(["-Xptxas", "-v"] if verbose else []), "-o", LIB + ".tmp", *sources()]
+    extra = os.environ.get("CMF_NVCC_EXTRA", "").split()      # e.g. -DCMF_CONV_PROF for the clock64 trace
+    cmd = [nvcc, *NVCC_FLAGS, *extra, *(["-Xptxas", "-v"] if verbose else []), "-o", LIB + ".tmp", *sources()]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if verbose or res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)

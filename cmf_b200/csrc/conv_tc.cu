@@ -1,0 +1,348 @@
+// 3x3 convolution, 64 -> 64 channels, stride 1, zero padding 1, NCHW fp32, on tcgen05 with 3xTF32.
+//
+// This is the conditioner hot spot of the image configs: every residual block of
+// the coupler ResNet (`networks.py:35-94,116-161` of the reference) applies two such convolutions to
+// the primal AND to all d tangent columns (`jvp_layers.py:49-64`), i.e. to B*(1+d) images per call.
+//
+// Formulation (implicit GEMM, nothing is materialised):
+//     y[n, co, p] = sum_{tap, ci} x[n, ci, p + dy*W + dx] * w[co, ci, tap]      (p = flat pixel)
+//   M = 128 consecutive flat pixels of one image, N = 64 output channels, K = 9 taps x 64 inputs.
+//   * The pixel operand lives in TENSOR MEMORY.  One TMA box per (tile, 32-channel chunk) brings the
+//     tile plus a halo of W+1 pixels on either side into shared memory ([channel][pixel], rows
+//     above/below the image are zero-filled by TMA's out-of-bounds rule).  A "row worker" thread
+//     owns one output pixel: for each of the 9 taps it reads its 32 shifted inputs, zeroes them
+//     when the tap leaves the image row (x + dx outside [0, W)), splits them exactly into a
+//     TF32 head and a remainder (v = hi + lo) and writes both to TMEM with tcgen05.st.  The MMA
+//     therefore reads only the weights from shared memory (2 KB per instruction instead of 6 KB):
+//     the tensor pipe is no longer bound by shared-memory bandwidth as the SS-mode Gram is.
+//   * The weights arrive pre-split (hi | lo, tap-major, K-major rows) from a tiny prep kernel and
+//     are streamed by TMA through a 4-deep ring; each stage is shared by the two pixel tiles of
+//     the CTA, which halves the L2 -> SM traffic (the L2 slice throughput, not HBM, is the limit
+//     once the pixel operand is read once instead of 9 times).
+//   * Three MMAs per K-step: hi*Whi + hi*Wlo + lo*Whi (lo*Wlo ~ 2^-22 relative is dropped, as in
+//     the Gram kernel).  The tensor core's FP32 accumulator truncates, so the accumulator is
+//     drained into registers with round-to-nearest adds every 6 stages (K = 192).
+//   * The same kernel is the data gradient: dgrad = conv(g_y, w^T flipped); the prep kernel writes
+//     that variant of the weights.
+#include "common.cuh"
+#include "tc_common.cuh"
+#include <cstdlib>
+
+namespace cmf {
+using namespace tc;
+
+namespace {
+
+constexpr int kC = 64;                 // channels (in = out)
+constexpr int kTileM = 128;            // output pixels per tile (TMEM lanes)
+constexpr int kTiles = 2;              // tiles per CTA sharing one weight stream
+constexpr int kChunkC = 32;            // input channels per stage (K = 32)
+constexpr int kTaps = 9;
+constexpr int kStages = 2 * kTaps;     // per tile: 2 channel chunks x 9 taps
+constexpr int kSeg = 6;                // stages per drained segment
+constexpr int kWRing = 4;
+constexpr int kWStageBytes = 2 * kC * kChunkC * 4;     // hi + lo tile: 16 KB
+constexpr int kMmaWarp1 = 2 + 4 * kTiles;              // second MMA issuer (tile 1)
+constexpr int kConvThreads = 32 * (3 + 4 * kTiles);    // 352
+constexpr int kConvTmemCols = 512;
+constexpr int kMaxBox = 256;
+
+__device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+#ifdef CMF_CONV_PROF
+__device__ long long g_conv_prof[128];
+#define PROF(i) do { if (blockIdx.x == 5000 && lane == 0) g_conv_prof[(i)] = clock64(); } while (0)
+#else
+#define PROF(i) do { } while (0)
+#endif
+
+struct ConvParams {
+    int N, H, W, HW;
+    int tiles_per_image;
+    long long total_tiles;
+    int hl;                            // halo pixels in front of the tile: W+1 rounded up to 4 (TMA needs 16-byte box starts)
+    const float* bias;                 // (64) or null
+    float* y;
+};
+
+// weight prep: w (co, ci, 3, 3) -> out[part][tap][row][col] with part 0 = TF32 head, 1 = remainder.
+// transpose == 0: row = co, col = ci, tap = ky*3+kx            (forward / tangent push)
+// transpose == 1: row = ci, col = co, tap = (2-ky)*3 + (2-kx)  (data gradient)
+__global__ void conv_prep_kernel(const float* __restrict__ w, int transpose, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= kTaps * kC * kC) return;
+    const int col = i % kC, row = (i / kC) % kC, tap = i / (kC * kC);
+    int co, ci, t;
+    if (!transpose) { co = row; ci = col; t = tap; }
+    else { ci = row; co = col; t = kTaps - 1 - tap; }
+    const float v = __ldg(w + ((long long)co * kC + ci) * kTaps + t);
+    float hi, lo;
+    split_tf32(v, hi, lo);
+    out[i] = hi;
+    out[kTaps * kC * kC + i] = lo;
+}
+
+// kPitch = pixels per halo row in shared memory = TMA box width (compile-time so that the 32
+// channel loads of a row worker are LDS with immediate offsets): 192 covers W <= 31, 256 W <= 61.
+template <int kPitch>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmw, ConvParams P) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ uint64_t w_full[kWRing], done[kWRing];     // done[s % 4]: the MMAs of stage s have completed for both tiles
+    __shared__ uint64_t a_full[kTiles][2];
+    __shared__ uint64_t at_full[kTiles][2];
+    __shared__ uint32_t tmem_base_smem;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 2) PROF(0);
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* wring = smem;                                         // kWRing x 16 KB, 1024-aligned
+    float* halo = reinterpret_cast<float*>(smem + kWRing * kWStageBytes);   // [tile][chunk][32][kPitch]
+    constexpr int kHaloElems = kChunkC * kPitch;
+
+    const long long tile0 = (long long)blockIdx.x * kTiles;
+    bool active[kTiles];
+    int img[kTiles], p0[kTiles];
+#pragma unroll
+    for (int t = 0; t < kTiles; ++t) {
+        const long long T = tile0 + t;
+        active[t] = T < P.total_tiles;
+        img[t] = active[t] ? (int)(T / P.tiles_per_image) : 0;
+        p0[t] = active[t] ? (int)(T % P.tiles_per_image) * kTileM : 0;
+    }
+
+    if (threadIdx.x == 0) {
+        for (int r = 0; r < kWRing; ++r) { mbar_init(&w_full[r], 1); mbar_init(&done[r], active[1] ? 2 : 1); }
+        for (int t = 0; t < kTiles; ++t) {
+            for (int c = 0; c < 2; ++c) {
+                mbar_init(&a_full[t][c], 1);
+                mbar_init(&at_full[t][c], kTileM / 32);     // one arrival per worker warp
+            }
+        }
+        mbar_fence_init();
+        prefetch_tmap(&tmx);
+        prefetch_tmap(&tmw);
+    }
+    if (warp == 1) tmem_alloc<kConvTmemCols>(&tmem_base_smem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+    if (warp == 2) PROF(1);
+    // TMEM columns: [0,256) accumulators, (tile, segment parity) -> 64 cols; [256,512) operand staging,
+    // (tile, buffer) -> 64 cols (hi | lo)
+    constexpr uint32_t kAccCol = 0, kStgCol = 256;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            constexpr uint32_t halo_bytes = (uint32_t)kHaloElems * 4u;
+            auto load_halo = [&](int c) {
+#pragma unroll
+                for (int t = 0; t < kTiles; ++t) {
+                    if (!active[t]) continue;
+                    mbar_arrive_expect_tx(&a_full[t][c], halo_bytes);
+                    tma_load_2d(halo + (size_t)(t * 2 + c) * kHaloElems, &tmx, &a_full[t][c], p0[t] - P.hl,
+                                img[t] * kC + c * kChunkC);
+                }
+            };
+            load_halo(0);
+            for (int s = 0; s < kStages; ++s) {
+                const int r = s % kWRing;
+                if (s >= kWRing) mbar_wait(&done[r], ((s / kWRing) - 1) & 1);
+                const int chunk = s / kTaps, tap = s % kTaps;
+                uint8_t* dst = wring + (size_t)r * kWStageBytes;
+                mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
+                tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
+                tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
+                if (s == 1) load_halo(1);
+            }
+        }
+    } else if (warp == 1 || warp == kMmaWarp1) {
+        // ------------------------------------------------------------------ MMA issuers, one warp per tile
+        // (the issue path of a single thread is latency-bound at ~50 cycles per tcgen05.mma; two
+        // issuers keep the tensor pipe fed).  The whole warp walks the loop converged; one elected
+        // lane issues.
+        const int t = warp == 1 ? 0 : 1;
+        if (active[t]) {
+            constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
+            const uint32_t acc0 = tmem_base + kAccCol + (uint32_t)(t * 2 * kC);
+            const uint32_t wring_addr = smem_u32(wring);
+            for (int s = 0; s < kStages; ++s) {
+                const int r = s % kWRing;
+                const int seg = s / kSeg, b = s & 1;
+                mbar_wait(&w_full[r], (s / kWRing) & 1);
+                mbar_wait(&at_full[t][b], (s >> 1) & 1);
+                // accumulator (seg & 1) was drained (segment seg-2) by every worker warp BEFORE it arrived on
+                // at_full for this stage (program order + tcgen05.wait::ld), so no extra barrier is needed
+                tc_fence_after();
+                const uint32_t acc = acc0 + (uint32_t)((seg & 1) * kC);
+                if (elect_one()) {
+                    const uint64_t dbh = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes));
+                    const uint64_t dbl = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes + kWStageBytes / 2));
+                    const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64);
+                    const uint32_t a_lo = a_hi + 32;
+#pragma unroll
+                    for (int k = 0; k < kChunkC / 8; ++k) {      // +32 bytes along K = +2 in the descriptor's address field
+                        umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, (s % kSeg != 0) || k != 0);
+                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, 1);
+                        umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                    }
+                    umma_commit(&done[r]);      // frees the weight slot and this tile's staging buffer; ends a segment
+                }
+                __syncwarp();
+                if (t == 0) PROF(32 + s);
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ row workers
+        const int t = (warp - 2) >> 2;
+        if (active[t]) {
+            const int rb = warp & 3;                       // TMEM lane quarter this warp may touch
+            const int m = rb * 32 + lane;                  // row of the tile = output pixel p0 + m
+            const int p = p0[t] + m;
+            const int xx = p % P.W;
+            const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
+            const uint32_t row_addr = smem_u32(halo) + (uint32_t)((t * 2 * kHaloElems + P.hl + m) * 4);
+            // the tap leaves the image row on the left (dx = -1) / right (dx = +1): operand reads as zero
+            const bool ok_l = xx > 0, ok_r = xx + 1 < P.W;
+            float accr[kC];
+#pragma unroll
+            for (int j = 0; j < kC; ++j) accr[j] = 0.f;
+            // software pipeline: the 32 shared-memory loads of stage s+1 are issued while the
+            // tcgen05.st of stage s is in flight (its completion wait is the longest latency here)
+            float v[32];
+            auto load_stage = [&](int s) {
+                const int chunk = s / kTaps, tap = s - chunk * kTaps;
+                const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
+                if (tap == 0) mbar_wait(&a_full[t][chunk], 0);
+                const uint32_t src = row_addr + (uint32_t)((chunk * kHaloElems + dy * P.W + dx) * 4);
+#pragma unroll
+                for (int c = 0; c < kChunkC; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
+            };
+            load_stage(0);
+            for (int s = 0; s < kStages; ++s) {
+                const int b = s & 1;
+                const int tap = s % kTaps, dx = tap % 3 - 1;
+                const bool ok = dx < 0 ? ok_l : (dx > 0 ? ok_r : true);
+                const uint32_t mh = ok ? 0xFFFFE000u : 0u;
+                const float okf = ok ? 1.f : 0.f;
+                float hi[32], lo[32];
+#pragma unroll
+                for (int c = 0; c < kChunkC; ++c) {
+                    hi[c] = __uint_as_float(__float_as_uint(v[c]) & mh);       // TF32 head (0 when masked)
+                    lo[c] = fmaf(v[c], okf, -hi[c]);                           // exact remainder
+                }
+                PROF(64 + s);
+                if (s >= 2) mbar_wait(&done[(s - 2) % kWRing], ((s - 2) / kWRing) & 1);
+                PROF(96 + s);
+                tc_fence_after();
+                const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64) + lane_addr;
+                tmem_st_32x32(stg, hi);
+                tmem_st_32x32(stg + 32, lo);
+                if (s + 1 < kStages) load_stage(s + 1);
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&at_full[t][b]);
+                if (warp == 2) PROF(2 + s);
+                // drain segment g = s / kSeg one stage late (at its last stage only for the final
+                // segment), so the tensor pipe already works on segment g+1 in the other accumulator
+                const bool last = s == kStages - 1;
+                if ((s % kSeg == 0 && s > 0) || last) {
+                    const int e = last ? s : s - 1;                 // final stage of the segment to drain
+                    const int g = e / kSeg;
+                    mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
+                    tc_fence_after();
+                    const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + (g & 1)) * kC) + lane_addr;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        float u[32];
+                        tmem_ld_32x32(acc + h * 32, u);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) accr[h * 32 + j] += u[j];
+                    }
+                    tc_fence_before();
+                }
+            }
+            if (p < P.HW) {
+                float* yo = P.y + (long long)img[t] * kC * P.HW + p;
+#pragma unroll
+                for (int j = 0; j < kC; ++j) yo[(long long)j * P.HW] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+            }
+            if (warp == 2) PROF(30);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kConvTmemCols>(tmem_base);
+    }
+}
+
+}  // namespace
+
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_conv3x3_c64_prep(const float* w, int transpose, float* wsplit, cmf_stream_t stream) {
+    CMF_REQUIRE(w && wsplit, "conv_prep: null pointer");
+    const int n = kTaps * kC * kC;
+    conv_prep_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(w, transpose != 0, wsplit);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int cmf_conv3x3_c64_usable(int N, int H, int W) {
+    if (N <= 0 || H <= 0 || W <= 0) return 0;
+    const long long HW = (long long)H * W;
+    const int need = kTileM + ((W + 4) & ~3) + (W + 1);        // halo box: front halo + tile + back halo
+    return (HW % 4 == 0) && need <= kMaxBox && (long long)N * kC < (1LL << 31) && HW < (1LL << 24);
+}
+
+extern "C" int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                                   float* y, cmf_stream_t stream) {
+    CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3: negative size");
+    if (N == 0 || H == 0 || W == 0) return 0;
+    CMF_REQUIRE(x && wsplit && y, "conv3x3: null pointer");
+    CMF_REQUIRE(cmf_conv3x3_c64_usable(N, H, W), "conv3x3: unsupported image size %dx%d (need H*W %% 4 == 0, W <= 61)", H, W);
+    CMF_REQUIRE(aligned16(x) && aligned16(wsplit), "conv3x3: x and wsplit must be 16-byte aligned");
+    ConvParams P{};
+    P.N = N; P.H = H; P.W = W; P.HW = H * W;
+    P.tiles_per_image = (int)ceil_div(P.HW, kTileM);
+    P.total_tiles = (long long)N * P.tiles_per_image;
+    P.hl = (W + 4) & ~3;
+    P.bias = bias; P.y = y;
+    const int pitch = (kTileM + P.hl + W + 1 <= 192) ? 192 : 256;
+    CUtensorMap tmx, tmw;
+    int rc = make_tmap_2d_plain_f32(&tmx, x, (uint64_t)N * kC, (uint64_t)P.HW, (uint64_t)P.HW, (uint32_t)pitch, kChunkC);
+    if (rc != 0) return rc;
+    rc = make_tmap_2d_f32(&tmw, wsplit, (uint64_t)2 * kTaps * kC, (uint64_t)kC, (uint64_t)kC, kC, 0);
+    if (rc != 0) return rc;
+    const size_t smem = (size_t)kWRing * kWStageBytes + (size_t)kTiles * 2 * kChunkC * pitch * 4 + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_tc_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(conv3x3_tc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) { set_error("conv3x3 attr: %s", cudaGetErrorString(e)); return (int)e; }
+        attr_set = true;
+    }
+    const unsigned grid = (unsigned)ceil_div(P.total_tiles, kTiles);
+    if (pitch == 192) conv3x3_tc_kernel<192><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmx, tmw, P);
+    else conv3x3_tc_kernel<256><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmx, tmw, P);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+#ifdef CMF_CONV_PROF
+extern "C" int cmf_debug_conv_prof(long long* host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, g_conv_prof, sizeof(long long) * 128);
+}
+#endif

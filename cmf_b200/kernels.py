@@ -202,3 +202,40 @@ def rqs_coupling_jvp_bwd(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound, g_x, g_V)
                                                 _ptr(g_CW), _ptr(g_CH), _ptr(g_DV), _stream()),
                    "cmf_rqs_coupling_jvp_bwd")
     return g_z, g_Vin, g_cw, g_ch, g_dv, g_CW, g_CH, g_DV
+
+
+# ------------------------------------------------------------------ conditioner convolution (N1)
+CONV_WSPLIT_FLOATS = 2 * 9 * 64 * 64
+
+
+def conv3x3_c64_usable(N: int, H: int, W: int) -> bool:
+    return bool(_lib.load().cmf_conv3x3_c64_usable(int(N), int(H), int(W)))
+
+
+def conv3x3_c64_prep(weight: Tensor, transpose: bool) -> Tensor:
+    """weight (64,64,3,3) -> pre-split (TF32 head | remainder), tap-major weights for
+    ``conv3x3_c64``; ``transpose`` selects the data-gradient variant."""
+    lib = _lib.load()
+    weight = _req(weight, "weight")
+    assert weight.shape == (64, 64, 3, 3), weight.shape
+    out = torch.empty(CONV_WSPLIT_FLOATS, dtype=torch.float32, device=weight.device)
+    with torch.cuda.device(weight.device):
+        _lib.check(lib.cmf_conv3x3_c64_prep(_ptr(weight), int(bool(transpose)), _ptr(out), _stream()),
+                   "cmf_conv3x3_c64_prep")
+    return out
+
+
+def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None) -> Tensor:
+    """x (N,64,H,W), wsplit from ``conv3x3_c64_prep`` -> y (N,64,H,W)."""
+    lib = _lib.load()
+    x, wsplit = _req(x, "x"), _req(wsplit, "wsplit")
+    N, C, H, W = x.shape
+    assert C == 64 and wsplit.numel() == CONV_WSPLIT_FLOATS
+    if bias is not None:
+        bias = _req(bias, "bias")
+        assert bias.numel() == 64
+    y = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_conv3x3_c64_fwd(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(y), _stream()),
+                   "cmf_conv3x3_c64_fwd")
+    return y

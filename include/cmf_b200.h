@@ -116,6 +116,22 @@ int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
                         const float* g_logdet, const float* g_l1, int penalty,
                         float* g_G, cmf_stream_t stream);
 
+/* Conditioner convolution: 3x3, 64 -> 64 channels, stride 1, zero padding 1, NCHW
+ * fp32 -- the two convolutions of every residual block of the coupler ResNet
+ * (cmf/models/components/networks.py:35-94,116-161), applied to the primal and to all d tangent
+ * columns (jvp_layers.py:49-64).  Replaces the cuDNN FP32 calls F.conv2d issues there.  tcgen05
+ * kind::tf32 with the 3xTF32 split (pixel operand staged in tensor memory, weights pre-split by
+ * cmf_conv3x3_c64_prep), FP32 round-to-nearest accumulation across K segments: results agree with
+ * an FP32 convolution to ~1e-6 relative.
+ *   prep:  w (64,64,3,3) -> wsplit (2*9*64*64 floats, 16-byte aligned).  transpose = 0 for the
+ *          forward / tangent push, 1 for the data gradient (g_x = conv(g_y, prep(w, 1))).
+ *   fwd:   x (N,64,H,W) -> y (N,64,H,W) (+ bias (64), may be NULL).  Needs H*W % 4 == 0 and
+ *          W <= 63 (cmf_conv3x3_c64_usable); other shapes stay on the library path. */
+int cmf_conv3x3_c64_usable(int N, int H, int W);
+int cmf_conv3x3_c64_prep(const float* w, int transpose, float* wsplit, cmf_stream_t stream);
+int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                        float* y, cmf_stream_t stream);
+
 /* Rational-quadratic spline coupling, inverse direction (z -> x), primal + d tangent columns.
  * Arithmetic of gitmodules/nsf/nde/transforms/splines/rational_quadratic.py:13-52,96-112 (linear
  * tails: identity outside [-tail_bound, tail_bound]) and the bin search of
