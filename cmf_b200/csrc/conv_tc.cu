@@ -39,7 +39,7 @@ constexpr int kTiles = 2;              // tiles per CTA sharing one weight strea
 constexpr int kChunkC = 32;            // input channels per stage (K = 32)
 constexpr int kTaps = 9;
 constexpr int kStages = 2 * kTaps;     // per tile: 2 channel chunks x 9 taps
-constexpr int kSeg = 6;                // stages per drained segment
+constexpr int kSeg = 1;                // stages per drained segment (K = 32)
 constexpr int kWRing = 4;
 constexpr int kWStageBytes = 2 * kC * kChunkC * 4;     // hi + lo tile: 16 KB
 constexpr int kMmaWarp1 = 2 + 4 * kTiles;              // second MMA issuer (tile 1)
@@ -80,8 +80,10 @@ __global__ void conv_prep_kernel(const float* __restrict__ w, int transpose, flo
     if (!transpose) { co = row; ci = col; t = tap; }
     else { ci = row; co = col; t = kTaps - 1 - tap; }
     const float v = __ldg(w + ((long long)co * kC + ci) * kTaps + t);
-    float hi, lo;
-    split_tf32(v, hi, lo);
+    // round-to-nearest head: the remainder is signed and half as large, so the tensor core's
+    // truncation of it to TF32 is unbiased
+    const float hi = __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
+    const float lo = v - hi;
     out[i] = hi;
     out[kTaps * kC * kC + i] = lo;
 }
@@ -186,12 +188,16 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                     const uint64_t dbl = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes + kWStageBytes / 2));
                     const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64);
                     const uint32_t a_lo = a_hi + 32;
+                    // cross terms first: they land in a fresh (small) accumulator, where the tensor
+                    // core's truncating FP32 add costs nothing; only the hi*hi adds that follow see a
+                    // large accumulator (kSeg * 4 - 1 truncations per drained segment)
 #pragma unroll
                     for (int k = 0; k < kChunkC / 8; ++k) {      // +32 bytes along K = +2 in the descriptor's address field
-                        umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, (s % kSeg != 0) || k != 0);
-                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, 1);
+                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, (s % kSeg != 0) || k != 0);
                         umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
                     }
+#pragma unroll
+                    for (int k = 0; k < kChunkC / 8; ++k) umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
                     umma_commit(&done[r]);      // frees the weight slot and this tile's staging buffer; ends a segment
                 }
                 __syncwarp();
@@ -234,8 +240,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                 float hi[32], lo[32];
 #pragma unroll
                 for (int c = 0; c < kChunkC; ++c) {
-                    hi[c] = __uint_as_float(__float_as_uint(v[c]) & mh);       // TF32 head (0 when masked)
-                    lo[c] = fmaf(v[c], okf, -hi[c]);                           // exact remainder
+                    hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & mh);   // TF32 head, round to nearest (0 when masked)
+                    lo[c] = fmaf(v[c], okf, -hi[c]);                                   // exact signed remainder
                 }
                 PROF(64 + s);
                 if (s >= 2) mbar_wait(&done[(s - 2) % kWRing], ((s - 2) / kWRing) & 1);
@@ -250,11 +256,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&at_full[t][b]);
                 if (warp == 2) PROF(2 + s);
-                // drain segment g = s / kSeg one stage late (at its last stage only for the final
-                // segment), so the tensor pipe already works on segment g+1 in the other accumulator
-                const bool last = s == kStages - 1;
-                if ((s % kSeg == 0 && s > 0) || last) {
-                    const int e = last ? s : s - 1;                 // final stage of the segment to drain
+                // drain a segment one stage late (the final one at its own last stage), so the tensor
+                // pipe already works on the next segment in the other accumulator
+                auto drain = [&](int e) {                           // e = final stage of the segment
                     const int g = e / kSeg;
                     mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
                     tc_fence_after();
@@ -267,7 +271,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                         for (int j = 0; j < 32; ++j) accr[h * 32 + j] += u[j];
                     }
                     tc_fence_before();
-                }
+                };
+                if (s % kSeg == 0 && s > 0) drain(s - 1);
+                if (s == kStages - 1) drain(s);
             }
             if (p < P.HW) {
                 float* yo = P.y + (long long)img[t] * kC * P.HW + p;

@@ -14,11 +14,31 @@ from __future__ import annotations
 
 from typing import Sequence, Tuple
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
 Tensor = torch.Tensor
+
+# CMF_CONV=cudnn keeps every conditioner convolution on the library path (A/B measurements)
+_TC_CONV = os.environ.get("CMF_CONV", "tc") != "cudnn"
+
+
+def _conv3x3_pair(conv: nn.Conv2d, h: Tensor, Hv):
+    """``conv(h)`` and the bias-free tangent push ``conv.weight * Hv`` (`jvp_layers.py:49-64`).
+    64 -> 64 channel 3x3 convolutions run on the tcgen05 kernel (weights pre-split once for both
+    calls); other shapes are library calls."""
+    from . import kernels, ops
+    if _TC_CONV and ops.conv3x3_c64_usable(h, conv.weight):
+        ws = kernels.conv3x3_c64_prep(conv.weight.detach(), False)
+        y = ops.conv3x3_c64(h, conv.weight, conv.bias, ws)
+        if Hv is not None and ops.conv3x3_c64_usable(Hv, conv.weight):
+            return y, ops.conv3x3_c64(Hv, conv.weight, None, ws)
+        Y = None if Hv is None else F.conv2d(Hv, conv.weight, None, padding=1)
+        return y, Y
+    return conv(h), (None if Hv is None else F.conv2d(Hv, conv.weight, None, padding=1))
 
 
 def _bcast(t: Tensor) -> Tensor:
@@ -65,15 +85,17 @@ class ResidualBlock(nn.Module):
         self.conv2 = nn.Conv2d(channels, channels, 3, padding=1, bias=True)
 
     def forward(self, x: Tensor) -> Tensor:
-        return self.conv2(torch.relu(self.conv1(torch.relu(x)))) + x
+        h = x
+        for conv in (self.conv1, self.conv2):
+            h, _ = _conv3x3_pair(conv, torch.relu(h), None)
+        return h + x
 
     def jvp_batched(self, x: Tensor, V: Tensor, d: int) -> Tuple[Tensor, Tensor]:
         """x (B,C,H,W), V (B*d,C,H,W)."""
         h, Hv = x, V
         for conv in (self.conv1, self.conv2):
             Hv = _mask_rows(Hv, h > 0, d)
-            h = conv(torch.relu(h))
-            Hv = F.conv2d(Hv, conv.weight, None, padding=1)
+            h, Hv = _conv3x3_pair(conv, torch.relu(h), Hv)
         return h + x, Hv + V
 
 

@@ -192,3 +192,42 @@ def rqs_coupling_jvp(z_m: Tensor, V_m: Optional[Tensor], cw: Tensor, ch: Tensor,
     (int32, -1 outside the interval) is bit-identical to the reference's
     ``utils.searchsorted(cumheights, inputs)`` (`gitmodules/nsf/utils/torchutils.py:133-138`)."""
     return _RqsCouplingJVP.apply(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound)
+
+
+class _Conv3x3C64(Function):
+    """3x3 / 64 -> 64 / pad 1 convolution on the tcgen05 kernel.  The data gradient is the same
+    kernel on the transposed, flipped weights; the weight gradient stays a library call
+    (``aten::convolution_backward``) until the tcgen05 wgrad lands."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, wsplit):
+        if wsplit is None:
+            wsplit = kernels.conv3x3_c64_prep(weight, False)
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        return kernels.conv3x3_c64(x, wsplit, bias)
+
+    @staticmethod
+    def backward(ctx, g_y):
+        x, weight = ctx.saved_tensors
+        g_y = g_y.contiguous()
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        g_x = kernels.conv3x3_c64(g_y, kernels.conv3x3_c64_prep(weight, True), None) if need_x else None
+        g_w = None
+        if need_w:
+            g_w = torch.ops.aten.convolution_backward(g_y, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                                      (False, True, False))[1]
+        g_b = g_y.sum(dim=(0, 2, 3)) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return g_x, g_w, g_b, None
+
+
+def conv3x3_c64(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, wsplit: Optional[Tensor] = None) -> Tensor:
+    """``F.conv2d(x, weight, bias, padding=1)`` for weight (64,64,3,3) (`networks.py:35-94`: the
+    residual-block convolutions of the coupler ResNet).  ``wsplit`` = a cached
+    ``kernels.conv3x3_c64_prep(weight, False)`` shared by the primal and the tangent call."""
+    return _Conv3x3C64.apply(x, weight, bias, wsplit)
+
+
+def conv3x3_c64_usable(x: Tensor, weight: Tensor) -> bool:
+    return (x.dim() == 4 and tuple(weight.shape) == (64, 64, 3, 3) and x.shape[1] == 64
+            and x.dtype == torch.float32 and kernels.conv3x3_c64_usable(x.shape[0], x.shape[2], x.shape[3]))

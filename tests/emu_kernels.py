@@ -94,5 +94,18 @@ def chol_logdet_bwd(L, G, g_logdet, g_l1, penalty):
     return out
 
 
+def conv3x3_c64_usable(N, H, W):
+    return N > 0 and (H * W) % 4 == 0 and 128 + ((W + 4) & ~3) + W + 1 <= 256
+
+
+def conv3x3_c64_prep(weight, transpose):
+    """stand-in for the pre-split weights: the (possibly transposed + flipped) fp32 weights"""
+    return (weight.flip(2, 3).transpose(0, 1) if transpose else weight).contiguous()
+
+
+def conv3x3_c64(x, wsplit, bias=None):
+    return torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
+
+
 ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_bwd",
-       "chol_logdet_fwd", "chol_logdet_bwd"]
+       "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64"]

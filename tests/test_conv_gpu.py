@@ -1,0 +1,101 @@
+"""tcgen05 conditioner convolution against an FP64 statement of the same op
+(`networks.py:35-94` of the reference: 3x3, 64 -> 64 channels, zero padding 1), through the C ABI.
+Tolerance: 2e-6 of the output scale (the north-star bar is 1e-4 relative; the kernel measures
+2-6e-7, cuDNN FP32's autotuned algorithms 4-7e-6 on these shapes)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from cmf_b200 import _lib, kernels as K, ops
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+SHAPES = [(1, 8, 8), (2, 8, 8), (3, 28, 28), (5, 14, 14), (1, 32, 32), (7, 6, 10), (4, 16, 16), (2, 2, 2),
+          (130, 14, 14), (1, 4, 60), (3, 1, 4)]
+
+
+def _rand(shape, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(DEV)
+
+
+def _rel(a, ref):
+    return ((a.double() - ref).abs().max() / ref.abs().max().clamp_min(1e-30)).item()
+
+
+@pytest.mark.parametrize("N,H,W", SHAPES)
+@pytest.mark.parametrize("bias", [True, False])
+def test_forward_and_data_gradient(N, H, W, bias):
+    x, w = _rand((N, 64, H, W), 1), _rand((64, 64, 3, 3), 2, 1 / 24)
+    b = _rand((64,), 3) if bias else None
+    y = K.conv3x3_c64(x, K.conv3x3_c64_prep(w, False), b)
+    ref = F.conv2d(x.double(), w.double(), None if b is None else b.double(), padding=1)
+    assert _rel(y, ref) < 2e-6
+    gy = _rand((N, 64, H, W), 4)
+    gx = K.conv3x3_c64(gy, K.conv3x3_c64_prep(w, True), None)
+    gref = F.conv_transpose2d(gy.double(), w.double(), padding=1)
+    assert _rel(gx, gref) < 2e-6
+
+
+def test_badly_scaled_channels():
+    """per-channel magnitudes spread over 1e6: the hi/lo split must stay exact"""
+    x, w = _rand((3, 64, 14, 14), 5), _rand((64, 64, 3, 3), 6, 1 / 24)
+    scale = torch.logspace(-3, 3, 64, device=DEV).view(1, 64, 1, 1)
+    x = x * scale
+    y = K.conv3x3_c64(x, K.conv3x3_c64_prep(w, False), None)
+    ref = F.conv2d(x.double(), w.double(), padding=1)
+    assert _rel(y, ref) < 1e-5
+
+
+def test_relu_inputs_accumulate_without_bias():
+    """all-positive products (post-ReLU inputs, positive weights) are the worst case for the
+    truncating tensor-core accumulator: one K = 576 accumulation drifts by ~1e-5; with the FP32
+    register drain every K = 96 the systematic part is ~2e-6 (cuDNN FP32: 2.5e-6 max, unbiased)"""
+    x, w = _rand((4, 64, 28, 28), 7).abs(), _rand((64, 64, 3, 3), 8, 1 / 24).abs()
+    y = K.conv3x3_c64(x, K.conv3x3_c64_prep(w, False), None)
+    ref = F.conv2d(x.double(), w.double(), padding=1)
+    rel = (y.double() - ref) / ref
+    assert rel.abs().max().item() < 1e-6 and abs(rel.mean().item()) < 3e-7
+
+
+def test_autograd_wrapper_matches_library_conv():
+    x, w, b = _rand((6, 64, 14, 14), 9), _rand((64, 64, 3, 3), 10, 1 / 24), _rand((64,), 11)
+    g = _rand((6, 64, 14, 14), 12)
+    outs = []
+    for fn in (lambda a, ww, bb: ops.conv3x3_c64(a, ww, bb),
+               lambda a, ww, bb: F.conv2d(a.double(), ww.double(), bb.double(), padding=1)):
+        a, ww, bb = (t.clone().requires_grad_(True) for t in (x, w, b))
+        y = fn(a, ww, bb)
+        y.backward(g.to(y.dtype))
+        outs.append((y, a.grad, ww.grad, bb.grad))
+    for got, ref in zip(*outs):
+        assert _rel(got, ref.double()) < 1e-5
+
+
+def test_shared_presplit_weights_and_tangent_batch():
+    """one prep serves the primal (with bias) and the bias-free tangent call"""
+    w, b = _rand((64, 64, 3, 3), 13, 1 / 24), _rand((64,), 14)
+    ws = K.conv3x3_c64_prep(w, False)
+    h, Hv = _rand((2, 64, 14, 14), 15), _rand((2 * 5, 64, 14, 14), 16)
+    y, Y = ops.conv3x3_c64(h, w, b, ws), ops.conv3x3_c64(Hv, w, None, ws)
+    assert _rel(y, F.conv2d(h.double(), w.double(), b.double(), padding=1)) < 1e-5
+    assert _rel(Y, F.conv2d(Hv.double(), w.double(), None, padding=1)) < 1e-5
+
+
+def test_unsupported_shapes_are_rejected():
+    assert not K.conv3x3_c64_usable(1, 7, 7)        # H*W % 4 != 0: TMA row stride not 16-byte aligned
+    assert not K.conv3x3_c64_usable(1, 64, 64)      # halo box wider than 256 pixels
+    assert K.conv3x3_c64_usable(3250, 28, 28)
+    x = _rand((1, 64, 7, 7), 17)
+    ws = K.conv3x3_c64_prep(_rand((64, 64, 3, 3), 18), False)
+    with pytest.raises(_lib.CmfB200Error):
+        K.conv3x3_c64(x, ws, None)
+    with pytest.raises(_lib.CmfB200Error):
+        K.conv3x3_c64(x.cpu(), ws, None)
+
+
+def test_empty_batch():
+    x = torch.empty(0, 64, 8, 8, device=DEV)
+    y = K.conv3x3_c64(x, K.conv3x3_c64_prep(_rand((64, 64, 3, 3), 19), False), None)
+    assert y.shape == x.shape
