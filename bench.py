@@ -55,7 +55,7 @@ def parse_args():
     ap.add_argument("--scope-a-batch", type=int, default=512)
     ap.add_argument("--cpu-sample", type=int, default=1, help="samples per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--only", default=None, choices=[None, "scope_a", "step"],
+    ap.add_argument("--only", default=None, choices=[None, "scope_a", "step", "profile"],
                     help="profiling aid: run only the kernels-only region / only the full step (no JSON contract)")
     return ap.parse_args()
 
@@ -305,6 +305,20 @@ def run_own_arm(args, cfg, schema):
 
     if args.only == "scope_a":
         print(json.dumps(scope_a(head, args.scope_a_batch, args.steps, args.warmup, dev)), flush=True)
+        return
+    if args.only == "profile":               # per-kernel CUDA time of ONE step (kineto); not a bench value
+        from torch.profiler import profile, ProfilerActivity
+        for _ in range(args.warmup):
+            step_resident()
+        barrier()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            step_resident()
+            barrier()
+        rows = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)
+        total = sum(e.device_time_total for e in rows)
+        print(f"one step: {total / 1e3:.1f} ms of kernel time, {sum(e.count for e in rows)} launches")
+        for e in rows[:40]:
+            print(f"{100 * e.device_time_total / total:6.2f}% {e.count:6d} {e.device_time_total / 1e3:9.2f} ms  {e.key[:110]}")
         return
     if args.only == "step":
         ms, launches = timed(step_resident, args.steps, args.warmup)

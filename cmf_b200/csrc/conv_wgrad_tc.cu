@@ -1,0 +1,352 @@
+// Weight gradient of the 3x3 / 64 -> 64 / pad 1 conditioner convolution on tcgen05 (3xTF32).
+//
+//     g_w[co, ci, tap] = sum_{n, p} g_y[n, co, p] * x[n, ci, p + dy*W + dx]        (p = flat pixel)
+//
+// The contraction runs over pixels, so pixels are the K dimension:
+//   A (tensor memory, M = 128 rows) = TWO taps x 64 input channels of shifted x: row (a, ci) holds
+//       x[ci, p + shift(2j+a)] for the 32 pixels of a sub-chunk.  Row workers (one thread per row)
+//       read their 32 consecutive pixels from the halo tile TMA left in shared memory, zero the
+//       pixels whose tap leaves the image row, split (round-to-nearest TF32 head + exact
+//       remainder) and write both with tcgen05.st -- the same staging scheme as the forward kernel.
+//   B (shared memory, N = 64 rows)  = g_y[co, p], K-major exactly as NCHW stores it: TMA drops
+//       [64 co] x [32 px] boxes in the 128-byte swizzle; two splitter warps rewrite each box in
+//       place into its TF32 head and write the remainder to a twin buffer (same swizzled
+//       offsets, so no address arithmetic).
+//   D (tensor memory) = 5 accumulators of 128 x 64: tap pair j -> g_w[:, :, 2j], g_w[:, :, 2j+1]
+//       (the 10th "tap" is a zero row block).
+// A CTA walks T consecutive 128-pixel tiles (default 14 = two 28x28 images) with all five
+// accumulators resident in TMEM, then writes its partial g_w; a second kernel sums the partials
+// in a fixed order with FP32 round-to-nearest adds (deterministic).  T bounds the length of the
+// truncating tensor-core accumulation: <= 672 MMAs per accumulator, a worst-case same-sign bias
+// of ~3e-5 -- adequate for a gradient that goes straight to the optimiser (nothing downstream
+// amplifies it, unlike the forward values that pass through G^-1).
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace cmf {
+using namespace tc;
+
+namespace {
+
+constexpr int kC = 64;
+constexpr int kTaps = 9;
+constexpr int kPairs = 5;               // tap pairs (the last pair is tap 8 + a zero block)
+constexpr int kTileM = 128;             // pixels per tile
+constexpr int kSub = 4;                 // sub-chunks of 32 pixels (= K per staging)
+constexpr int kStagings = kSub * kPairs;          // 20 per tile
+constexpr int kStgBufs = 3;
+constexpr int kBBytes = kC * 32 * 4;    // one [64 co][32 px] box: 8 KB
+constexpr int kWgThreads = 32 * 12;     // TMA, MMA, 8 row workers, 2 splitters
+constexpr int kAccCols = kPairs * kC;   // 320
+constexpr int kWgTmemCols = 512;
+
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float4 lds_v4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float tf32_head_rn(float v) {
+    return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xFFFFE000u);
+}
+
+struct WgradParams {
+    int N, H, W, HW;
+    int tiles_per_image;
+    long long total_tiles;
+    int tiles_per_cta;
+    int hl;
+    float* partial;                     // [grid][9][64 ci][64 co]
+};
+
+template <int kPitch>
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmg, WgradParams P) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ uint64_t x_full[2], g_full[2], tile_done[2];
+    __shared__ uint64_t b_ready[kSub], qdone[kSub];
+    __shared__ uint64_t st_full[kStgBufs], st_done[kStgBufs];
+    __shared__ uint32_t tmem_base_smem;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    constexpr int kXBytes = kC * kPitch * 4;
+    uint8_t* gyhi = smem;                                   // [2 tiles][4 sub-chunks][8 KB], swizzled boxes
+    uint8_t* gylo = smem + 2 * kSub * kBBytes;              // [4][8 KB]
+    uint8_t* xh = gylo + kSub * kBBytes;                    // [2][64 ci][kPitch px]
+
+    const long long tile_begin = (long long)blockIdx.x * P.tiles_per_cta;
+    const int nt = (int)min((long long)P.tiles_per_cta, P.total_tiles - tile_begin);
+
+    if (threadIdx.x == 0) {
+        for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 1); mbar_init(&g_full[b], 1); mbar_init(&tile_done[b], 1); }
+        for (int q = 0; q < kSub; ++q) { mbar_init(&b_ready[q], 2); mbar_init(&qdone[q], 1); }
+        for (int b = 0; b < kStgBufs; ++b) { mbar_init(&st_full[b], 4); mbar_init(&st_done[b], 1); }
+        mbar_fence_init();
+        prefetch_tmap(&tmx);
+        prefetch_tmap(&tmg);
+    }
+    if (warp == 1) tmem_alloc<kWgTmemCols>(&tmem_base_smem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+    constexpr uint32_t kStgCol = kAccCols;                  // staging (buffer b) at columns 320 + 64 b: hi | lo
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            for (int i = 0; i < nt; ++i) {
+                const int buf = i & 1;
+                const long long T = tile_begin + i;
+                const int img = (int)(T / P.tiles_per_image), p0 = (int)(T % P.tiles_per_image) * kTileM;
+                if (i >= 2) mbar_wait(&tile_done[buf], ((i >> 1) - 1) & 1);
+                mbar_arrive_expect_tx(&x_full[buf], (uint32_t)kXBytes);
+                tma_load_2d(xh + (size_t)buf * kXBytes, &tmx, &x_full[buf], p0 - P.hl, img * kC);
+                mbar_arrive_expect_tx(&g_full[buf], (uint32_t)(kSub * kBBytes));
+                for (int q = 0; q < kSub; ++q)
+                    tma_load_2d(gyhi + (size_t)(buf * kSub + q) * kBBytes, &tmg, &g_full[buf], p0 + 32 * q, img * kC);
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
+        const uint32_t gyhi_addr = smem_u32(gyhi), gylo_addr = smem_u32(gylo);
+        int ns = 0;                                          // global staging counter
+        for (int i = 0; i < nt; ++i) {
+            const int buf = i & 1;
+            for (int n = 0; n < kStagings; ++n, ++ns) {
+                const int q = n / kPairs, j = n - q * kPairs;
+                const int sb = ns % kStgBufs;
+                if (j == 0) mbar_wait(&b_ready[q], i & 1);
+                mbar_wait(&st_full[sb], (ns / kStgBufs) & 1);
+                tc_fence_after();
+                if (elect_one()) {
+                    const uint32_t acc = tmem_base + (uint32_t)(j * kC);
+                    const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)(sb * 64), a_lo = a_hi + 32;
+                    const uint64_t dbh = umma_desc_sw128(gyhi_addr + (uint32_t)((buf * kSub + q) * kBBytes));
+                    const uint64_t dbl = umma_desc_sw128(gylo_addr + (uint32_t)(q * kBBytes));
+                    const uint32_t first = (i == 0 && q == 0) ? 0u : 1u;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, first | (uint32_t)(k != 0));
+                        umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
+                    umma_commit(&st_done[sb]);
+                    if (j == kPairs - 1) umma_commit(&qdone[q]);
+                    if (n == kStagings - 1) umma_commit(&tile_done[buf]);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (warp >= 10) {
+        // ------------------------------------------------------------------ g_y splitters (64 threads)
+        const int tid = threadIdx.x - 320;
+        const uint32_t gyhi_addr = smem_u32(gyhi), gylo_addr = smem_u32(gylo);
+        for (int i = 0; i < nt; ++i) {
+            const int buf = i & 1;
+            mbar_wait(&g_full[buf], (i >> 1) & 1);
+            for (int q = 0; q < kSub; ++q) {
+                if (i >= 1) mbar_wait(&qdone[q], (i - 1) & 1);      // remainder buffer q free again
+                const uint32_t src = gyhi_addr + (uint32_t)((buf * kSub + q) * kBBytes), dst = gylo_addr + (uint32_t)(q * kBBytes);
+#pragma unroll
+                for (int it = 0; it < kBBytes / 16 / 64; ++it) {
+                    const uint32_t off = (uint32_t)((tid + 64 * it) * 16);
+                    const float4 v = lds_v4(src + off);
+                    float4 h, l;
+                    h.x = tf32_head_rn(v.x); h.y = tf32_head_rn(v.y); h.z = tf32_head_rn(v.z); h.w = tf32_head_rn(v.w);
+                    l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;
+                    sts_v4(src + off, h);
+                    sts_v4(dst + off, l);
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&b_ready[q]);
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ row workers (x operand)
+        const int g = (warp - 2) >> 2;                    // this group stages n with n % 2 == g
+        const int rb = warp & 3;
+        const int m = rb * 32 + lane;
+        const int a = m >> 6, ci = m & 63;
+        const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
+        const uint32_t xh_addr = smem_u32(xh) + (uint32_t)((ci * kPitch + P.hl) * 4);
+        int ns = g;
+        for (int i = 0; i < nt; ++i) {
+            const int buf = i & 1;
+            const long long T = tile_begin + i;
+            const int p0 = (int)(T % P.tiles_per_image) * kTileM;
+            // bit k of ml[q] / mr[q]: pixel p0 + 32 q + k may use a tap with dx = -1 / +1
+            uint32_t ml[kSub], mr[kSub];
+#pragma unroll
+            for (int q = 0; q < kSub; ++q) {
+                const int xx = (p0 + 32 * q + lane) % P.W;
+                ml[q] = __ballot_sync(0xffffffffu, xx > 0);
+                mr[q] = __ballot_sync(0xffffffffu, xx + 1 < P.W);
+            }
+            mbar_wait(&x_full[buf], (i >> 1) & 1);
+            for (int n = g; n < kStagings; n += 2, ns += 2) {
+                const int q = n / kPairs, j = n - q * kPairs;
+                const int tap = 2 * j + a;
+                const int sb = ns % kStgBufs;
+                float hi[32], lo[32];
+                if (tap < kTaps) {
+                    const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
+                    const uint32_t src = xh_addr + (uint32_t)((buf * kC * kPitch + 32 * q + dy * P.W + dx) * 4);
+                    const uint32_t mb = dx < 0 ? ml[q] : (dx > 0 ? mr[q] : 0xffffffffu);
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) {
+                        const uint32_t keep = (uint32_t)((int32_t)(mb << (31 - k)) >> 31);     // all ones / zero
+                        const float v = __uint_as_float(__float_as_uint(lds_f32(src + 4 * k)) & keep);
+                        hi[k] = tf32_head_rn(v);
+                        lo[k] = v - hi[k];
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) { hi[k] = 0.f; lo[k] = 0.f; }
+                }
+                if (ns >= kStgBufs) mbar_wait(&st_done[sb], ((ns / kStgBufs) - 1) & 1);
+                tc_fence_after();
+                const uint32_t stg = tmem_base + kStgCol + (uint32_t)(sb * 64) + lane_addr;
+                tmem_st_32x32(stg, hi);
+                tmem_st_32x32(stg + 32, lo);
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&st_full[sb]);
+            }
+        }
+        // ------------------------------------------------------------------ epilogue: partial g_w
+        if (nt > 0) {
+            const int last = nt - 1;
+            mbar_wait(&tile_done[last & 1], (last >> 1) & 1);
+            tc_fence_after();
+            float* out = P.partial + (size_t)blockIdx.x * (kTaps * kC * kC);
+            for (int j = (g == 0 ? 0 : 3); j < (g == 0 ? 3 : kPairs); ++j) {
+                const int tap = 2 * j + a;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v[32];
+                    tmem_ld_32x32(tmem_base + lane_addr + (uint32_t)(j * kC + 32 * h), v);
+                    if (tap < kTaps) {
+                        float4* dst = reinterpret_cast<float4*>(out + ((size_t)tap * kC + ci) * kC + 32 * h);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) dst[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kWgTmemCols>(tmem_base);
+    }
+}
+
+// g_w[co, ci, tap] (+)= sum_c partial[c, tap, ci, co], fixed order, four independent FP32 chains
+__global__ void conv_wgrad_reduce_kernel(const float* __restrict__ partial, int nparts, int accumulate, float* __restrict__ gw) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;          // = (tap * 64 + ci) * 64 + co
+    if (i >= kTaps * kC * kC) return;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    const size_t stride = (size_t)kTaps * kC * kC;
+    int c = 0;
+    for (; c + 4 <= nparts; c += 4) {
+        s0 += __ldg(partial + (size_t)c * stride + i);
+        s1 += __ldg(partial + (size_t)(c + 1) * stride + i);
+        s2 += __ldg(partial + (size_t)(c + 2) * stride + i);
+        s3 += __ldg(partial + (size_t)(c + 3) * stride + i);
+    }
+    for (; c < nparts; ++c) s0 += __ldg(partial + (size_t)c * stride + i);
+    const float s = (s0 + s1) + (s2 + s3);
+    const int co = i % kC, ci = (i / kC) % kC, tap = i / (kC * kC);
+    float* dst = gw + ((size_t)co * kC + ci) * kTaps + tap;
+    *dst = accumulate ? *dst + s : s;
+}
+
+int wgrad_plan(int N, int H, int W, int* tiles_per_cta, long long* grid) {
+    const long long HW = (long long)H * W;
+    const long long tpi = ceil_div(HW, kTileM), total = (long long)N * tpi;
+    long long T = 14;                                   // two 28x28 images: <= 672 truncating MMAs per accumulator
+    if (ceil_div(total, T) < 148) T = ceil_div(total, 148);
+    if (T < 1) T = 1;
+    *tiles_per_cta = (int)T;
+    *grid = ceil_div(total, T);
+    return 0;
+}
+
+}  // namespace
+
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_conv3x3_c64_wgrad_usable(int N, int H, int W) {
+    if (N <= 0 || H <= 0 || W <= 0) return 0;
+    const long long HW = (long long)H * W;
+    const int need = kTileM + ((W + 4) & ~3) + (W + 1);
+    return (HW % 4 == 0) && need <= 228 && (long long)N * kC < (1LL << 31) && HW < (1LL << 24);
+}
+
+extern "C" size_t cmf_conv3x3_c64_wgrad_workspace(int N, int H, int W) {
+    if (N <= 0 || H <= 0 || W <= 0) return 0;
+    int T; long long grid;
+    wgrad_plan(N, H, W, &T, &grid);
+    return (size_t)grid * kTaps * kC * kC * sizeof(float);
+}
+
+extern "C" int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const float* g_y, float* workspace,
+                                     int accumulate, float* g_w, cmf_stream_t stream) {
+    CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3_wgrad: negative size");
+    CMF_REQUIRE(g_w, "conv3x3_wgrad: null g_w");
+    if (N == 0 || H == 0 || W == 0) {
+        if (!accumulate) {
+            cudaError_t e = cudaMemsetAsync(g_w, 0, sizeof(float) * kTaps * kC * kC, (cudaStream_t)stream);
+            if (e != cudaSuccess) { set_error("conv3x3_wgrad memset: %s", cudaGetErrorString(e)); return (int)e; }
+        }
+        return 0;
+    }
+    CMF_REQUIRE(x && g_y && workspace, "conv3x3_wgrad: null pointer");
+    CMF_REQUIRE(cmf_conv3x3_c64_wgrad_usable(N, H, W), "conv3x3_wgrad: unsupported image size %dx%d (need H*W %% 4 == 0, W <= 47)", H, W);
+    CMF_REQUIRE(aligned16(x) && aligned16(g_y) && aligned16(workspace), "conv3x3_wgrad: x, g_y and workspace must be 16-byte aligned");
+    WgradParams P{};
+    P.N = N; P.H = H; P.W = W; P.HW = H * W;
+    P.tiles_per_image = (int)ceil_div(P.HW, kTileM);
+    P.total_tiles = (long long)N * P.tiles_per_image;
+    long long grid;
+    wgrad_plan(N, H, W, &P.tiles_per_cta, &grid);
+    P.hl = (W + 4) & ~3;
+    P.partial = workspace;
+    const int pitch = (kTileM + P.hl + W + 1 <= 196) ? 196 : 228;
+    CUtensorMap tmx, tmg;
+    int rc = make_tmap_2d_plain_f32(&tmx, x, (uint64_t)N * kC, (uint64_t)P.HW, (uint64_t)P.HW, (uint32_t)pitch, kC);
+    if (rc != 0) return rc;
+    rc = make_tmap_2d_f32(&tmg, g_y, (uint64_t)N * kC, (uint64_t)P.HW, (uint64_t)P.HW, kC, 0);
+    if (rc != 0) return rc;
+    const size_t smem = (size_t)3 * kSub * kBBytes + (size_t)2 * kC * pitch * 4 + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv3x3_wgrad_tc_kernel<196>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(conv3x3_wgrad_tc_kernel<228>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        if (e != cudaSuccess) { set_error("conv3x3_wgrad attr: %s", cudaGetErrorString(e)); return (int)e; }
+        attr_set = true;
+    }
+    if (pitch == 196) conv3x3_wgrad_tc_kernel<196><<<(unsigned)grid, kWgThreads, smem, (cudaStream_t)stream>>>(tmx, tmg, P);
+    else conv3x3_wgrad_tc_kernel<228><<<(unsigned)grid, kWgThreads, smem, (cudaStream_t)stream>>>(tmx, tmg, P);
+    CMF_CHECK_LAUNCH();
+    conv_wgrad_reduce_kernel<<<(kTaps * kC * kC + 255) / 256, 256, 0, (cudaStream_t)stream>>>(workspace, (int)grid, accumulate, g_w);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}

@@ -239,3 +239,22 @@ def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None) -> Ten
         _lib.check(lib.cmf_conv3x3_c64_fwd(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(y), _stream()),
                    "cmf_conv3x3_c64_fwd")
     return y
+
+
+def conv3x3_c64_wgrad_usable(N: int, H: int, W: int) -> bool:
+    return bool(_lib.load().cmf_conv3x3_c64_wgrad_usable(int(N), int(H), int(W)))
+
+
+def conv3x3_c64_wgrad(x: Tensor, g_y: Tensor) -> Tensor:
+    """x, g_y (N,64,H,W) -> g_w (64,64,3,3) = weight gradient of ``conv2d(x, w, padding=1)``."""
+    lib = _lib.load()
+    x, g_y = _req(x, "x"), _req(g_y, "g_y")
+    N, C, H, W = x.shape
+    assert C == 64 and g_y.shape == x.shape
+    g_w = torch.empty(64, 64, 3, 3, dtype=torch.float32, device=x.device)
+    nbytes = lib.cmf_conv3x3_c64_wgrad_workspace(N, H, W)
+    ws = torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_conv3x3_c64_wgrad(N, H, W, _ptr(x), _ptr(g_y), _ptr(ws), 0, _ptr(g_w), _stream()),
+                   "cmf_conv3x3_c64_wgrad")
+    return g_w

@@ -195,9 +195,9 @@ def rqs_coupling_jvp(z_m: Tensor, V_m: Optional[Tensor], cw: Tensor, ch: Tensor,
 
 
 class _Conv3x3C64(Function):
-    """3x3 / 64 -> 64 / pad 1 convolution on the tcgen05 kernel.  The data gradient is the same
-    kernel on the transposed, flipped weights; the weight gradient stays a library call
-    (``aten::convolution_backward``) until the tcgen05 wgrad lands."""
+    """3x3 / 64 -> 64 / pad 1 convolution on the tcgen05 kernels.  The data gradient is the forward
+    kernel on the transposed, flipped weights; the weight gradient is the pixels-as-K kernel
+    (library ``aten::convolution_backward`` only for image widths it does not cover)."""
 
     @staticmethod
     def forward(ctx, x, weight, bias, wsplit):
@@ -214,7 +214,9 @@ class _Conv3x3C64(Function):
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         g_x = kernels.conv3x3_c64(g_y, kernels.conv3x3_c64_prep(weight, True), None) if need_x else None
         g_w = None
-        if need_w:
+        if need_w and kernels.conv3x3_c64_wgrad_usable(x.shape[0], x.shape[2], x.shape[3]):
+            g_w = kernels.conv3x3_c64_wgrad(x, g_y)
+        elif need_w:
             g_w = torch.ops.aten.convolution_backward(g_y, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
                                                       (False, True, False))[1]
         g_b = g_y.sum(dim=(0, 2, 3)) if (ctx.has_bias and ctx.needs_input_grad[2]) else None

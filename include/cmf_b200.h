@@ -132,6 +132,16 @@ int cmf_conv3x3_c64_prep(const float* w, int transpose, float* wsplit, cmf_strea
 int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                         float* y, cmf_stream_t stream);
 
+/* Weight gradient of the same convolution: g_w (64,64,3,3) (+)= sum_{n,p} g_y[n,co,p] x[n,ci,p+tap]
+ * (what autograd derives for F.conv2d at cmf/trainer.py:216, aten::convolution_backward).
+ * tcgen05 3xTF32 with pixels as the K dimension; CTAs write partial sums into `workspace`
+ * (cmf_conv3x3_c64_wgrad_workspace bytes, 16-byte aligned) and a second kernel adds them in a fixed
+ * order (deterministic).  Needs H*W % 4 == 0 and W <= 47 (cmf_conv3x3_c64_wgrad_usable). */
+int cmf_conv3x3_c64_wgrad_usable(int N, int H, int W);
+size_t cmf_conv3x3_c64_wgrad_workspace(int N, int H, int W);
+int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const float* g_y, float* workspace,
+                          int accumulate, float* g_w, cmf_stream_t stream);
+
 /* Rational-quadratic spline coupling, inverse direction (z -> x), primal + d tangent columns.
  * Arithmetic of gitmodules/nsf/nde/transforms/splines/rational_quadratic.py:13-52,96-112 (linear
  * tails: identity outside [-tail_bound, tail_bound]) and the bin search of

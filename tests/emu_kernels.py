@@ -107,5 +107,16 @@ def conv3x3_c64(x, wsplit, bias=None):
     return torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
 
 
+def conv3x3_c64_wgrad_usable(N, H, W):
+    return N > 0 and (H * W) % 4 == 0 and 128 + ((W + 4) & ~3) + W + 1 <= 228
+
+
+def conv3x3_c64_wgrad(x, g_y):
+    w = torch.zeros(64, 64, 3, 3, dtype=x.dtype, device=x.device)
+    return torch.ops.aten.convolution_backward(g_y, x, w, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                               (False, True, False))[1]
+
+
 ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_bwd",
-       "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64"]
+       "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64",
+       "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

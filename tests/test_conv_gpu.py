@@ -38,6 +38,34 @@ def test_forward_and_data_gradient(N, H, W, bias):
     assert _rel(gx, gref) < 2e-6
 
 
+def _wgrad_ref(x, gy):
+    w = torch.zeros(64, 64, 3, 3, device=DEV, dtype=torch.float64)
+    return torch.ops.aten.convolution_backward(gy.double(), x.double(), w, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                               (False, True, False))[1]
+
+
+@pytest.mark.parametrize("N,H,W", SHAPES + [(40, 28, 28), (300, 14, 14)])
+def test_weight_gradient(N, H, W):
+    """pixels-as-K tcgen05 kernel + fixed-order partial reduction vs FP64; several CTAs and tiles
+    per CTA in the larger cases"""
+    x, gy = _rand((N, 64, H, W), 20), _rand((N, 64, H, W), 21)
+    if not K.conv3x3_c64_wgrad_usable(N, H, W):                # wider than the halo box: rejected, not approximated
+        with pytest.raises(_lib.CmfB200Error):
+            K.conv3x3_c64_wgrad(x, gy)
+        return
+    gw = K.conv3x3_c64_wgrad(x, gy)
+    assert _rel(gw, _wgrad_ref(x, gy)) < 5e-6
+    assert torch.equal(gw, K.conv3x3_c64_wgrad(x, gy))          # deterministic
+
+
+def test_weight_gradient_same_sign_terms():
+    """all-positive terms: the longest truncating accumulation (T = 14 tiles per CTA)"""
+    x, gy = _rand((64, 64, 28, 28), 22).abs(), _rand((64, 64, 28, 28), 23).abs()
+    gw = K.conv3x3_c64_wgrad(x, gy)
+    ref = _wgrad_ref(x, gy)
+    assert ((gw.double() - ref) / ref).abs().max().item() < 5e-5
+
+
 def test_badly_scaled_channels():
     """per-channel magnitudes spread over 1e6: the hi/lo split must stay exact"""
     x, w = _rand((3, 64, 14, 14), 5), _rand((64, 64, 3, 3), 6, 1 / 24)
@@ -86,6 +114,7 @@ def test_shared_presplit_weights_and_tangent_batch():
 def test_unsupported_shapes_are_rejected():
     assert not K.conv3x3_c64_usable(1, 7, 7)        # H*W % 4 != 0: TMA row stride not 16-byte aligned
     assert not K.conv3x3_c64_usable(1, 64, 64)      # halo box wider than 256 pixels
+    assert K.conv3x3_c64_wgrad_usable(8, 32, 32) and not K.conv3x3_c64_wgrad_usable(8, 48, 48)
     assert K.conv3x3_c64_usable(3250, 28, 28)
     x = _rand((1, 64, 7, 7), 17)
     ws = K.conv3x3_c64_prep(_rand((64, 64, 3, 3), 18), False)
