@@ -66,7 +66,14 @@ struct ConvParams {
     long long total_tiles;
     int hl;                            // halo pixels in front of the tile: W+1 rounded up to 4 (TMA needs 16-byte box starts)
     const float* bias;                 // (64) or null
+    // fused epilogue:  t = acc + bias;  if (mask_first) t *= m;  if (res) t += res;  y = t;
+    //                  if (y2) y2 = t * m      with m = mask_src[n / mask_div, co, p] > 0
+    const float* mask_src;             // (N / mask_div, 64, H, W) pre-ReLU primal activations, or null
+    int mask_div;
+    int mask_first;
+    const float* res;                  // (N, 64, H, W) or null
     float* y;
+    float* y2;                         // (N, 64, H, W) or null
 };
 
 // weight prep: w (co, ci, 3, 3) -> out[part][tap][row][col] with part 0 = TF32 head, 1 = remainder.
@@ -276,9 +283,39 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                 if (s == kStages - 1) drain(s);
             }
             if (p < P.HW) {
-                float* yo = P.y + (long long)img[t] * kC * P.HW + p;
+                const long long o = (long long)img[t] * kC * P.HW + p;
+                if (!P.mask_src && !P.res) {
 #pragma unroll
-                for (int j = 0; j < kC; ++j) yo[(long long)j * P.HW] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                    for (int j = 0; j < kC; ++j) P.y[o + (long long)j * P.HW] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                } else {
+                    const float* ms = P.mask_src ? P.mask_src + (long long)(img[t] / P.mask_div) * kC * P.HW + p : nullptr;
+                    const float* rs = P.res ? P.res + o : nullptr;
+                    float* y1 = P.y + o;
+                    float* y2 = P.y2 ? P.y2 + o : nullptr;
+                    const bool mask_first = P.mask_first != 0;
+                    const long long hw = P.HW;
+                    // batches of 8 channels: all loads of a batch are issued before its stores, so their
+                    // latencies overlap (the compiler cannot hoist loads over possibly aliasing stores)
+#pragma unroll
+                    for (int jb = 0; jb < kC; jb += 8) {
+                        float mv[8], rv[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            mv[e] = ms ? __ldg(ms + (jb + e) * hw) : 1.f;
+                            rv[e] = rs ? __ldg(rs + (jb + e) * hw) : 0.f;
+                        }
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const int j = jb + e;
+                            float v = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                            const bool keep = mv[e] > 0.f;
+                            if (mask_first && !keep) v = 0.f;
+                            v += rv[e];
+                            y1[j * hw] = v;
+                            if (y2) y2[j * hw] = keep ? v : 0.f;
+                        }
+                    }
+                }
             }
             if (warp == 2) PROF(30);
         }
@@ -312,8 +349,9 @@ extern "C" int cmf_conv3x3_c64_usable(int N, int H, int W) {
     return (HW % 4 == 0) && need <= kMaxBox && (long long)N * kC < (1LL << 31) && HW < (1LL << 24);
 }
 
-extern "C" int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
-                                   float* y, cmf_stream_t stream) {
+extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                                     const float* mask_src, int mask_div, int mask_first, const float* res,
+                                     float* y, float* y2, cmf_stream_t stream) {
     CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3: negative size");
     if (N == 0 || H == 0 || W == 0) return 0;
     CMF_REQUIRE(x && wsplit && y, "conv3x3: null pointer");
@@ -324,7 +362,10 @@ extern "C" int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const fl
     P.tiles_per_image = (int)ceil_div(P.HW, kTileM);
     P.total_tiles = (long long)N * P.tiles_per_image;
     P.hl = (W + 4) & ~3;
-    P.bias = bias; P.y = y;
+    CMF_REQUIRE(!mask_src || (mask_div >= 1 && N % mask_div == 0), "conv3x3: mask_div must divide N");
+    CMF_REQUIRE(!y2 || mask_src, "conv3x3: second output needs a mask source");
+    P.bias = bias; P.y = y; P.y2 = y2;
+    P.mask_src = mask_src; P.mask_div = mask_src ? mask_div : 1; P.mask_first = mask_first; P.res = res;
     const int pitch = (kTileM + P.hl + W + 1 <= 192) ? 192 : 256;
     CUtensorMap tmx, tmw;
     int rc = make_tmap_2d_plain_f32(&tmx, x, (uint64_t)N * kC, (uint64_t)P.HW, (uint64_t)P.HW, (uint32_t)pitch, kChunkC);
@@ -352,3 +393,8 @@ extern "C" int cmf_debug_conv_prof(long long* host_out) {
     return (int)cudaMemcpyFromSymbol(host_out, g_conv_prof, sizeof(long long) * 128);
 }
 #endif
+
+extern "C" int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                                   float* y, cmf_stream_t stream) {
+    return cmf_conv3x3_c64_fused(N, H, W, x, wsplit, bias, nullptr, 1, 0, nullptr, y, nullptr, stream);
+}

@@ -225,8 +225,11 @@ def conv3x3_c64_prep(weight: Tensor, transpose: bool) -> Tensor:
     return out
 
 
-def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None) -> Tensor:
-    """x (N,64,H,W), wsplit from ``conv3x3_c64_prep`` -> y (N,64,H,W)."""
+def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_src: Optional[Tensor] = None,
+                mask_div: int = 1, mask_first: bool = False, res: Optional[Tensor] = None, second: bool = False):
+    """x (N,64,H,W), wsplit from ``conv3x3_c64_prep`` -> y (N,64,H,W), with the fused epilogue of
+    ``cmf_conv3x3_c64_fused``:  t = conv(x) + bias; if mask_first: t *= m; if res: t += res; y = t;
+    ``second`` additionally returns y2 = t * m  (m = mask_src[n // mask_div] > 0)."""
     lib = _lib.load()
     x, wsplit = _req(x, "x"), _req(wsplit, "wsplit")
     N, C, H, W = x.shape
@@ -234,11 +237,20 @@ def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None) -> Ten
     if bias is not None:
         bias = _req(bias, "bias")
         assert bias.numel() == 64
+    if mask_src is not None:
+        mask_src = _req(mask_src, "mask_src")
+        assert N % mask_div == 0 and tuple(mask_src.shape) == (N // mask_div, 64, H, W), (mask_src.shape, x.shape, mask_div)
+    if res is not None:
+        res = _req(res, "res")
+        assert res.shape == x.shape
+    assert not second or mask_src is not None
     y = torch.empty_like(x)
+    y2 = torch.empty_like(x) if second else None
     with torch.cuda.device(x.device):
-        _lib.check(lib.cmf_conv3x3_c64_fwd(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(y), _stream()),
-                   "cmf_conv3x3_c64_fwd")
-    return y
+        _lib.check(lib.cmf_conv3x3_c64_fused(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src), int(mask_div),
+                                             int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2), _stream()),
+                   "cmf_conv3x3_c64_fused")
+    return (y, y2) if second else y
 
 
 def conv3x3_c64_wgrad_usable(N: int, H: int, W: int) -> bool:

@@ -99,6 +99,80 @@ class ResidualBlock(nn.Module):
         return h + x, Hv + V
 
 
+class _ResidualStackTangent(torch.autograd.Function):
+    """Tangent push through a run of residual blocks (`networks.py:62-79` applied per block) with
+    every elementwise neighbour of the convolutions folded into a convolution epilogue:
+
+        A0 = m0 * V;  A1 = m1 * conv1(A0);  S = conv2(A1) + V;  next A0 = m0' * S      (m = primal > 0)
+
+    forward : conv1 epilogue applies m1; conv2 epilogue adds the skip and also emits the masked copy
+              the next block consumes (two outputs, one pass).
+    backward: g_C1 = m1 * dgrad2(g) (epilogue mask), g = m0 * dgrad1(g_C1) + g (mask, then skip add);
+              weight gradients from the saved masked activations.
+    The masks come from the PRIMAL activations (not differentiated: the reference's relu JVP
+    `jvp_layers.py:38-46` is piecewise constant in them)."""
+
+    @staticmethod
+    def forward(ctx, V, d, *tensors):
+        from . import kernels
+        K = len(tensors) // 4
+        xs, h1s = tensors[0::4], tensors[1::4]
+        w1s, w2s = tensors[2::4], tensors[3::4]
+        S = V.contiguous()
+        A0 = _mask_rows(S, xs[0] > 0, d)
+        saved = []
+        for k in range(K):
+            A1 = kernels.conv3x3_c64(A0, kernels.conv3x3_c64_prep(w1s[k], False), None, mask_src=h1s[k], mask_div=d,
+                                     mask_first=True)
+            ws2 = kernels.conv3x3_c64_prep(w2s[k], False)
+            saved += [A0, A1]
+            if k + 1 < K:
+                S, A0 = kernels.conv3x3_c64(A1, ws2, None, mask_src=xs[k + 1], mask_div=d, res=S, second=True)
+            else:
+                S = kernels.conv3x3_c64(A1, ws2, None, res=S)
+        ctx.d, ctx.K = d, K
+        ctx.save_for_backward(*xs, *h1s, *w1s, *w2s, *saved)
+        return S
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import kernels
+        K, d = ctx.K, ctx.d
+        t = ctx.saved_tensors
+        xs, h1s, w1s, w2s, saved = t[:K], t[K:2 * K], t[2 * K:3 * K], t[3 * K:4 * K], t[4 * K:]
+        g = g.contiguous()
+        grads = [None] * (4 * K)
+        for k in reversed(range(K)):
+            A0, A1 = saved[2 * k], saved[2 * k + 1]
+            grads[4 * k + 3] = kernels.conv3x3_c64_wgrad(A1, g)
+            gC1 = kernels.conv3x3_c64(g, kernels.conv3x3_c64_prep(w2s[k], True), None, mask_src=h1s[k], mask_div=d,
+                                      mask_first=True)
+            grads[4 * k + 2] = kernels.conv3x3_c64_wgrad(A0, gC1)
+            g = kernels.conv3x3_c64(gC1, kernels.conv3x3_c64_prep(w1s[k], True), None, mask_src=xs[k], mask_div=d,
+                                    mask_first=True, res=g)
+        return (g, None, *grads)
+
+
+def _residual_stack_jvp(blocks, h: Tensor, Hv: Tensor, d: int):
+    """primal (autograd, per block) + tangents (one fused node) through consecutive residual blocks"""
+    from . import kernels
+    N, _, H, W = Hv.shape
+    fused = (_TC_CONV and all(b.conv1.weight.shape == (64, 64, 3, 3) for b in blocks) and Hv.shape[1] == 64
+             and kernels.conv3x3_c64_usable(N, H, W) and kernels.conv3x3_c64_wgrad_usable(N, H, W))
+    if not fused:
+        for b in blocks:
+            h, Hv = b.jvp_batched(h, Hv, d)
+        return h, Hv
+    args = []
+    for b in blocks:
+        x_in = h
+        h1, _ = _conv3x3_pair(b.conv1, torch.relu(x_in), None)
+        h2, _ = _conv3x3_pair(b.conv2, torch.relu(h1), None)
+        h = h2 + x_in
+        args += [x_in.detach(), h1.detach(), b.conv1.weight, b.conv2.weight]
+    return h, _ResidualStackTangent.apply(Hv, d, *args)
+
+
 def _mask_rows(V: Tensor, keep: Tensor, d: int) -> Tensor:
     """V (B*d, ...) * keep (B, ...) broadcast over the d tangents of each sample."""
     B = keep.shape[0]
@@ -151,10 +225,17 @@ class ScaledTanhResNet(nn.Module):
         B, d = V.shape[:2]
         Hv = V.reshape(B * d, *V.shape[2:])
         h = x
-        body = self.module if pos is None else self.module[:-2]
-        for mod in body:
+        body = list(self.module if pos is None else self.module[:-2])
+        i = 0
+        while i < len(body):
+            mod = body[i]
+            i += 1
             if isinstance(mod, ResidualBlock):
-                h, Hv = mod.jvp_batched(h, Hv, d)
+                run = [mod]
+                while i < len(body) and isinstance(body[i], ResidualBlock):
+                    run.append(body[i])
+                    i += 1
+                h, Hv = _residual_stack_jvp(run, h, Hv, d)
             elif isinstance(mod, nn.Conv2d):
                 Hv = F.conv2d(Hv, mod.weight, None, stride=mod.stride, padding=mod.padding)
                 h = mod(h)

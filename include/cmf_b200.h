@@ -131,6 +131,14 @@ int cmf_conv3x3_c64_usable(int N, int H, int W);
 int cmf_conv3x3_c64_prep(const float* w, int transpose, float* wsplit, cmf_stream_t stream);
 int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                         float* y, cmf_stream_t stream);
+/* Same convolution with the elementwise neighbours of the residual block fused into the epilogue
+ * (networks.py:62-79: relu JVP = mask by the primal's sign, skip connection):
+ *     t = conv(x) + bias;  if (mask_first) t *= m;  if (res) t += res;  y = t;  if (y2) y2 = t * m
+ * with m = (mask_src[n / mask_div, co, p] > 0), mask_src = pre-ReLU PRIMAL activations
+ * (N / mask_div, 64, H, W): mask_div = d tangent columns per sample.  mask_src, res, y2 may be NULL. */
+int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                          const float* mask_src, int mask_div, int mask_first, const float* res,
+                          float* y, float* y2, cmf_stream_t stream);
 
 /* Weight gradient of the same convolution: g_w (64,64,3,3) (+)= sum_{n,p} g_y[n,co,p] x[n,ci,p+tap]
  * (what autograd derives for F.conv2d at cmf/trainer.py:216, aten::convolution_backward).

@@ -103,8 +103,16 @@ def conv3x3_c64_prep(weight, transpose):
     return (weight.flip(2, 3).transpose(0, 1) if transpose else weight).contiguous()
 
 
-def conv3x3_c64(x, wsplit, bias=None):
-    return torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
+def conv3x3_c64(x, wsplit, bias=None, mask_src=None, mask_div=1, mask_first=False, res=None, second=False):
+    t = torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
+    m = None
+    if mask_src is not None:
+        m = (mask_src > 0).to(t.dtype).repeat_interleave(mask_div, dim=0)
+    if mask_first:
+        t = t * m
+    if res is not None:
+        t = t + res
+    return (t, t * m) if second else t
 
 
 def conv3x3_c64_wgrad_usable(N, H, W):

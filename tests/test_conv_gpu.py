@@ -111,6 +111,52 @@ def test_shared_presplit_weights_and_tangent_batch():
     assert _rel(Y, F.conv2d(Hv.double(), w.double(), None, padding=1)) < 1e-5
 
 
+@pytest.mark.parametrize("N,H,W,d", [(6, 14, 14, 3), (4, 28, 28, 2), (5, 8, 8, 1), (130, 14, 14, 65)])
+@pytest.mark.parametrize("mode", ["mask", "res_second", "mask_res", "res"])
+def test_fused_epilogue(N, H, W, d, mode):
+    """relu-JVP mask (sign of the primal, one primal image per d tangent images) and skip
+    connection folded into the epilogue, against the same composition in FP64"""
+    import emu_kernels as E
+    x, w = _rand((N, 64, H, W), 30), _rand((64, 64, 3, 3), 31, 1 / 24)
+    prim, res = _rand((N // d, 64, H, W), 32), _rand((N, 64, H, W), 33)
+    kw = {"mask": dict(mask_src=prim, mask_div=d, mask_first=True),
+          "res_second": dict(mask_src=prim, mask_div=d, res=res, second=True),
+          "mask_res": dict(mask_src=prim, mask_div=d, mask_first=True, res=res),
+          "res": dict(res=res)}[mode]
+    got = K.conv3x3_c64(x, K.conv3x3_c64_prep(w, False), None, **kw)
+    kw64 = {k: (v.double() if torch.is_tensor(v) else v) for k, v in kw.items()}
+    ref = E.conv3x3_c64(x.double(), w.double(), None, **kw64)
+    got, ref = (got, ref) if isinstance(got, tuple) else ((got,), (ref,))
+    for g_, r_ in zip(got, ref):
+        assert _rel(g_, r_) < 2e-6
+        assert torch.equal(g_ == 0, r_ == 0) or mode == "res"      # masked entries are exact zeros
+
+
+def test_residual_stack_tangent_matches_autograd():
+    """the fused tangent node of a residual-block run vs the per-op autograd path (library convs)"""
+    from cmf_b200 import networks as NW
+    torch.backends.cudnn.allow_tf32 = False          # the library path must be FP32 to serve as the reference
+    torch.manual_seed(0)
+    blocks = [NW.ResidualBlock(64).to(DEV) for _ in range(3)]
+    B, d = 2, 3
+    h0, V0 = _rand((B, 64, 14, 14), 40), _rand((B * d, 64, 14, 14), 41)
+    gH, gV = _rand((B, 64, 14, 14), 42), _rand((B * d, 64, 14, 14), 43)
+    results = []
+    for fused in (True, False):
+        NW._TC_CONV = fused
+        try:
+            for b in blocks:
+                b.zero_grad()
+            h, V = h0.clone().requires_grad_(True), V0.clone().requires_grad_(True)
+            hh, VV = NW._residual_stack_jvp(blocks, h, V, d)
+            ((hh * gH).sum() + (VV * gV).sum()).backward()
+            results.append([hh.detach(), VV.detach(), h.grad, V.grad] + [p.grad.clone() for b in blocks for p in b.parameters()])
+        finally:
+            NW._TC_CONV = True
+    for a, b in zip(*results):
+        assert _rel(a, b.double()) < 2e-5
+
+
 def test_unsupported_shapes_are_rejected():
     assert not K.conv3x3_c64_usable(1, 7, 7)        # H*W % 4 != 0: TMA row stride not 16-byte aligned
     assert not K.conv3x3_c64_usable(1, 64, 64)      # halo box wider than 256 pixels
