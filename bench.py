@@ -160,6 +160,43 @@ def run_reference_arm(args, cfg, schema):
 
 
 # ------------------------------------------------------------------------------------------------
+# The dominant kernels of the step (tcgen05 conditioner convolutions), timed per launch
+# ------------------------------------------------------------------------------------------------
+def conv_kernel_times(step, dev):
+    """One extra (untimed-for-the-metric) step with CUDA events around every launch of the two
+    tcgen05 convolution kernels.  Returns per kernel: launches, total ms, algorithmic FLOPs
+    (2 * N * 64 * 64 * 9 * H * W per launch) and TFLOP/s."""
+    from cmf_b200 import kernels as K
+    rec = {"conv3x3_tc_kernel": [], "conv3x3_wgrad_tc_kernel": []}
+    orig_f, orig_w = K.conv3x3_c64, K.conv3x3_c64_wgrad
+
+    def wrap(name, fn):
+        def inner(x, *a, **kw):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = fn(x, *a, **kw)
+            e1.record()
+            N, _, H, W = x.shape
+            rec[name].append((e0, e1, 2.0 * N * 64 * 64 * 9 * H * W))
+            return out
+        return inner
+
+    K.conv3x3_c64, K.conv3x3_c64_wgrad = wrap("conv3x3_tc_kernel", orig_f), wrap("conv3x3_wgrad_tc_kernel", orig_w)
+    try:
+        step()
+        torch.cuda.synchronize()
+    finally:
+        K.conv3x3_c64, K.conv3x3_c64_wgrad = orig_f, orig_w
+    out = {}
+    for name, items in rec.items():
+        ms = sum(a.elapsed_time(b) for a, b, _ in items)
+        fl = sum(f for _, _, f in items)
+        out[name] = {"launches": len(items), "ms_per_step": ms, "algorithmic_flops_per_step": fl,
+                     "tflops": fl / (ms * 1e-3) / 1e12 if ms > 0 else 0.0}
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # Scope A: the hand-written kernels alone, against their algorithmic bytes
 # ------------------------------------------------------------------------------------------------
 def scope_a(head, B, steps, warmup, dev):
@@ -321,6 +358,16 @@ def run_own_arm(args, cfg, schema):
             print(f"{100 * e.device_time_total / total:6.2f}% {e.count:6d} {e.device_time_total / 1e3:9.2f} ms  {e.key[:110]}")
         return
     if args.only == "step":
+        if os.environ.get("CMF_NCU_RANGE"):      # ncu --profile-from-start off: capture the timed steps only
+            for _ in range(args.warmup):
+                step_resident()
+            barrier()
+            torch.cuda.profiler.start()
+            for _ in range(args.steps):
+                step_resident()
+            barrier()
+            torch.cuda.profiler.stop()
+            return
         ms, launches = timed(step_resident, args.steps, args.warmup)
         print(json.dumps({"ms_per_step": ms / args.steps, "gpu_launches": launches}), flush=True)
         return
@@ -332,8 +379,9 @@ def run_own_arm(args, cfg, schema):
     value = world * B * args.steps / (ms * 1e-3)
     e2e = world * B * args.steps / (ms_e2e * 1e-3)
 
-    sa = None
+    sa = conv = None
     if rank == 0:
+        conv = conv_kernel_times(step_resident, dev)
         sa = scope_a(head, args.scope_a_batch, max(args.steps, 5), 3, dev)
     clocks = sampler.stop() if rank == 0 else None
     peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
@@ -375,10 +423,22 @@ def run_own_arm(args, cfg, schema):
                         "bytes_per_sample": sa["bytes_per_sample"], "achieved_gbs": scope_gbs,
                         "frac_of_hbm": scope_gbs / peaks["hbm_gbs"], "class_ms_per_step": sa["class_ms"],
                         "launches_per_step": sa["launches_per_class"]},
-            "roofline": {"kernel": "coupling_bwd_{vec4,map} (10 launches/step)", "bound": "hbm",
-                         "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
-                         "algorithmic_bytes_per_step": cb_bytes},
+            # dominant kernel of the step: the tcgen05 conditioner convolution (forward + data gradient)
+            "roofline": {"kernel": f"conv3x3_tc_kernel ({conv['conv3x3_tc_kernel']['launches']} launches/step, "
+                                   f"{conv['conv3x3_tc_kernel']['ms_per_step']:.0f} ms of the step)",
+                         "bound": "tensor", "achieved": conv["conv3x3_tc_kernel"]["tflops"],
+                         "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
+                         "frac": conv["conv3x3_tc_kernel"]["tflops"] / peaks["bf16_tflops"],
+                         "traffic": None, "peak_source": peak_kind,
+                         "note": "FP32-accurate 3xTF32: kind::tf32 runs at half the bf16 rate and each product "
+                                 "takes 3 MMAs, so the ceiling of this arithmetic is 1/6 of the bf16 peak",
+                         "frac_of_3xtf32_ceiling": 6.0 * conv["conv3x3_tc_kernel"]["tflops"] / peaks["bf16_tflops"],
+                         "algorithmic_flops_per_step": conv["conv3x3_tc_kernel"]["algorithmic_flops_per_step"]},
+            "conv_kernels": conv,
+            "roofline_scope_a": {"kernel": "coupling_bwd_{vec4,map} (10 launches/step)", "bound": "hbm",
+                                 "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                 "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
+                                 "algorithmic_bytes_per_step": cb_bytes},
             "peak_mem_gib": peak_mem,
         }
         if cpu is not None:

@@ -16,7 +16,7 @@
 //       (the 10th "tap" is a zero row block).
 // A CTA walks T consecutive 128-pixel tiles (default 14 = two 28x28 images) with all five
 // accumulators resident in TMEM, then writes its partial g_w; a second kernel sums the partials
-// in a fixed order with FP32 round-to-nearest adds (deterministic).  T bounds the length of the
+// in a fixed order with FP32 round-to-nearest adds.  T bounds the length of the
 // truncating tensor-core accumulation: <= 672 MMAs per accumulator, a worst-case same-sign bias
 // of ~3e-5 -- adequate for a gradient that goes straight to the optimiser (nothing downstream
 // amplifies it, unlike the forward values that pass through G^-1).
@@ -36,7 +36,12 @@ constexpr int kSub = 4;                 // sub-chunks of 32 pixels (= K per stag
 constexpr int kStagings = kSub * kPairs;          // 20 per tile
 constexpr int kStgBufs = 3;
 constexpr int kBBytes = kC * 32 * 4;    // one [64 co][32 px] box: 8 KB
-constexpr int kWgThreads = 32 * 12;     // TMA, MMA, 8 row workers, 2 splitters
+constexpr int kWgThreads = 32 * 13;     // TMA, MMA 0, 8 row workers, 2 splitters, MMA 1
+constexpr int kMmaWarp1 = 12;
+#ifndef CMF_WG_ISSUERS
+#define CMF_WG_ISSUERS 2
+#endif
+constexpr int kIssuers = CMF_WG_ISSUERS;
 constexpr int kAccCols = kPairs * kC;   // 320
 constexpr int kWgTmemCols = 512;
 
@@ -73,6 +78,7 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
     __shared__ uint64_t x_full[2], g_full[2], tile_done[2];
     __shared__ uint64_t b_ready[kSub], qdone[kSub];
     __shared__ uint64_t st_full[kStgBufs], st_done[kStgBufs];
+    __shared__ uint64_t acc_init;
     __shared__ uint32_t tmem_base_smem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -86,9 +92,10 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
     const int nt = (int)min((long long)P.tiles_per_cta, P.total_tiles - tile_begin);
 
     if (threadIdx.x == 0) {
-        for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 1); mbar_init(&g_full[b], 1); mbar_init(&tile_done[b], 1); }
-        for (int q = 0; q < kSub; ++q) { mbar_init(&b_ready[q], 2); mbar_init(&qdone[q], 1); }
-        for (int b = 0; b < kStgBufs; ++b) { mbar_init(&st_full[b], 4); mbar_init(&st_done[b], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 1); mbar_init(&g_full[b], 1); mbar_init(&tile_done[b], kIssuers); }
+        for (int q = 0; q < kSub; ++q) { mbar_init(&b_ready[q], 2); mbar_init(&qdone[q], kIssuers); }
+        for (int b = 0; b < kStgBufs; ++b) { mbar_init(&st_full[b], 4); mbar_init(&st_done[b], kIssuers); }
+        mbar_init(&acc_init, 8);
         mbar_fence_init();
         prefetch_tmap(&tmx);
         prefetch_tmap(&tmg);
@@ -115,11 +122,20 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     tma_load_2d(gyhi + (size_t)(buf * kSub + q) * kBBytes, &tmg, &g_full[buf], p0 + 32 * q, img * kC);
             }
         }
-    } else if (warp == 1) {
-        // ------------------------------------------------------------------ MMA issuer
+    } else if (warp == 1 || (warp == kMmaWarp1 && kIssuers == 2)) {
+        // ------------------------------------------------------------------ MMA issuers
+        // A single thread's issue path costs ~50 cycles per tcgen05.mma (240 MMAs per tile would
+        // take 1.5x the tensor time), so TWO warps issue: both walk EVERY staging -- each sees every
+        // phase of st_full, which the parity waits require -- and issuer w takes the K-steps
+        // {2w, 2w+1} of it.  Both add into the same accumulator; the accumulators are zeroed by the
+        // row workers up front, so no MMA depends on being first.
+        const int w = warp == 1 ? 0 : 1;
         constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
+        constexpr int kPer = 4 / kIssuers;
         const uint32_t gyhi_addr = smem_u32(gyhi), gylo_addr = smem_u32(gylo);
-        int ns = 0;                                          // global staging counter
+        mbar_wait(&acc_init, 0);
+        tc_fence_after();
+        int ns = 0;
         for (int i = 0; i < nt; ++i) {
             const int buf = i & 1;
             for (int n = 0; n < kStagings; ++n, ++ns) {
@@ -133,14 +149,13 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)(sb * 64), a_lo = a_hi + 32;
                     const uint64_t dbh = umma_desc_sw128(gyhi_addr + (uint32_t)((buf * kSub + q) * kBBytes));
                     const uint64_t dbl = umma_desc_sw128(gylo_addr + (uint32_t)(q * kBBytes));
-                    const uint32_t first = (i == 0 && q == 0) ? 0u : 1u;
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, first | (uint32_t)(k != 0));
+                    for (int kk = 0; kk < kPer; ++kk) {
+                        const int k = w * kPer + kk;
+                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, 1);
                         umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                        umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
                     }
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
                     umma_commit(&st_done[sb]);
                     if (j == kPairs - 1) umma_commit(&qdone[q]);
                     if (n == kStagings - 1) umma_commit(&tile_done[buf]);
@@ -148,6 +163,8 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                 __syncwarp();
             }
         }
+    } else if (warp == kMmaWarp1) {
+        // second issuer slot unused (kIssuers == 1)
     } else if (warp >= 10) {
         // ------------------------------------------------------------------ g_y splitters (64 threads)
         const int tid = threadIdx.x - 320;
@@ -180,7 +197,18 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         const int m = rb * 32 + lane;
         const int a = m >> 6, ci = m & 63;
         const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
-        const uint32_t xh_addr = smem_u32(xh) + (uint32_t)((ci * kPitch + P.hl) * 4);
+        const uint32_t xrow_addr = smem_u32(xh) + (uint32_t)(ci * kPitch * 4);
+        {   // zero the five accumulators (group g: columns [160 g, 160 g + 160) of this warp's lane quarter)
+            float zero[32];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) zero[k] = 0.f;
+#pragma unroll
+            for (int c = 0; c < 5; ++c) tmem_st_32x32(tmem_base + lane_addr + (uint32_t)(g * 160 + c * 32), zero);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_init);
+        }
         int ns = g;
         for (int i = 0; i < nt; ++i) {
             const int buf = i & 1;
@@ -202,15 +230,34 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                 float hi[32], lo[32];
                 if (tap < kTaps) {
                     const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
-                    const uint32_t src = xh_addr + (uint32_t)((buf * kC * kPitch + 32 * q + dy * P.W + dx) * 4);
-                    const uint32_t mb = dx < 0 ? ml[q] : (dx > 0 ? mr[q] : 0xffffffffu);
+                    // 32 consecutive pixels of row ci starting at `base`.  Rows are kPitch floats
+                    // apart with kPitch/4 odd, so 128-bit loads are bank-conflict free across the 32
+                    // channel lanes (32-bit loads would be 4-way conflicted); the window is loaded
+                    // 16-byte aligned (9 vectors) and the misalignment base & 3 -- the same for every
+                    // lane -- is resolved by a 4-way static dispatch.
+                    const int base = P.hl + 32 * q + dy * P.W + dx;
+                    const int off = base & 3;
+                    const uint32_t src = xrow_addr + (uint32_t)((buf * kC * kPitch + (base - off)) * 4);
+                    float wv[36];
 #pragma unroll
-                    for (int k = 0; k < 32; ++k) {
-                        const uint32_t keep = (uint32_t)((int32_t)(mb << (31 - k)) >> 31);     // all ones / zero
-                        const float v = __uint_as_float(__float_as_uint(lds_f32(src + 4 * k)) & keep);
-                        hi[k] = tf32_head_rn(v);
-                        lo[k] = v - hi[k];
+                    for (int e = 0; e < 9; ++e) {
+                        const float4 t4 = lds_v4(src + 16 * e);
+                        wv[4 * e] = t4.x; wv[4 * e + 1] = t4.y; wv[4 * e + 2] = t4.z; wv[4 * e + 3] = t4.w;
                     }
+                    uint32_t mlq = ml[0], mrq = mr[0];
+#pragma unroll
+                    for (int qq = 1; qq < kSub; ++qq) { if (q == qq) { mlq = ml[qq]; mrq = mr[qq]; } }
+                    const uint32_t mb = dx < 0 ? mlq : (dx > 0 ? mrq : 0xffffffffu);
+#define CMF_WG_SPLIT(OFF)                                                                         \
+    _Pragma("unroll") for (int k = 0; k < 32; ++k) {                                              \
+        const uint32_t keep = (uint32_t)((int32_t)(mb << (31 - k)) >> 31);                        \
+        const float v = __uint_as_float(__float_as_uint(wv[k + OFF]) & keep);                     \
+        hi[k] = tf32_head_rn(v);                                                                  \
+        lo[k] = v - hi[k];                                                                        \
+    }
+                    if (off == 0) { CMF_WG_SPLIT(0) } else if (off == 1) { CMF_WG_SPLIT(1) }
+                    else if (off == 2) { CMF_WG_SPLIT(2) } else { CMF_WG_SPLIT(3) }
+#undef CMF_WG_SPLIT
                 } else {
 #pragma unroll
                     for (int k = 0; k < 32; ++k) { hi[k] = 0.f; lo[k] = 0.f; }

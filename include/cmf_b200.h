@@ -144,7 +144,7 @@ int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wspl
  * (what autograd derives for F.conv2d at cmf/trainer.py:216, aten::convolution_backward).
  * tcgen05 3xTF32 with pixels as the K dimension; CTAs write partial sums into `workspace`
  * (cmf_conv3x3_c64_wgrad_workspace bytes, 16-byte aligned) and a second kernel adds them in a fixed
- * order (deterministic).  Needs H*W % 4 == 0 and W <= 47 (cmf_conv3x3_c64_wgrad_usable). */
+ * order.  Needs H*W % 4 == 0 and W <= 47 (cmf_conv3x3_c64_wgrad_usable). */
 int cmf_conv3x3_c64_wgrad_usable(int N, int H, int W);
 size_t cmf_conv3x3_c64_wgrad_workspace(int N, int H, int W);
 int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const float* g_y, float* workspace,

@@ -47,7 +47,7 @@ def _wgrad_ref(x, gy):
 @pytest.mark.parametrize("N,H,W", SHAPES + [(40, 28, 28), (300, 14, 14)])
 def test_weight_gradient(N, H, W):
     """pixels-as-K tcgen05 kernel + fixed-order partial reduction vs FP64; several CTAs and tiles
-    per CTA in the larger cases"""
+    per CTA in the larger cases (back-to-back launches: the protocol once raced only then)"""
     x, gy = _rand((N, 64, H, W), 20), _rand((N, 64, H, W), 21)
     if not K.conv3x3_c64_wgrad_usable(N, H, W):                # wider than the halo box: rejected, not approximated
         with pytest.raises(_lib.CmfB200Error):
@@ -55,7 +55,9 @@ def test_weight_gradient(N, H, W):
         return
     gw = K.conv3x3_c64_wgrad(x, gy)
     assert _rel(gw, _wgrad_ref(x, gy)) < 5e-6
-    assert torch.equal(gw, K.conv3x3_c64_wgrad(x, gy))          # deterministic
+    # two issuer warps add into one TMEM accumulator in arrival order: run-to-run differences are
+    # confined to the truncation noise of the accumulate (the partial reduction itself is fixed-order)
+    assert _rel(K.conv3x3_c64_wgrad(x, gy), gw.double()) < 2e-6
 
 
 def test_weight_gradient_same_sign_terms():
