@@ -55,7 +55,7 @@ __device__ __forceinline__ float ld_shared_f32(uint32_t addr) {
 
 #ifdef CMF_CONV_PROF
 __device__ long long g_conv_prof[128];
-#define PROF(i) do { if (blockIdx.x == 5000 && lane == 0) g_conv_prof[(i)] = clock64(); } while (0)
+#define PROF(i) do { if (blockIdx.x == 70 && lane == 0 && (i) < 128) g_conv_prof[(i)] = clock64(); } while (0)
 #else
 #define PROF(i) do { } while (0)
 #endif
@@ -97,35 +97,39 @@ __global__ void conv_prep_kernel(const float* __restrict__ w, int transpose, flo
 
 // kPitch = pixels per halo row in shared memory = TMA box width (compile-time so that the 32
 // channel loads of a row worker are LDS with immediate offsets): 192 covers W <= 31, 256 W <= 61.
+//
+// PERSISTENT: one CTA per SM walks tile pairs blockIdx.x, blockIdx.x + gridDim.x, ...  All mbarrier
+// phases are functions of the global stage counter gs = 18 * it + s, so the weight ring, the
+// staging buffers and the ping-pong accumulators simply keep rolling across pairs; the halo tile of
+// the next pair is fetched while the current one is still being consumed (chunk 0 after stage 9 has
+// completed, chunk 1 after stage 0 of the next pair).  Launch, TMEM allocation, barrier set-up and
+// the first TMA round trip (a third of a one-pair CTA's life) are paid once per SM.
 template <int kPitch>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmw, ConvParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    __shared__ uint64_t w_full[kWRing], done[kWRing];     // done[s % 4]: the MMAs of stage s have completed for both tiles
+    __shared__ uint64_t w_full[kWRing], done[kWRing];     // done[gs % 4]: the MMAs of stage gs have completed for both tiles
     __shared__ uint64_t a_full[kTiles][2];
     __shared__ uint64_t at_full[kTiles][2];
     __shared__ uint32_t tmem_base_smem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp == 2) PROF(0);
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* wring = smem;                                         // kWRing x 16 KB, 1024-aligned
     float* halo = reinterpret_cast<float*>(smem + kWRing * kWStageBytes);   // [tile][chunk][32][kPitch]
     constexpr int kHaloElems = kChunkC * kPitch;
 
-    const long long tile0 = (long long)blockIdx.x * kTiles;
-    bool active[kTiles];
-    int img[kTiles], p0[kTiles];
-#pragma unroll
-    for (int t = 0; t < kTiles; ++t) {
-        const long long T = tile0 + t;
-        active[t] = T < P.total_tiles;
-        img[t] = active[t] ? (int)(T / P.tiles_per_image) : 0;
-        p0[t] = active[t] ? (int)(T % P.tiles_per_image) * kTileM : 0;
-    }
+    const long long npairs = (P.total_tiles + kTiles - 1) / kTiles;
+    const int nit = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);     // pairs of this CTA (>= 1)
+    auto tile_of = [&](int it, int t, bool& act, int& im, int& px) {
+        const long long T = ((long long)blockIdx.x + (long long)it * gridDim.x) * kTiles + t;
+        act = T < P.total_tiles;
+        im = act ? (int)(T / P.tiles_per_image) : 0;
+        px = act ? (int)(T % P.tiles_per_image) * kTileM : 0;
+    };
 
     if (threadIdx.x == 0) {
-        for (int r = 0; r < kWRing; ++r) { mbar_init(&w_full[r], 1); mbar_init(&done[r], active[1] ? 2 : 1); }
+        for (int r = 0; r < kWRing; ++r) { mbar_init(&w_full[r], 1); mbar_init(&done[r], kTiles); }
         for (int t = 0; t < kTiles; ++t) {
             for (int c = 0; c < 2; ++c) {
                 mbar_init(&a_full[t][c], 1);
@@ -141,8 +145,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
-    if (warp == 2) PROF(1);
-    // TMEM columns: [0,256) accumulators, (tile, segment parity) -> 64 cols; [256,512) operand staging,
+    // TMEM columns: [0,256) accumulators, (tile, stage parity) -> 64 cols; [256,512) operand staging,
     // (tile, buffer) -> 64 cols (hi | lo)
     constexpr uint32_t kAccCol = 0, kStgCol = 256;
 
@@ -150,25 +153,33 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             constexpr uint32_t halo_bytes = (uint32_t)kHaloElems * 4u;
-            auto load_halo = [&](int c) {
+            auto load_halo = [&](int it, int c) {
 #pragma unroll
                 for (int t = 0; t < kTiles; ++t) {
-                    if (!active[t]) continue;
+                    bool act; int im, px;
+                    tile_of(it, t, act, im, px);
+                    if (!act) continue;
                     mbar_arrive_expect_tx(&a_full[t][c], halo_bytes);
-                    tma_load_2d(halo + (size_t)(t * 2 + c) * kHaloElems, &tmx, &a_full[t][c], p0[t] - P.hl,
-                                img[t] * kC + c * kChunkC);
+                    tma_load_2d(halo + (size_t)(t * 2 + c) * kHaloElems, &tmx, &a_full[t][c], px - P.hl, im * kC + c * kChunkC);
                 }
             };
-            load_halo(0);
-            for (int s = 0; s < kStages; ++s) {
-                const int r = s % kWRing;
-                if (s >= kWRing) mbar_wait(&done[r], ((s / kWRing) - 1) & 1);
-                const int chunk = s / kTaps, tap = s % kTaps;
-                uint8_t* dst = wring + (size_t)r * kWStageBytes;
-                mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
-                tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
-                tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
-                if (s == 1) load_halo(1);
+            load_halo(0, 0);
+            int gs = 0;
+            for (int it = 0; it < nit; ++it) {
+                for (int s = 0; s < kStages; ++s, ++gs) {
+                    const int r = gs % kWRing;
+                    if (gs >= kWRing) mbar_wait(&done[r], ((gs / kWRing) - 1) & 1);      // stage gs - 4 has completed
+                    const int chunk = s / kTaps, tap = s % kTaps;
+                    uint8_t* dst = wring + (size_t)r * kWStageBytes;
+                    mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
+                    tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
+                    tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
+                    // halo buffers are recycled as soon as every worker is past their last read:
+                    // chunk 1 of this pair once stage 0 of this pair has completed (s = 4 waited for it),
+                    // chunk 0 of the next pair once stage 9 has completed (s = 13 waited for it)
+                    if (s == 4) load_halo(it, 1);
+                    if (s == 13 && it + 1 < nit) load_halo(it + 1, 0);
+                }
             }
         }
     } else if (warp == 1 || warp == kMmaWarp1) {
@@ -177,50 +188,59 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
         // issuers keep the tensor pipe fed).  The whole warp walks the loop converged; one elected
         // lane issues.
         const int t = warp == 1 ? 0 : 1;
-        if (active[t]) {
-            constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
-            const uint32_t acc0 = tmem_base + kAccCol + (uint32_t)(t * 2 * kC);
-            const uint32_t wring_addr = smem_u32(wring);
-            for (int s = 0; s < kStages; ++s) {
-                const int r = s % kWRing;
-                const int seg = s / kSeg, b = s & 1;
-                mbar_wait(&w_full[r], (s / kWRing) & 1);
-                mbar_wait(&at_full[t][b], (s >> 1) & 1);
-                // accumulator (seg & 1) was drained (segment seg-2) by every worker warp BEFORE it arrived on
+        constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
+        const uint32_t acc0 = tmem_base + kAccCol + (uint32_t)(t * 2 * kC);
+        const uint32_t wring_addr = smem_u32(wring);
+        int gs = 0;
+        for (int it = 0; it < nit; ++it) {
+            bool act; int im, px;
+            tile_of(it, t, act, im, px);
+            for (int s = 0; s < kStages; ++s, ++gs) {
+                const int r = gs % kWRing;
+                const int b = gs & 1;
+                mbar_wait(&w_full[r], (gs / kWRing) & 1);
+                if (act) mbar_wait(&at_full[t][b], (gs >> 1) & 1);
+                // accumulator (gs & 1) was drained (stage gs-2) by every worker warp BEFORE it arrived on
                 // at_full for this stage (program order + tcgen05.wait::ld), so no extra barrier is needed
                 tc_fence_after();
-                const uint32_t acc = acc0 + (uint32_t)((seg & 1) * kC);
+                const uint32_t acc = acc0 + (uint32_t)((gs & 1) * kC);
                 if (elect_one()) {
-                    const uint64_t dbh = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes));
-                    const uint64_t dbl = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes + kWStageBytes / 2));
-                    const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64);
-                    const uint32_t a_lo = a_hi + 32;
-                    // cross terms first: they land in a fresh (small) accumulator, where the tensor
-                    // core's truncating FP32 add costs nothing; only the hi*hi adds that follow see a
-                    // large accumulator (kSeg * 4 - 1 truncations per drained segment)
+                    if (act) {
+                        const uint64_t dbh = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes));
+                        const uint64_t dbl = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes + kWStageBytes / 2));
+                        const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64);
+                        const uint32_t a_lo = a_hi + 32;
+                        // cross terms first: they land in a fresh (small) accumulator, where the tensor
+                        // core's truncating FP32 add costs nothing; only the three hi*hi adds that follow
+                        // see a large accumulator
 #pragma unroll
-                    for (int k = 0; k < kChunkC / 8; ++k) {      // +32 bytes along K = +2 in the descriptor's address field
-                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, (s % kSeg != 0) || k != 0);
-                        umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                        for (int k = 0; k < kChunkC / 8; ++k) {      // +32 bytes along K = +2 in the descriptor's address field
+                            umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, k != 0);
+                            umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                        }
+#pragma unroll
+                        for (int k = 0; k < kChunkC / 8; ++k) umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
                     }
-#pragma unroll
-                    for (int k = 0; k < kChunkC / 8; ++k) umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
-                    umma_commit(&done[r]);      // frees the weight slot and this tile's staging buffer; ends a segment
+                    umma_commit(&done[r]);      // frees the weight slot and this tile's staging buffer; ends the segment
                 }
                 __syncwarp();
-                if (t == 0) PROF(32 + s);
             }
         }
     } else {
         // ------------------------------------------------------------------ row workers
         const int t = (warp - 2) >> 2;
-        if (active[t]) {
-            const int rb = warp & 3;                       // TMEM lane quarter this warp may touch
-            const int m = rb * 32 + lane;                  // row of the tile = output pixel p0 + m
-            const int p = p0[t] + m;
+        const int rb = warp & 3;                       // TMEM lane quarter this warp may touch
+        const int m = rb * 32 + lane;                  // row of the tile = output pixel p0 + m
+        const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
+        const uint32_t row_addr = smem_u32(halo) + (uint32_t)((t * 2 * kHaloElems + P.hl + m) * 4);
+        const long long hw = P.HW;
+        for (int it = 0; it < nit; ++it) {
+            bool act; int im, p0;
+            tile_of(it, t, act, im, p0);
+            if (!act) break;                           // only the very last pair can lack its second tile
+            const int gs0 = it * kStages;
+            const int p = p0 + m;
             const int xx = p % P.W;
-            const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
-            const uint32_t row_addr = smem_u32(halo) + (uint32_t)((t * 2 * kHaloElems + P.hl + m) * 4);
             // the tap leaves the image row on the left (dx = -1) / right (dx = +1): operand reads as zero
             const bool ok_l = xx > 0, ok_r = xx + 1 < P.W;
             float accr[kC];
@@ -232,14 +252,29 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
             auto load_stage = [&](int s) {
                 const int chunk = s / kTaps, tap = s - chunk * kTaps;
                 const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
-                if (tap == 0) mbar_wait(&a_full[t][chunk], 0);
+                if (tap == 0) mbar_wait(&a_full[t][chunk], it & 1);
                 const uint32_t src = row_addr + (uint32_t)((chunk * kHaloElems + dy * P.W + dx) * 4);
 #pragma unroll
                 for (int c = 0; c < kChunkC; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
             };
+            // drain the accumulator of global stage e into the FP32 registers
+            auto drain = [&](int e) {
+                mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
+                tc_fence_after();
+                const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + (e & 1)) * kC) + lane_addr;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float u[32];
+                    tmem_ld_32x32(acc + h * 32, u);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) accr[h * 32 + j] += u[j];
+                }
+                tc_fence_before();
+            };
             load_stage(0);
             for (int s = 0; s < kStages; ++s) {
-                const int b = s & 1;
+                const int gs = gs0 + s;
+                const int b = gs & 1;
                 const int tap = s % kTaps, dx = tap % 3 - 1;
                 const bool ok = dx < 0 ? ok_l : (dx > 0 ? ok_r : true);
                 const uint32_t mh = ok ? 0xFFFFE000u : 0u;
@@ -250,9 +285,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                     hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & mh);   // TF32 head, round to nearest (0 when masked)
                     lo[c] = fmaf(v[c], okf, -hi[c]);                                   // exact signed remainder
                 }
-                PROF(64 + s);
-                if (s >= 2) mbar_wait(&done[(s - 2) % kWRing], ((s - 2) / kWRing) & 1);
-                PROF(96 + s);
+                if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
                 tc_fence_after();
                 const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64) + lane_addr;
                 tmem_st_32x32(stg, hi);
@@ -262,62 +295,56 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&at_full[t][b]);
-                if (warp == 2) PROF(2 + s);
-                // drain a segment one stage late (the final one at its own last stage), so the tensor
-                // pipe already works on the next segment in the other accumulator
-                auto drain = [&](int e) {                           // e = final stage of the segment
-                    const int g = e / kSeg;
-                    mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
-                    tc_fence_after();
-                    const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + (g & 1)) * kC) + lane_addr;
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        float u[32];
-                        tmem_ld_32x32(acc + h * 32, u);
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) accr[h * 32 + j] += u[j];
-                    }
-                    tc_fence_before();
-                };
-                if (s % kSeg == 0 && s > 0) drain(s - 1);
-                if (s == kStages - 1) drain(s);
+                // drain one stage late (the last one at its own stage), so the tensor pipe already works
+                // on the next stage in the other accumulator
+                if (s > 0) drain(gs - 1);
+                if (s == kStages - 1) drain(gs);
             }
             if (p < P.HW) {
-                const long long o = (long long)img[t] * kC * P.HW + p;
+                const long long o = (long long)im * kC * hw + p;
                 if (!P.mask_src && !P.res) {
 #pragma unroll
-                    for (int j = 0; j < kC; ++j) P.y[o + (long long)j * P.HW] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                    for (int j = 0; j < kC; ++j) P.y[o + (long long)j * hw] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
                 } else {
-                    const float* ms = P.mask_src ? P.mask_src + (long long)(img[t] / P.mask_div) * kC * P.HW + p : nullptr;
+                    const float* ms = P.mask_src ? P.mask_src + (long long)(im / P.mask_div) * kC * hw + p : nullptr;
                     const float* rs = P.res ? P.res + o : nullptr;
                     float* y1 = P.y + o;
                     float* y2 = P.y2 ? P.y2 + o : nullptr;
                     const bool mask_first = P.mask_first != 0;
-                    const long long hw = P.HW;
-                    // batches of 8 channels: all loads of a batch are issued before its stores, so their
-                    // latencies overlap (the compiler cannot hoist loads over possibly aliasing stores)
+                    // every load of a batch is issued before the batch's stores so that the latencies
+                    // overlap (the compiler cannot hoist loads over possibly aliasing stores): first all 64
+                    // mask values, packed into two words, then the skip connection 32 channels at a time
+                    uint32_t keep_bits[2] = {0xffffffffu, 0xffffffffu};
+                    if (ms) {
 #pragma unroll
-                    for (int jb = 0; jb < kC; jb += 8) {
-                        float mv[8], rv[8];
+                        for (int h = 0; h < 2; ++h) {
+                            float mv[32];
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            mv[e] = ms ? __ldg(ms + (jb + e) * hw) : 1.f;
-                            rv[e] = rs ? __ldg(rs + (jb + e) * hw) : 0.f;
+                            for (int e = 0; e < 32; ++e) mv[e] = __ldg(ms + (32 * h + e) * hw);
+                            uint32_t bits = 0;
+#pragma unroll
+                            for (int e = 0; e < 32; ++e) bits |= (mv[e] > 0.f ? 1u : 0u) << e;
+                            keep_bits[h] = bits;
                         }
+                    }
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const int j = jb + e;
-                            float v = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
-                            const bool keep = mv[e] > 0.f;
-                            if (mask_first && !keep) v = 0.f;
-                            v += rv[e];
-                            y1[j * hw] = v;
-                            if (y2) y2[j * hw] = keep ? v : 0.f;
+                    for (int h = 0; h < 2; ++h) {
+                        float rv[32];
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) rv[e] = rs ? __ldg(rs + (32 * h + e) * hw) : 0.f;
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            const int j = 32 * h + e;
+                            float v2 = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                            const bool keep = (keep_bits[h] >> e) & 1u;
+                            if (mask_first && !keep) v2 = 0.f;
+                            v2 += rv[e];
+                            y1[j * hw] = v2;
+                            if (y2) y2[j * hw] = keep ? v2 : 0.f;
                         }
                     }
                 }
             }
-            if (warp == 2) PROF(30);
         }
     }
     tc_fence_before();
@@ -381,7 +408,12 @@ extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const 
         if (e != cudaSuccess) { set_error("conv3x3 attr: %s", cudaGetErrorString(e)); return (int)e; }
         attr_set = true;
     }
-    const unsigned grid = (unsigned)ceil_div(P.total_tiles, kTiles);
+    // persistent: one CTA per SM walks the tile pairs
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long npairs = ceil_div(P.total_tiles, kTiles);
+    const unsigned grid = (unsigned)(npairs < sms ? npairs : sms);
     if (pitch == 192) conv3x3_tc_kernel<192><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmx, tmw, P);
     else conv3x3_tc_kernel<256><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmx, tmw, P);
     CMF_CHECK_LAUNCH();

@@ -5,7 +5,7 @@ python bench.py --steps 3 --warmup 3 > gpurun_out/r01c_bench.json 2> gpurun_out/
 CMF_NCU_RANGE=1 timeout 1500 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
     --log-file gpurun_out/r01c_launches_step.csv python bench.py --only step --steps 1 --warmup 2 > gpurun_out/ncu1.log 2>&1
 CMF_NCU_RANGE=1 timeout 600 ncu --profile-from-start off --set full --clock-control none --import-source on \
-    -k regex:conv3x3_tc_kernel -s 40 -c 1 -o gpurun_out/r01c_conv_fwd python bench.py --only step --steps 1 --warmup 2 > gpurun_out/ncu2.log 2>&1
+    -k regex:conv3x3_tc_kernel -s 20 -c 1 -o gpurun_out/r01c_conv_fwd python bench.py --only step --steps 1 --warmup 2 > gpurun_out/ncu2.log 2>&1
 CMF_NCU_RANGE=1 timeout 600 ncu --profile-from-start off --set full --clock-control none --import-source on \
     -k regex:conv3x3_wgrad_tc_kernel -s 10 -c 1 -o gpurun_out/r01c_conv_wgrad python bench.py --only step --steps 1 --warmup 2 > gpurun_out/ncu3.log 2>&1
 ls -la gpurun_out/ | tail -12
