@@ -25,6 +25,7 @@ call `cmf/trainer.py:213-216` makes -- followed by the flat-bucket gradient all-
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import os
 import subprocess
@@ -279,7 +280,7 @@ def run_own_arm(args, cfg, schema):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     torch.backends.cuda.matmul.allow_tf32 = False      # FP32-accurate conditioners (parity contract)
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cudnn.benchmark = True
@@ -379,9 +380,9 @@ def run_own_arm(args, cfg, schema):
     value = world * B * args.steps / (ms * 1e-3)
     e2e = world * B * args.steps / (ms_e2e * 1e-3)
 
-    sa = conv = None
+    sa = None
+    conv = conv_kernel_times(step_resident, dev)      # a full step incl. the gradient all-reduce: EVERY rank runs it
     if rank == 0:
-        conv = conv_kernel_times(step_resident, dev)
         sa = scope_a(head, args.scope_a_batch, max(args.steps, 5), 3, dev)
     clocks = sampler.stop() if rank == 0 else None
     peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
