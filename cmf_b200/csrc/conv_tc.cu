@@ -6,22 +6,27 @@
 //
 // Formulation (implicit GEMM, nothing is materialised):
 //     y[n, co, p] = sum_{tap, ci} x[n, ci, p + dy*W + dx] * w[co, ci, tap]      (p = flat pixel)
-//   M = 128 consecutive flat pixels of one image, N = 64 output channels, K = 9 taps x 64 inputs.
-//   * The pixel operand lives in TENSOR MEMORY.  One TMA box per (tile, 32-channel chunk) brings the
-//     tile plus a halo of W+1 pixels on either side into shared memory ([channel][pixel], rows
-//     above/below the image are zero-filled by TMA's out-of-bounds rule).  A "row worker" thread
-//     owns one output pixel: for each of the 9 taps it reads its 32 shifted inputs, zeroes them
-//     when the tap leaves the image row (x + dx outside [0, W)), splits them exactly into a
-//     TF32 head and a remainder (v = hi + lo) and writes both to TMEM with tcgen05.st.  The MMA
-//     therefore reads only the weights from shared memory (2 KB per instruction instead of 6 KB):
-//     the tensor pipe is no longer bound by shared-memory bandwidth as the SS-mode Gram is.
+//   M = 128 consecutive pixels of the PACKED pixel stream (image 0's H*W pixels, then image 1's,
+//   ...: a tile may straddle images, so no MMA row is wasted on the ragged end of an image --
+//   28x28 needs 6.125 tiles per image instead of 7, 14x14 1.53 instead of 2), N = 64 output
+//   channels, K = 9 taps x 64 inputs.
+//   * The pixel operand lives in TENSOR MEMORY.  Per (tile, 32-channel chunk) the producer warp
+//     (lane = channel) copies the tile's window of the stream -- the tile plus W+1 pixels either
+//     side -- into shared memory as [channel][pixel] with one bulk copy (cp.async.bulk) per
+//     channel and image touched.  A "row worker" thread owns one output pixel: for each of the 9
+//     taps it reads its 32 shifted inputs (or zero when the tap leaves ITS image: y + dy outside
+//     [0, H) or x + dx outside [0, W) -- so whatever the window holds beyond an image border is
+//     never used), splits them exactly into a TF32 head and a remainder (v = hi + lo) and writes
+//     both to TMEM with tcgen05.st.  The MMA therefore reads only the weights from shared memory
+//     (2 KB per instruction instead of 6 KB): the tensor pipe is no longer bound by shared-memory
+//     bandwidth as the SS-mode Gram is.
 //   * The weights arrive pre-split (hi | lo, tap-major, K-major rows) from a tiny prep kernel and
 //     are streamed by TMA through a 4-deep ring; each stage is shared by the two pixel tiles of
 //     the CTA, which halves the L2 -> SM traffic (the L2 slice throughput, not HBM, is the limit
 //     once the pixel operand is read once instead of 9 times).
 //   * Three MMAs per K-step: hi*Whi + hi*Wlo + lo*Whi (lo*Wlo ~ 2^-22 relative is dropped, as in
 //     the Gram kernel).  The tensor core's FP32 accumulator truncates, so the accumulator is
-//     drained into registers with round-to-nearest adds every 6 stages (K = 192).
+//     drained into registers with round-to-nearest adds after every stage (K = 32).
 //   * The same kernel is the data gradient: dgrad = conv(g_y, w^T flipped); the prep kernel writes
 //     that variant of the weights.
 #include "common.cuh"
@@ -62,9 +67,11 @@ __device__ long long g_conv_prof[128];
 
 struct ConvParams {
     int N, H, W, HW;
-    int tiles_per_image;
-    long long total_tiles;
-    int hl;                            // halo pixels in front of the tile: W+1 rounded up to 4 (TMA needs 16-byte box starts)
+    long long total_px;                // N * H * W: length of the packed pixel stream
+    long long total_tiles;             // ceil(total_px / 128)
+    int hl;                            // halo pixels in front of the tile: W+1 rounded up to 4 (bulk copies need 16-byte starts)
+    int win;                           // window length in pixels: hl + 128 + W + 1 rounded up to 4 (<= kPitch)
+    const float* x;                    // (N, 64, H, W)
     const float* bias;                 // (64) or null
     // fused epilogue:  t = acc + bias;  if (mask_first) t *= m;  if (res) t += res;  y = t;
     //                  if (y2) y2 = t * m      with m = mask_src[n / mask_div, co, p] > 0
@@ -106,7 +113,7 @@ __global__ void conv_prep_kernel(const float* __restrict__ w, int transpose, flo
 // the first TMA round trip (a third of a one-pair CTA's life) are paid once per SM.
 template <int kPitch>
 __global__ void __launch_bounds__(kConvThreads, 1)
-conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmw, ConvParams P) {
+conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ uint64_t w_full[kWRing], done[kWRing];     // done[gs % 4]: the MMAs of stage gs have completed for both tiles
     __shared__ uint64_t a_full[kTiles][2];
@@ -121,11 +128,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
 
     const long long npairs = (P.total_tiles + kTiles - 1) / kTiles;
     const int nit = (int)((npairs - blockIdx.x + gridDim.x - 1) / gridDim.x);     // pairs of this CTA (>= 1)
-    auto tile_of = [&](int it, int t, bool& act, int& im, int& px) {
+    // tile t of this CTA's it-th pair: first pixel g0 of the packed stream
+    auto tile_of = [&](int it, int t, bool& act, long long& g0) {
         const long long T = ((long long)blockIdx.x + (long long)it * gridDim.x) * kTiles + t;
         act = T < P.total_tiles;
-        im = act ? (int)(T / P.tiles_per_image) : 0;
-        px = act ? (int)(T % P.tiles_per_image) * kTileM : 0;
+        g0 = act ? T * kTileM : 0;
     };
 
     if (threadIdx.x == 0) {
@@ -137,7 +144,6 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
             }
         }
         mbar_fence_init();
-        prefetch_tmap(&tmx);
         prefetch_tmap(&tmw);
     }
     if (warp == 1) tmem_alloc<kConvTmemCols>(&tmem_base_smem);
@@ -151,35 +157,57 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
-            constexpr uint32_t halo_bytes = (uint32_t)kHaloElems * 4u;
-            auto load_halo = [&](int it, int c) {
+        // The whole warp walks the stage loop converged: lane 0 streams the weights; the halo
+        // windows are fetched by all 32 lanes, lane = channel of the chunk.  Column j of a window
+        // row is pixel g0 - hl + j of the packed stream; the stream is contiguous in memory only
+        // inside one image, so each lane issues one bulk copy per image the window touches
+        // (starts and lengths are multiples of 4 pixels because H*W, hl and 128 are).
+        auto load_halo = [&](int it, int c) {
 #pragma unroll
-                for (int t = 0; t < kTiles; ++t) {
-                    bool act; int im, px;
-                    tile_of(it, t, act, im, px);
-                    if (!act) continue;
-                    mbar_arrive_expect_tx(&a_full[t][c], halo_bytes);
-                    tma_load_2d(halo + (size_t)(t * 2 + c) * kHaloElems, &tmx, &a_full[t][c], px - P.hl, im * kC + c * kChunkC);
+            for (int t = 0; t < kTiles; ++t) {
+                bool act; long long g0;
+                tile_of(it, t, act, g0);
+                if (!act) continue;
+                const long long ws = g0 - P.hl;
+                long long lo = ws < 0 ? 0 : ws;
+                long long hi = ws + P.win;
+                if (hi > P.total_px) hi = P.total_px;
+                if (lane == 0) mbar_arrive_expect_tx(&a_full[t][c], (uint32_t)((hi - lo) * 4 * kChunkC));
+                __syncwarp();
+                const uint32_t dst_row = smem_u32(halo + (size_t)(t * 2 + c) * kHaloElems + (size_t)lane * kPitch);
+                const uint32_t bar = smem_u32(&a_full[t][c]);
+                const long long hw = P.HW;
+                for (long long im = lo / hw; lo < hi; ++im) {
+                    long long end = (im + 1) * hw;
+                    if (end > hi) end = hi;
+                    const float* src = P.x + ((im * kC + c * kChunkC + lane) * hw + (lo - im * hw));
+                    asm volatile(
+                        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                            "r"(dst_row + (uint32_t)((lo - ws) * 4)), "l"(src), "r"((uint32_t)((end - lo) * 4)), "r"(bar)
+                        : "memory");
+                    lo = end;
                 }
-            };
-            load_halo(0, 0);
-            int gs = 0;
-            for (int it = 0; it < nit; ++it) {
-                for (int s = 0; s < kStages; ++s, ++gs) {
-                    const int r = gs % kWRing;
-                    if (gs >= kWRing) mbar_wait(&done[r], ((gs / kWRing) - 1) & 1);      // stage gs - 4 has completed
+            }
+        };
+        load_halo(0, 0);
+        int gs = 0;
+        for (int it = 0; it < nit; ++it) {
+            for (int s = 0; s < kStages; ++s, ++gs) {
+                const int r = gs % kWRing;
+                if (gs >= kWRing) mbar_wait(&done[r], ((gs / kWRing) - 1) & 1);      // stage gs - 4 has completed
+                if (lane == 0) {
                     const int chunk = s / kTaps, tap = s % kTaps;
                     uint8_t* dst = wring + (size_t)r * kWStageBytes;
                     mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
                     tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
                     tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
-                    // halo buffers are recycled as soon as every worker is past their last read:
-                    // chunk 1 of this pair once stage 0 of this pair has completed (s = 4 waited for it),
-                    // chunk 0 of the next pair once stage 9 has completed (s = 13 waited for it)
-                    if (s == 4) load_halo(it, 1);
-                    if (s == 13 && it + 1 < nit) load_halo(it + 1, 0);
                 }
+                // halo buffers are recycled as soon as every worker is past their last read:
+                // chunk 1 of this pair once stage 0 of this pair has completed (s = 4 waited for it),
+                // chunk 0 of the next pair once stage 9 has completed (s = 13 waited for it)
+                if (s == 4) load_halo(it, 1);
+                if (s == 13 && it + 1 < nit) load_halo(it + 1, 0);
+                __syncwarp();
             }
         }
     } else if (warp == 1 || warp == kMmaWarp1) {
@@ -193,8 +221,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
         const uint32_t wring_addr = smem_u32(wring);
         int gs = 0;
         for (int it = 0; it < nit; ++it) {
-            bool act; int im, px;
-            tile_of(it, t, act, im, px);
+            bool act; long long g0;
+            tile_of(it, t, act, g0);
             for (int s = 0; s < kStages; ++s, ++gs) {
                 const int r = gs % kWRing;
                 const int b = gs & 1;
@@ -235,14 +263,27 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
         const uint32_t row_addr = smem_u32(halo) + (uint32_t)((t * 2 * kHaloElems + P.hl + m) * 4);
         const long long hw = P.HW;
         for (int it = 0; it < nit; ++it) {
-            bool act; int im, p0;
-            tile_of(it, t, act, im, p0);
+            bool act; long long g0;
+            tile_of(it, t, act, g0);
             if (!act) break;                           // only the very last pair can lack its second tile
             const int gs0 = it * kStages;
-            const int p = p0 + m;
-            const int xx = p % P.W;
-            // the tap leaves the image row on the left (dx = -1) / right (dx = +1): operand reads as zero
-            const bool ok_l = xx > 0, ok_r = xx + 1 < P.W;
+            // this worker's pixel of the packed stream -> (image, flat pixel, row, column)
+            const long long g = g0 + m;
+            const bool valid = g < P.total_px;         // the stream's last tile may be ragged
+            const int im = valid ? (int)(g / hw) : 0;
+            const int p = valid ? (int)(g - (long long)im * hw) : 0;
+            const int yy = p / P.W, xx = p - yy * P.W;
+            // bit tap of okbits: the tap stays inside this pixel's image (otherwise the operand is zero;
+            // the window holds a neighbouring image's pixels or nothing at that position)
+            uint32_t okbits = 0;
+            if (valid) {
+#pragma unroll
+                for (int tp = 0; tp < kTaps; ++tp) {
+                    const int dy = tp / 3 - 1, dx = tp % 3 - 1;
+                    const bool ok = yy + dy >= 0 && yy + dy < P.H && xx + dx >= 0 && xx + dx < P.W;
+                    okbits |= (ok ? 1u : 0u) << tp;
+                }
+            }
             float accr[kC];
 #pragma unroll
             for (int j = 0; j < kC; ++j) accr[j] = 0.f;
@@ -254,8 +295,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                 const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
                 if (tap == 0) mbar_wait(&a_full[t][chunk], it & 1);
                 const uint32_t src = row_addr + (uint32_t)((chunk * kHaloElems + dy * P.W + dx) * 4);
+                const bool ok = (okbits >> tap) & 1u;
 #pragma unroll
-                for (int c = 0; c < kChunkC; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
+                for (int c = 0; c < kChunkC; ++c) v[c] = ok ? ld_shared_f32(src + (uint32_t)(c * kPitch * 4)) : 0.f;
             };
             // drain the accumulator of global stage e into the FP32 registers
             auto drain = [&](int e) {
@@ -275,15 +317,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
             for (int s = 0; s < kStages; ++s) {
                 const int gs = gs0 + s;
                 const int b = gs & 1;
-                const int tap = s % kTaps, dx = tap % 3 - 1;
-                const bool ok = dx < 0 ? ok_l : (dx > 0 ? ok_r : true);
-                const uint32_t mh = ok ? 0xFFFFE000u : 0u;
-                const float okf = ok ? 1.f : 0.f;
                 float hi[32], lo[32];
 #pragma unroll
                 for (int c = 0; c < kChunkC; ++c) {
-                    hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & mh);   // TF32 head, round to nearest (0 when masked)
-                    lo[c] = fmaf(v[c], okf, -hi[c]);                                   // exact signed remainder
+                    hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & 0xFFFFE000u);   // TF32 head, round to nearest
+                    lo[c] = v[c] - hi[c];                                                       // exact signed remainder
                 }
                 if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
                 tc_fence_after();
@@ -300,7 +338,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant
                 if (s > 0) drain(gs - 1);
                 if (s == kStages - 1) drain(gs);
             }
-            if (p < P.HW) {
+            if (valid) {
                 const long long o = (long long)im * kC * hw + p;
                 if (!P.mask_src && !P.res) {
 #pragma unroll
@@ -386,18 +424,18 @@ extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const 
     CMF_REQUIRE(aligned16(x) && aligned16(wsplit), "conv3x3: x and wsplit must be 16-byte aligned");
     ConvParams P{};
     P.N = N; P.H = H; P.W = W; P.HW = H * W;
-    P.tiles_per_image = (int)ceil_div(P.HW, kTileM);
-    P.total_tiles = (long long)N * P.tiles_per_image;
+    P.total_px = (long long)N * P.HW;
+    P.total_tiles = ceil_div(P.total_px, (long long)kTileM);
+    P.x = x;
     P.hl = (W + 4) & ~3;
     CMF_REQUIRE(!mask_src || (mask_div >= 1 && N % mask_div == 0), "conv3x3: mask_div must divide N");
     CMF_REQUIRE(!y2 || mask_src, "conv3x3: second output needs a mask source");
     P.bias = bias; P.y = y; P.y2 = y2;
     P.mask_src = mask_src; P.mask_div = mask_src ? mask_div : 1; P.mask_first = mask_first; P.res = res;
-    const int pitch = (kTileM + P.hl + W + 1 <= 192) ? 192 : 256;
-    CUtensorMap tmx, tmw;
-    int rc = make_tmap_2d_plain_f32(&tmx, x, (uint64_t)N * kC, (uint64_t)P.HW, (uint64_t)P.HW, (uint32_t)pitch, kChunkC);
-    if (rc != 0) return rc;
-    rc = make_tmap_2d_f32(&tmw, wsplit, (uint64_t)2 * kTaps * kC, (uint64_t)kC, (uint64_t)kC, kC, 0);
+    P.win = (kTileM + P.hl + W + 1 + 3) & ~3;
+    const int pitch = P.win <= 192 ? 192 : 256;
+    CUtensorMap tmw;
+    int rc = make_tmap_2d_f32(&tmw, wsplit, (uint64_t)2 * kTaps * kC, (uint64_t)kC, (uint64_t)kC, kC, 0);
     if (rc != 0) return rc;
     const size_t smem = (size_t)kWRing * kWStageBytes + (size_t)kTiles * 2 * kChunkC * pitch * 4 + 1024;
     static bool attr_set = false;
@@ -414,8 +452,8 @@ extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const long long npairs = ceil_div(P.total_tiles, kTiles);
     const unsigned grid = (unsigned)(npairs < sms ? npairs : sms);
-    if (pitch == 192) conv3x3_tc_kernel<192><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmx, tmw, P);
-    else conv3x3_tc_kernel<256><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmx, tmw, P);
+    if (pitch == 192) conv3x3_tc_kernel<192><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);
+    else conv3x3_tc_kernel<256><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);
     CMF_CHECK_LAUNCH();
     return 0;
 }

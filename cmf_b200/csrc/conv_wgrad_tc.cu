@@ -71,6 +71,14 @@ struct WgradParams {
     float* partial;                     // [grid][9][64 ci][64 co]
 };
 
+// The last tile of an image is ragged (28x28: 16 of 128 pixels, 14x14: 68): its 32-pixel sub-chunks
+// that lie entirely past the image are all-zero K-steps and are skipped -- 25 instead of 28
+// sub-chunks per 28x28 image, 7 instead of 8 per 14x14 image.  Every role derives the same count.
+__device__ __forceinline__ int live_subchunks(int hw, int p0) {
+    const int n = (hw - p0 + 31) >> 5;
+    return n < kSub ? n : kSub;
+}
+
 template <int kPitch>
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmg, WgradParams P) {
@@ -138,7 +146,9 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         int ns = 0;
         for (int i = 0; i < nt; ++i) {
             const int buf = i & 1;
-            for (int n = 0; n < kStagings; ++n, ++ns) {
+            const int nq = live_subchunks(P.HW, (int)((tile_begin + i) % P.tiles_per_image) * kTileM);
+            const int cnt = nq * kPairs;
+            for (int n = 0; n < cnt; ++n, ++ns) {
                 const int q = n / kPairs, j = n - q * kPairs;
                 const int sb = ns % kStgBufs;
                 if (j == 0) mbar_wait(&b_ready[q], i & 1);
@@ -158,10 +168,18 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     }
                     umma_commit(&st_done[sb]);
                     if (j == kPairs - 1) umma_commit(&qdone[q]);
-                    if (n == kStagings - 1) umma_commit(&tile_done[buf]);
                 }
                 __syncwarp();
             }
+            // skipped sub-chunks: keep the b_ready / qdone phases in step (one per tile), and release
+            // the tile's buffers only after the splitters are done rewriting ALL of its g_y boxes
+            for (int q = nq; q < kSub; ++q) {
+                mbar_wait(&b_ready[q], i & 1);
+                if (elect_one()) umma_commit(&qdone[q]);
+                __syncwarp();
+            }
+            if (elect_one()) umma_commit(&tile_done[buf]);
+            __syncwarp();
         }
     } else if (warp == kMmaWarp1) {
         // second issuer slot unused (kIssuers == 1)
@@ -209,11 +227,12 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_init);
         }
-        int ns = g;
+        int ns_base = 0;                                  // stagings of the tiles before this one
         for (int i = 0; i < nt; ++i) {
             const int buf = i & 1;
             const long long T = tile_begin + i;
             const int p0 = (int)(T % P.tiles_per_image) * kTileM;
+            const int cnt = live_subchunks(P.HW, p0) * kPairs;
             // bit k of ml[q] / mr[q]: pixel p0 + 32 q + k may use a tap with dx = -1 / +1
             uint32_t ml[kSub], mr[kSub];
 #pragma unroll
@@ -223,7 +242,9 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                 mr[q] = __ballot_sync(0xffffffffu, xx + 1 < P.W);
             }
             mbar_wait(&x_full[buf], (i >> 1) & 1);
-            for (int n = g; n < kStagings; n += 2, ns += 2) {
+            // group g stages the stagings whose GLOBAL index is congruent to g mod 2 (cnt may be odd)
+            for (int n = (ns_base & 1) == g ? 0 : 1; n < cnt; n += 2) {
+                const int ns = ns_base + n;
                 const int q = n / kPairs, j = n - q * kPairs;
                 const int tap = 2 * j + a;
                 const int sb = ns % kStgBufs;
@@ -272,6 +293,7 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&st_full[sb]);
             }
+            ns_base += cnt;
         }
         // ------------------------------------------------------------------ epilogue: partial g_w
         if (nt > 0) {
