@@ -178,7 +178,9 @@ def conv_kernel_times(step, dev):
             out = fn(x, *a, **kw)
             e1.record()
             N, _, H, W = x.shape
-            rec[name].append((e0, e1, 2.0 * N * 64 * 64 * 9 * H * W))
+            variant = f"N={N} {H}x{W}" + "".join(f" +{k}" for k in ("mask_src", "res", "second") if kw.get(k) is not None
+                                                 and kw.get(k) is not False)
+            rec[name].append((e0, e1, 2.0 * N * 64 * 64 * 9 * H * W, variant))
             return out
         return inner
 
@@ -190,10 +192,16 @@ def conv_kernel_times(step, dev):
         K.conv3x3_c64, K.conv3x3_c64_wgrad = orig_f, orig_w
     out = {}
     for name, items in rec.items():
-        ms = sum(a.elapsed_time(b) for a, b, _ in items)
-        fl = sum(f for _, _, f in items)
+        ms = sum(a.elapsed_time(b) for a, b, *_ in items)
+        fl = sum(it[2] for it in items)
+        by = {}
+        for a, b, f, variant in items:
+            v = by.setdefault(variant, [0, 0.0, 0.0])
+            v[0] += 1; v[1] += a.elapsed_time(b); v[2] += f
         out[name] = {"launches": len(items), "ms_per_step": ms, "algorithmic_flops_per_step": fl,
-                     "tflops": fl / (ms * 1e-3) / 1e12 if ms > 0 else 0.0}
+                     "tflops": fl / (ms * 1e-3) / 1e12 if ms > 0 else 0.0,
+                     "by_variant": {k: {"launches": v[0], "ms": round(v[1], 3), "tflops": round(v[2] / (v[1] * 1e-3) / 1e12, 1)}
+                                    for k, v in sorted(by.items(), key=lambda kv: -kv[1][1])}}
     return out
 
 

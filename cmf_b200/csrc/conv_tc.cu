@@ -12,8 +12,8 @@
 //   channels, K = 9 taps x 64 inputs.
 //   * The pixel operand lives in TENSOR MEMORY.  Per (tile, 32-channel chunk) the producer warp
 //     (lane = channel) copies the tile's window of the stream -- the tile plus W+1 pixels either
-//     side -- into shared memory as [channel][pixel] with one bulk copy (cp.async.bulk) per
-//     channel and image touched.  A "row worker" thread owns one output pixel: for each of the 9
+//     side -- into shared memory as [channel][pixel] with 16-byte cp.async copies (a TMA box cannot
+//     put two images' pixels in one row).  A "row worker" thread owns one output pixel: for each of the 9
 //     taps it reads its 32 shifted inputs (or zero when the tap leaves ITS image: y + dy outside
 //     [0, H) or x + dx outside [0, W) -- so whatever the window holds beyond an image border is
 //     never used), splits them exactly into a TF32 head and a remainder (v = hi + lo) and writes
@@ -48,7 +48,8 @@ constexpr int kSeg = 1;                // stages per drained segment (K = 32)
 constexpr int kWRing = 4;
 constexpr int kWStageBytes = 2 * kC * kChunkC * 4;     // hi + lo tile: 16 KB
 constexpr int kMmaWarp1 = 2 + 4 * kTiles;              // second MMA issuer (tile 1)
-constexpr int kConvThreads = 32 * (3 + 4 * kTiles);    // 352
+constexpr int kHaloWarp = 3 + 4 * kTiles;               // halo-window loader
+constexpr int kConvThreads = 32 * (4 + 4 * kTiles);    // 384
 constexpr int kConvTmemCols = 512;
 constexpr int kMaxBox = 256;
 
@@ -118,6 +119,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
     __shared__ uint64_t w_full[kWRing], done[kWRing];     // done[gs % 4]: the MMAs of stage gs have completed for both tiles
     __shared__ uint64_t a_full[kTiles][2];
     __shared__ uint64_t at_full[kTiles][2];
+    __shared__ uint64_t halo_go;                           // producer -> halo warp: the next halo buffers are free
     __shared__ uint32_t tmem_base_smem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -137,9 +139,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
 
     if (threadIdx.x == 0) {
         for (int r = 0; r < kWRing; ++r) { mbar_init(&w_full[r], 1); mbar_init(&done[r], kTiles); }
+        mbar_init(&halo_go, 1);
         for (int t = 0; t < kTiles; ++t) {
             for (int c = 0; c < 2; ++c) {
-                mbar_init(&a_full[t][c], 1);
+                mbar_init(&a_full[t][c], 32);              // one cp.async arrival per producer lane
                 mbar_init(&at_full[t][c], kTileM / 32);     // one arrival per worker warp
             }
         }
@@ -156,58 +159,72 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
     constexpr uint32_t kAccCol = 0, kStgCol = 256;
 
     if (warp == 0) {
-        // ------------------------------------------------------------------ TMA producer
-        // The whole warp walks the stage loop converged: lane 0 streams the weights; the halo
-        // windows are fetched by all 32 lanes, lane = channel of the chunk.  Column j of a window
-        // row is pixel g0 - hl + j of the packed stream; the stream is contiguous in memory only
-        // inside one image, so each lane issues one bulk copy per image the window touches
-        // (starts and lengths are multiples of 4 pixels because H*W, hl and 128 are).
-        auto load_halo = [&](int it, int c) {
-#pragma unroll
-            for (int t = 0; t < kTiles; ++t) {
-                bool act; long long g0;
-                tile_of(it, t, act, g0);
-                if (!act) continue;
-                const long long ws = g0 - P.hl;
-                long long lo = ws < 0 ? 0 : ws;
-                long long hi = ws + P.win;
-                if (hi > P.total_px) hi = P.total_px;
-                if (lane == 0) mbar_arrive_expect_tx(&a_full[t][c], (uint32_t)((hi - lo) * 4 * kChunkC));
-                __syncwarp();
-                const uint32_t dst_row = smem_u32(halo + (size_t)(t * 2 + c) * kHaloElems + (size_t)lane * kPitch);
-                const uint32_t bar = smem_u32(&a_full[t][c]);
-                const long long hw = P.HW;
-                for (long long im = lo / hw; lo < hi; ++im) {
-                    long long end = (im + 1) * hw;
-                    if (end > hi) end = hi;
-                    const float* src = P.x + ((im * kC + c * kChunkC + lane) * hw + (lo - im * hw));
-                    asm volatile(
-                        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
-                            "r"(dst_row + (uint32_t)((lo - ws) * 4)), "l"(src), "r"((uint32_t)((end - lo) * 4)), "r"(bar)
-                        : "memory");
-                    lo = end;
-                }
-            }
-        };
-        load_halo(0, 0);
-        int gs = 0;
-        for (int it = 0; it < nit; ++it) {
-            for (int s = 0; s < kStages; ++s, ++gs) {
-                const int r = gs % kWRing;
-                if (gs >= kWRing) mbar_wait(&done[r], ((gs / kWRing) - 1) & 1);      // stage gs - 4 has completed
-                if (lane == 0) {
+        // ------------------------------------------------------------------ weight producer (TMA)
+        if (lane == 0) {
+            int gs = 0;
+            for (int it = 0; it < nit; ++it) {
+                for (int s = 0; s < kStages; ++s, ++gs) {
+                    const int r = gs % kWRing;
+                    if (gs >= kWRing) mbar_wait(&done[r], ((gs / kWRing) - 1) & 1);      // stage gs - 4 has completed
                     const int chunk = s / kTaps, tap = s % kTaps;
                     uint8_t* dst = wring + (size_t)r * kWStageBytes;
                     mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
                     tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
                     tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
+                    // halo buffers are recycled as soon as every worker is past their last read:
+                    // chunk 1 of this pair once stage 0 of this pair has completed (s = 4 waited for it),
+                    // chunk 0 of the next pair once stage 9 has completed (s = 13 waited for it).  The
+                    // halo warp is told; it cannot fall more than one phase behind, because the next
+                    // signal needs a stage that consumes the data of this one.
+                    if (s == 4 || (s == 13 && it + 1 < nit)) mbar_arrive(&halo_go);
                 }
-                // halo buffers are recycled as soon as every worker is past their last read:
-                // chunk 1 of this pair once stage 0 of this pair has completed (s = 4 waited for it),
-                // chunk 0 of the next pair once stage 9 has completed (s = 13 waited for it)
-                if (s == 4) load_halo(it, 1);
-                if (s == 13 && it + 1 < nit) load_halo(it + 1, 0);
-                __syncwarp();
+            }
+        }
+    } else if (warp == kHaloWarp) {
+        // ------------------------------------------------------------------ halo-window loader
+        // All 32 lanes fetch the windows with 16-byte cp.async copies (LDGSTS).  Column j of a window
+        // row is pixel g0 - hl + j of the packed stream, which is contiguous in memory only inside
+        // one image: a lane owns the 4-pixel columns {lane, lane + 32} of the window, resolves their
+        // (image, pixel) once and walks the 32 channel rows of the chunk -- consecutive lanes copy
+        // consecutive 16 bytes of a row.  (One TMA box cannot place two images' pixels in one row;
+        // one-row bulk copies cost ~0.25 ms per launch, and issuing the copies from the weight
+        // producer holds up the weight stream: both measured.)  Completion is signalled per lane
+        // with cp.async.mbarrier.arrive.noinc (a_full counts 32).
+        auto load_halo = [&](int it, int c, int t) {
+            bool act; long long g0;
+            tile_of(it, t, act, g0);
+            if (!act) return;
+            const long long ws = g0 - P.hl;
+            const uint32_t dst_buf = smem_u32(halo + (size_t)(t * 2 + c) * kHaloElems);
+            const long long hw = P.HW;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int col = 4 * (lane + 32 * h);
+                const long long sp = ws + col;
+                if (col < P.win && sp >= 0 && sp < P.total_px) {
+                    const long long im = sp / hw;
+                    const float* src = P.x + ((im * kC + c * kChunkC) * hw + (sp - im * hw));
+                    const uint32_t dst = dst_buf + (uint32_t)(col * 4);
+#pragma unroll 8
+                    for (int r = 0; r < kChunkC; ++r)
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)(r * kPitch * 4)),
+                                     "l"(src + (long long)r * hw)
+                                     : "memory");
+                }
+            }
+            asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&a_full[t][c])) : "memory");
+        };
+        load_halo(0, 0, 0);
+        load_halo(0, 0, 1);
+        int k = 0;
+        for (int it = 0; it < nit; ++it) {
+            mbar_wait(&halo_go, k & 1); ++k;
+            load_halo(it, 1, 0);
+            load_halo(it, 1, 1);
+            if (it + 1 < nit) {
+                mbar_wait(&halo_go, k & 1); ++k;
+                load_halo(it + 1, 0, 0);
+                load_halo(it + 1, 0, 1);
             }
         }
     } else if (warp == 1 || warp == kMmaWarp1) {
