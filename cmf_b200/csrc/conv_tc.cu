@@ -77,6 +77,7 @@ struct ConvParams {
     // fused epilogue:  t = acc + bias;  if (mask_first) t *= m;  if (res) t += res;  y = t;
     //                  if (y2) y2 = t * m      with m = mask_src[n / mask_div, co, p] > 0
     const float* mask_src;             // (N / mask_div, 64, H, W) pre-ReLU primal activations, or null
+    const uint2* mask_bits;            // (N / mask_div, H*W) packed signs of the same (cmf_relu_mask_pack), or null
     int mask_div;
     int mask_first;
     const float* res;                  // (N, 64, H, W) or null
@@ -101,6 +102,23 @@ __global__ void conv_prep_kernel(const float* __restrict__ w, int transpose, flo
     const float lo = v - hi;
     out[i] = hi;
     out[kTaps * kC * kC + i] = lo;
+}
+
+// bits[n, p] = {bit e: x[n, e, p] > 0 (channels 0..31), bit e: x[n, 32 + e, p] > 0}: the relu-JVP mask of
+// a primal activation, packed once and reused by the d tangent images of the sample in the forward
+// and the backward launches (64 strided loads per output pixel become one 8-byte load)
+__global__ void relu_mask_pack_kernel(long long total, int hw, const float* __restrict__ x, uint2* __restrict__ bits) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;      // = n * hw + p
+    if (i >= total) return;
+    const long long n = i / hw;
+    const float* src = x + (n * kC) * hw + (i - n * hw);
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+        lo |= (__ldg(src + (long long)e * hw) > 0.f ? 1u : 0u) << e;
+        hi |= (__ldg(src + (long long)(32 + e) * hw) > 0.f ? 1u : 0u) << e;
+    }
+    bits[i] = make_uint2(lo, hi);
 }
 
 // kPitch = pixels per halo row in shared memory = TMA box width (compile-time so that the 32
@@ -357,7 +375,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             }
             if (valid) {
                 const long long o = (long long)im * kC * hw + p;
-                if (!P.mask_src && !P.res) {
+                if (!P.mask_src && !P.mask_bits && !P.res) {
 #pragma unroll
                     for (int j = 0; j < kC; ++j) P.y[o + (long long)j * hw] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
                 } else {
@@ -370,7 +388,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     // overlap (the compiler cannot hoist loads over possibly aliasing stores): first all 64
                     // mask values, packed into two words, then the skip connection 32 channels at a time
                     uint32_t keep_bits[2] = {0xffffffffu, 0xffffffffu};
-                    if (ms) {
+                    if (P.mask_bits) {       // one 8-byte load instead of 64 strided ones
+                        const uint2 mb = __ldg(P.mask_bits + (long long)(im / P.mask_div) * hw + p);
+                        keep_bits[0] = mb.x;
+                        keep_bits[1] = mb.y;
+                    } else if (ms) {
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
                             float mv[32];
@@ -431,9 +453,9 @@ extern "C" int cmf_conv3x3_c64_usable(int N, int H, int W) {
     return (HW % 4 == 0) && need <= kMaxBox && (long long)N * kC < (1LL << 31) && HW < (1LL << 24);
 }
 
-extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
-                                     const float* mask_src, int mask_div, int mask_first, const float* res,
-                                     float* y, float* y2, cmf_stream_t stream) {
+static int conv_launch(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                       const float* mask_src, const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
+                       float* y, float* y2, cmf_stream_t stream) {
     CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3: negative size");
     if (N == 0 || H == 0 || W == 0) return 0;
     CMF_REQUIRE(x && wsplit && y, "conv3x3: null pointer");
@@ -445,10 +467,13 @@ extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const 
     P.total_tiles = ceil_div(P.total_px, (long long)kTileM);
     P.x = x;
     P.hl = (W + 4) & ~3;
-    CMF_REQUIRE(!mask_src || (mask_div >= 1 && N % mask_div == 0), "conv3x3: mask_div must divide N");
-    CMF_REQUIRE(!y2 || mask_src, "conv3x3: second output needs a mask source");
+    const bool masked = mask_src || mask_bits;
+    CMF_REQUIRE(!masked || (mask_div >= 1 && N % mask_div == 0), "conv3x3: mask_div must divide N");
+    CMF_REQUIRE(!y2 || masked, "conv3x3: second output needs a mask source");
+    CMF_REQUIRE(!mask_bits || (reinterpret_cast<uintptr_t>(mask_bits) & 7u) == 0, "conv3x3: mask_bits must be 8-byte aligned");
     P.bias = bias; P.y = y; P.y2 = y2;
-    P.mask_src = mask_src; P.mask_div = mask_src ? mask_div : 1; P.mask_first = mask_first; P.res = res;
+    P.mask_src = mask_bits ? nullptr : mask_src; P.mask_bits = reinterpret_cast<const uint2*>(mask_bits);
+    P.mask_div = masked ? mask_div : 1; P.mask_first = mask_first; P.res = res;
     P.win = (kTileM + P.hl + W + 1 + 3) & ~3;
     const int pitch = P.win <= 192 ? 192 : 256;
     CUtensorMap tmw;
@@ -480,6 +505,29 @@ extern "C" int cmf_debug_conv_prof(long long* host_out) {
     return (int)cudaMemcpyFromSymbol(host_out, g_conv_prof, sizeof(long long) * 128);
 }
 #endif
+
+extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                                     const float* mask_src, int mask_div, int mask_first, const float* res,
+                                     float* y, float* y2, cmf_stream_t stream) {
+    return conv_launch(N, H, W, x, wsplit, bias, mask_src, nullptr, mask_div, mask_first, res, y, y2, stream);
+}
+
+extern "C" int cmf_conv3x3_c64_fused_bits(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                                          const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
+                                          float* y, float* y2, cmf_stream_t stream) {
+    return conv_launch(N, H, W, x, wsplit, bias, nullptr, mask_bits, mask_div, mask_first, res, y, y2, stream);
+}
+
+extern "C" int cmf_relu_mask_pack(int N, int HW, const float* x, uint32_t* bits, cmf_stream_t stream) {
+    CMF_REQUIRE(N >= 0 && HW >= 0, "relu_mask_pack: negative size");
+    if (N == 0 || HW == 0) return 0;
+    CMF_REQUIRE(x && bits, "relu_mask_pack: null pointer");
+    CMF_REQUIRE((reinterpret_cast<uintptr_t>(bits) & 7u) == 0, "relu_mask_pack: bits must be 8-byte aligned");
+    const long long total = (long long)N * HW;
+    relu_mask_pack_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(total, HW, x, reinterpret_cast<uint2*>(bits));
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
 
 extern "C" int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                                    float* y, cmf_stream_t stream) {

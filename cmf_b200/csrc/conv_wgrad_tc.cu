@@ -347,8 +347,24 @@ __global__ void conv_wgrad_reduce_kernel(const float* __restrict__ partial, int 
 int wgrad_plan(int N, int H, int W, int* tiles_per_cta, long long* grid) {
     const long long HW = (long long)H * W;
     const long long tpi = ceil_div(HW, kTileM), total = (long long)N * tpi;
-    long long T = 14;                                   // two 28x28 images: <= 672 truncating MMAs per accumulator
-    if (ceil_div(total, T) < 148) T = ceil_div(total, 148);
+    // T tiles per CTA.  Bound: <= 672 truncating MMAs per accumulator (12 per live sub-chunk), i.e.
+    // T * (live sub-chunks per tile, averaged over an image) <= 56 -- 14 tiles of a 28x28 image, 16 of
+    // a 14x14 one.  One CTA per SM is resident, so the launch costs waves * T tile-times: pick the T
+    // that minimises it (14x14, N = 3200: T = 14 needs 458 CTAs = 4 waves, T = 15 needs 427 = 3).
+    const long long sub_per_image = ceil_div(HW, 32);
+    long long tmax = 56 * tpi / sub_per_image;
+    if (tmax > 16) tmax = 16;
+    if (tmax < 1) tmax = 1;
+    long long T = tmax, best = -1;
+    if (ceil_div(total, tmax) < kNumSMs) {
+        T = ceil_div(total, kNumSMs);                   // small problem: spread over the SMs
+    } else {
+        for (long long t = tmax; t >= (tmax + 1) / 2; --t) {
+            // + 1: a CTA's fixed cost (prologue, 147 KB partial written and re-read by the reduction)
+            const long long cost = ceil_div(ceil_div(total, t), kNumSMs) * (t + 1);
+            if (best < 0 || cost < best) { best = cost; T = t; }
+        }
+    }
     if (T < 1) T = 1;
     *tiles_per_cta = (int)T;
     *grid = ceil_div(total, T);

@@ -225,11 +225,26 @@ def conv3x3_c64_prep(weight: Tensor, transpose: bool) -> Tensor:
     return out
 
 
+def relu_mask_pack(x: Tensor) -> Tensor:
+    """x (N,64,H,W) primal activations -> packed signs (N, H*W, 2) int32 for ``conv3x3_c64(mask_src=...)``:
+    bit e of word 0 / 1 = (x[n, e, p] > 0) / (x[n, 32 + e, p] > 0)."""
+    lib = _lib.load()
+    x = _req(x, "x")
+    N, C, H, W = x.shape
+    assert C == 64
+    bits = torch.empty(N, H * W, 2, dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_relu_mask_pack(N, H * W, _ptr(x), _ptr(bits), _stream()), "cmf_relu_mask_pack")
+    return bits
+
+
 def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_src: Optional[Tensor] = None,
                 mask_div: int = 1, mask_first: bool = False, res: Optional[Tensor] = None, second: bool = False):
     """x (N,64,H,W), wsplit from ``conv3x3_c64_prep`` -> y (N,64,H,W), with the fused epilogue of
     ``cmf_conv3x3_c64_fused``:  t = conv(x) + bias; if mask_first: t *= m; if res: t += res; y = t;
-    ``second`` additionally returns y2 = t * m  (m = mask_src[n // mask_div] > 0)."""
+    ``second`` additionally returns y2 = t * m  (m = mask_src[n // mask_div] > 0).  ``mask_src`` is
+    either the float activations (N // mask_div, 64, H, W) or their packed signs from
+    ``relu_mask_pack`` (int32, (N // mask_div, H*W, 2))."""
     lib = _lib.load()
     x, wsplit = _req(x, "x"), _req(wsplit, "wsplit")
     N, C, H, W = x.shape
@@ -237,7 +252,11 @@ def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_s
     if bias is not None:
         bias = _req(bias, "bias")
         assert bias.numel() == 64
-    if mask_src is not None:
+    packed = mask_src is not None and mask_src.dtype == torch.int32
+    if packed:
+        assert mask_src.is_cuda and mask_src.is_contiguous()
+        assert N % mask_div == 0 and tuple(mask_src.shape) == (N // mask_div, H * W, 2), (mask_src.shape, x.shape, mask_div)
+    elif mask_src is not None:
         mask_src = _req(mask_src, "mask_src")
         assert N % mask_div == 0 and tuple(mask_src.shape) == (N // mask_div, 64, H, W), (mask_src.shape, x.shape, mask_div)
     if res is not None:
@@ -247,8 +266,9 @@ def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_s
     y = torch.empty_like(x)
     y2 = torch.empty_like(x) if second else None
     with torch.cuda.device(x.device):
-        _lib.check(lib.cmf_conv3x3_c64_fused(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src), int(mask_div),
-                                             int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2), _stream()),
+        fn = lib.cmf_conv3x3_c64_fused_bits if packed else lib.cmf_conv3x3_c64_fused
+        _lib.check(fn(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src), int(mask_div),
+                      int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2), _stream()),
                    "cmf_conv3x3_c64_fused")
     return (y, y2) if second else y
 

@@ -116,10 +116,13 @@ class _ResidualStackTangent(torch.autograd.Function):
     def forward(ctx, V, d, *tensors):
         from . import kernels
         K = len(tensors) // 4
-        xs, h1s = tensors[0::4], tensors[1::4]
         w1s, w2s = tensors[2::4], tensors[3::4]
         S = V.contiguous()
-        A0 = _mask_rows(S, xs[0] > 0, d)
+        A0 = _mask_rows(S, tensors[0] > 0, d)
+        # the relu-JVP masks as packed sign bits (one 8-byte word per pixel): read by the epilogues of
+        # the forward and the backward launches, and 32x smaller to keep for the backward
+        xs = [kernels.relu_mask_pack(t) for t in tensors[0::4]]
+        h1s = [kernels.relu_mask_pack(t) for t in tensors[1::4]]
         saved = []
         for k in range(K):
             A1 = kernels.conv3x3_c64(A0, kernels.conv3x3_c64_prep(w1s[k], False), None, mask_src=h1s[k], mask_div=d,

@@ -139,6 +139,15 @@ int cmf_conv3x3_c64_fwd(int N, int H, int W, const float* x, const float* wsplit
 int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                           const float* mask_src, int mask_div, int mask_first, const float* res,
                           float* y, float* y2, cmf_stream_t stream);
+/* The same with the mask given as packed sign bits: cmf_relu_mask_pack turns the primal activations
+ * x (N, 64, HW) into bits (N, HW, 2) uint32 -- bit e of word 0 / word 1 = (x[n, e, p] > 0) /
+ * (x[n, 32 + e, p] > 0), 8-byte aligned -- once per residual block; the d tangent images of a
+ * sample then read ONE 8-byte word per output pixel instead of 64 strided floats, in the forward
+ * and in the backward launches. */
+int cmf_relu_mask_pack(int N, int HW, const float* x, uint32_t* bits, cmf_stream_t stream);
+int cmf_conv3x3_c64_fused_bits(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
+                               const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
+                               float* y, float* y2, cmf_stream_t stream);
 
 /* Weight gradient of the same convolution: g_w (64,64,3,3) (+)= sum_{n,p} g_y[n,co,p] x[n,ci,p+tap]
  * (what autograd derives for F.conv2d at cmf/trainer.py:216, aten::convolution_backward).

@@ -103,11 +103,28 @@ def conv3x3_c64_prep(weight, transpose):
     return (weight.flip(2, 3).transpose(0, 1) if transpose else weight).contiguous()
 
 
+def relu_mask_pack(x):
+    """(N,64,H,W) -> (N, H*W, 2) int32, bit e of word h = x[n, 32 h + e, p] > 0"""
+    N, C, H, W = x.shape
+    pos = (x > 0).flatten(2).view(N, 2, 32, H * W).to(torch.int64)                 # (N, word, bit, p)
+    words = (pos << torch.arange(32, device=x.device).view(1, 1, 32, 1)).sum(2)      # (N, 2, p), 0 .. 2^32-1
+    words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)
+    return words.transpose(1, 2).contiguous().to(torch.int32)
+
+
+def _unpack_mask(bits, H, W):
+    N = bits.shape[0]
+    w = bits.to(torch.int64) & 0xFFFFFFFF                                            # (N, p, 2)
+    b = (w.unsqueeze(-1) >> torch.arange(32, device=bits.device)) & 1                # (N, p, 2, 32)
+    return b.permute(0, 2, 3, 1).reshape(N, 64, H, W).bool()
+
+
 def conv3x3_c64(x, wsplit, bias=None, mask_src=None, mask_div=1, mask_first=False, res=None, second=False):
     t = torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
     m = None
     if mask_src is not None:
-        m = (mask_src > 0).to(t.dtype).repeat_interleave(mask_div, dim=0)
+        keep = _unpack_mask(mask_src, *x.shape[2:]) if mask_src.dtype == torch.int32 else mask_src > 0
+        m = keep.to(t.dtype).repeat_interleave(mask_div, dim=0)
     if mask_first:
         t = t * m
     if res is not None:
@@ -126,5 +143,5 @@ def conv3x3_c64_wgrad(x, g_y):
 
 
 ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_bwd",
-       "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64",
+       "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

@@ -134,6 +134,27 @@ def test_fused_epilogue(N, H, W, d, mode):
         assert torch.equal(g_ == 0, r_ == 0) or mode == "res"      # masked entries are exact zeros
 
 
+@pytest.mark.parametrize("N,H,W,d", [(6, 14, 14, 3), (4, 28, 28, 2), (130, 14, 14, 65), (9, 6, 10, 3)])
+def test_packed_relu_mask_is_the_same_mask(N, H, W, d):
+    """cmf_relu_mask_pack + cmf_conv3x3_c64_fused_bits: bit-identical outputs to the float-mask epilogue
+    (zeros and negative zeros of the primal count as masked in both)"""
+    import emu_kernels as E
+    x, w = _rand((N, 64, H, W), 50), _rand((64, 64, 3, 3), 51, 1 / 24)
+    prim, res = _rand((N // d, 64, H, W), 52), _rand((N, 64, H, W), 53)
+    prim[0, :, 0, :2] = 0.0
+    prim[0, 5, 1, 1] = -0.0
+    bits = K.relu_mask_pack(prim)
+    assert bits.dtype == torch.int32 and tuple(bits.shape) == (N // d, H * W, 2)
+    assert torch.equal(bits.cpu(), E.relu_mask_pack(prim.cpu()))
+    ws = K.conv3x3_c64_prep(w, False)
+    for kw in (dict(mask_first=True), dict(res=res, second=True), dict(mask_first=True, res=res)):
+        a = K.conv3x3_c64(x, ws, None, mask_src=prim, mask_div=d, **kw)
+        b = K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=d, **kw)
+        a, b = (a, b) if isinstance(a, tuple) else ((a,), (b,))
+        for u, v in zip(a, b):
+            assert torch.equal(u, v)
+
+
 def test_residual_stack_tangent_matches_autograd():
     """the fused tangent node of a residual-block run vs the per-op autograd path (library convs)"""
     from cmf_b200 import networks as NW
