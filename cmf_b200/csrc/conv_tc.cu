@@ -44,7 +44,6 @@ constexpr int kTiles = 2;              // tiles per CTA sharing one weight strea
 constexpr int kChunkC = 32;            // input channels per stage (K = 32)
 constexpr int kTaps = 9;
 constexpr int kStages = 2 * kTaps;     // per tile: 2 channel chunks x 9 taps
-constexpr int kSeg = 1;                // stages per drained segment (K = 32)
 constexpr int kWRing = 4;
 constexpr int kWStageBytes = 2 * kC * kChunkC * 4;     // hi + lo tile: 16 KB
 constexpr int kMmaWarp1 = 2 + 4 * kTiles;              // second MMA issuer (tile 1)
@@ -130,7 +129,9 @@ __global__ void relu_mask_pack_kernel(long long total, int hw, const float* __re
 // the next pair is fetched while the current one is still being consumed (chunk 0 after stage 9 has
 // completed, chunk 1 after stage 0 of the next pair).  Launch, TMEM allocation, barrier set-up and
 // the first TMA round trip (a third of a one-pair CTA's life) are paid once per SM.
-template <int kPitch>
+// kSeg = stages (K = 32 each) accumulated on the tensor core between two drains of the accumulator
+// into the FP32 registers; kStages % kSeg == 0, so segments never straddle tile pairs.
+template <int kPitch, int kSeg>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -263,10 +264,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 const int b = gs & 1;
                 mbar_wait(&w_full[r], (gs / kWRing) & 1);
                 if (act) mbar_wait(&at_full[t][b], (gs >> 1) & 1);
-                // accumulator (gs & 1) was drained (stage gs-2) by every worker warp BEFORE it arrived on
+                // accumulator (segment gs / kSeg, parity) was drained (two segments ago) by every worker warp BEFORE it arrived on
                 // at_full for this stage (program order + tcgen05.wait::ld), so no extra barrier is needed
                 tc_fence_after();
-                const uint32_t acc = acc0 + (uint32_t)((gs & 1) * kC);
+                const uint32_t acc = acc0 + (uint32_t)(((gs / kSeg) & 1) * kC);
+                const uint32_t fresh = (gs % kSeg) == 0 ? 0u : 1u;      // 0: first stage of a segment overwrites
                 if (elect_one()) {
                     if (act) {
                         const uint64_t dbh = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes));
@@ -278,7 +280,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                         // see a large accumulator
 #pragma unroll
                         for (int k = 0; k < kChunkC / 8; ++k) {      // +32 bytes along K = +2 in the descriptor's address field
-                            umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, k != 0);
+                            umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, (k != 0) | fresh);
                             umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
                         }
 #pragma unroll
@@ -334,11 +336,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
 #pragma unroll
                 for (int c = 0; c < kChunkC; ++c) v[c] = ok ? ld_shared_f32(src + (uint32_t)(c * kPitch * 4)) : 0.f;
             };
-            // drain the accumulator of global stage e into the FP32 registers
+            // drain the accumulator of the segment that ended with global stage e into the FP32 registers
             auto drain = [&](int e) {
                 mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
                 tc_fence_after();
-                const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + (e & 1)) * kC) + lane_addr;
+                const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + ((e / kSeg) & 1)) * kC) + lane_addr;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     float u[32];
@@ -370,7 +372,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 if (lane == 0) mbar_arrive(&at_full[t][b]);
                 // drain one stage late (the last one at its own stage), so the tensor pipe already works
                 // on the next stage in the other accumulator
-                if (s > 0) drain(gs - 1);
+                if (s > 0 && (gs % kSeg) == 0) drain(gs - 1);
                 if (s == kStages - 1) drain(gs);
             }
             if (valid) {
@@ -480,22 +482,27 @@ static int conv_launch(int N, int H, int W, const float* x, const float* wsplit,
     int rc = make_tmap_2d_f32(&tmw, wsplit, (uint64_t)2 * kTaps * kC, (uint64_t)kC, (uint64_t)kC, kC, 0);
     if (rc != 0) return rc;
     const size_t smem = (size_t)kWRing * kWStageBytes + (size_t)kTiles * 2 * kChunkC * pitch * 4 + 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv3x3_tc_kernel<192>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(conv3x3_tc_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e != cudaSuccess) { set_error("conv3x3 attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
-    }
     // persistent: one CTA per SM walks the tile pairs
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const long long npairs = ceil_div(P.total_tiles, kTiles);
     const unsigned grid = (unsigned)(npairs < sms ? npairs : sms);
-    if (pitch == 192) conv3x3_tc_kernel<192><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);
-    else conv3x3_tc_kernel<256><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);
+    static int seg = 0;
+    if (seg == 0) { const char* e = getenv("CMF_CONV_SEG"); seg = e ? atoi(e) : 1; if (seg < 1 || seg > 3) seg = 1; }
+#define CMF_CONV_LAUNCH(PITCH, SEG)                                                                                   \
+    do {                                                                                                               \
+        static bool attr_set = false;                                                                                  \
+        if (!attr_set) {                                                                                               \
+            cudaError_t e = cudaFuncSetAttribute(conv3x3_tc_kernel<PITCH, SEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
+            if (e != cudaSuccess) { set_error("conv3x3 attr: %s", cudaGetErrorString(e)); return (int)e; }           \
+            attr_set = true;                                                                                           \
+        }                                                                                                              \
+        conv3x3_tc_kernel<PITCH, SEG><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);                     \
+    } while (0)
+    if (pitch == 192) { if (seg == 1) CMF_CONV_LAUNCH(192, 1); else if (seg == 2) CMF_CONV_LAUNCH(192, 2); else CMF_CONV_LAUNCH(192, 3); }
+    else { if (seg == 1) CMF_CONV_LAUNCH(256, 1); else if (seg == 2) CMF_CONV_LAUNCH(256, 2); else CMF_CONV_LAUNCH(256, 3); }
+#undef CMF_CONV_LAUNCH
     CMF_CHECK_LAUNCH();
     return 0;
 }

@@ -1,3 +1,5 @@
 export PYTHONPATH=.
-timeout -k 10 300 python -m pytest tests/test_conv_gpu.py -x -q -m gpu 2>&1 | tail -3
-for d in 0 1; do echo "== CMF_CONV_DBG=$d"; CMF_CONV_DBG=$d timeout -k 5 120 python scripts/conv_check.py --bench 2>&1 | grep "tc  "; done
+timeout 100 python scripts/_one_conv.py || exit 1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv3x3_tc_kernel -s 2 -c 1 -f -o gpurun_out/r01d_conv_fwd python scripts/_one_conv.py > gpurun_out/ncu_fwd.log 2>&1
+tail -3 gpurun_out/ncu_fwd.log
+ls -la gpurun_out/*.ncu-rep
