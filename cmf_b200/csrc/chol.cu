@@ -20,6 +20,7 @@ namespace cmf {
 
 constexpr int kCholThreads = 128;
 constexpr int kCholMaxD = 128;
+constexpr int kCholWideMinD = 32;     // from here up: one sample per CTA (chol_wide_*)
 
 __device__ __forceinline__ float group_sum(float v, float* red, int tps, int lane) {
     // sum over the tps threads of one sample; red points at this sample's tps-float scratch
@@ -164,6 +165,343 @@ chol_logdet_bwd_kernel(int B, int d, int tps, const float* __restrict__ L, const
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// 32 <= d <= 128 (the image configs: d = 64 MNIST-shape, 64..128 CIFAR-shape): one sample per CTA.
+// Same left-looking algorithm and the same contract as above, restructured for latency: rows are
+// padded to ld floats with ld % 4 == 0 and ld / 4 odd, so a thread reads ITS row (and, broadcast,
+// the pivot row) with conflict-free 128-bit loads and the dot products run on four independent FMA
+// chains -- the scalar version above is bound by one LDS latency per FMA.  B = 512, d = 64:
+// forward 79 -> see profiles; backward: W = L^-1 by columns (128-bit loads of the L row), then
+// G^-1 = W^T W as a 4x4 register-tiled product over all 256 threads instead of one column per thread.
+// ---------------------------------------------------------------------------------------------
+constexpr int kWideFwdThreads = 256;
+constexpr int kWideBwdThreads = 256;
+
+__host__ __device__ inline int wide_ld(int d) {
+    int ld = (d + 3) & ~3;
+    if (((ld >> 2) & 1) == 0) ld += 4;
+    return ld;
+}
+
+__device__ __forceinline__ float block_sum(float v, float* red) {     // red: >= 8 floats; all threads call
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[w] = v;
+    __syncthreads();
+    float s = 0.f;
+    for (int i = 0; i < nw; ++i) s += red[i];
+    return s;
+}
+
+// tpr = threads per row (a power of two <= 8, d * tpr <= 256): the tpr lanes of a row split the
+// 128-bit chunks of the two dot products and combine them with xor shuffles, so a column step is
+// one short chain (load, <= 2 FMAs deep per 16 columns, two shuffles, rsqrt, multiply, store,
+// barrier) instead of k dependent iterations.  L grows in a zero-initialised buffer of its own:
+// chunks may then run past column k (the tail multiplies zeros) and need no scalar remainder.
+__device__ __forceinline__ float rsqrt_nr(float x) {       // 1 / sqrt(x) to ~1 ulp
+    const float r = rsqrtf(x);
+    return r * fmaf(-0.5f * x * r, r, 1.5f);
+}
+
+__global__ void __launch_bounds__(kWideFwdThreads)
+chol_wide_fwd_kernel(int d, int ld, int tpr, int vec, const float* __restrict__ G, float* __restrict__ L,
+                     float* __restrict__ logdet, float* __restrict__ l1_off, float* __restrict__ l1_diag,
+                     int32_t* __restrict__ info) {
+    extern __shared__ __align__(16) float smem[];
+    float* Gs = smem;                          // [d][ld]  the input
+    float* Lz = smem + (size_t)d * ld;         // [d][ld]  the factor, zero where not (yet) written
+    float* red = Lz + (size_t)d * ld;          // [8]
+    __shared__ int failed;
+    const int b = blockIdx.x, t = threadIdx.x;
+    const int i = t / tpr, sub = t - i * tpr;
+    const float* Gb = G + (size_t)b * d * d;
+    float off = 0.f, dia = 0.f;
+    if (t == 0) failed = 0;
+    for (int e = t; e < d * ld; e += kWideFwdThreads) Lz[e] = 0.f;
+    if (vec) {
+        const int d4 = d >> 2;
+        for (int e = t; e < d * d4; e += kWideFwdThreads) {
+            const int r = e / d4, c = (e - r * d4) << 2;
+            const float4 g = ldg4(Gb + (size_t)r * d + c);
+            *reinterpret_cast<float4*>(Gs + r * ld + c) = g;
+            const float a[4] = {fabsf(g.x), fabsf(g.y), fabsf(g.z), fabsf(g.w)};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { if (c + q == r) dia += a[q]; else off += a[q]; }
+        }
+    } else {
+        for (int e = t; e < d * d; e += kWideFwdThreads) {
+            const int r = e / d, c = e - r * d;
+            const float g = __ldg(Gb + e);
+            Gs[r * ld + c] = g;
+            if (r == c) dia += fabsf(g); else off += fabsf(g);
+        }
+    }
+    __syncthreads();
+
+    bool ok = true;
+    float mylog = 0.f, mypiv = 0.f;
+    const float4* ri4 = reinterpret_cast<const float4*>(Lz + (size_t)(i < d ? i : 0) * ld);
+    for (int k = 0; k < d; ++k) {
+        const bool active = ok && i >= k && i < d;
+        float dot = 0.f, p = 0.f;
+        if (active) {
+            const float4* rk4 = reinterpret_cast<const float4*>(Lz + (size_t)k * ld);
+            const int nq = (k + 3) >> 2;
+            float d1 = 0.f, p1 = 0.f;
+            int q = sub;
+            for (; q + tpr < nq; q += 2 * tpr) {
+                const float4 a = ri4[q], c = rk4[q], a2 = ri4[q + tpr], c2 = rk4[q + tpr];
+                dot = fmaf(a.x, c.x, dot); dot = fmaf(a.y, c.y, dot); dot = fmaf(a.z, c.z, dot); dot = fmaf(a.w, c.w, dot);
+                p = fmaf(c.x, c.x, p); p = fmaf(c.y, c.y, p); p = fmaf(c.z, c.z, p); p = fmaf(c.w, c.w, p);
+                d1 = fmaf(a2.x, c2.x, d1); d1 = fmaf(a2.y, c2.y, d1); d1 = fmaf(a2.z, c2.z, d1); d1 = fmaf(a2.w, c2.w, d1);
+                p1 = fmaf(c2.x, c2.x, p1); p1 = fmaf(c2.y, c2.y, p1); p1 = fmaf(c2.z, c2.z, p1); p1 = fmaf(c2.w, c2.w, p1);
+            }
+            if (q < nq) {
+                const float4 a = ri4[q], c = rk4[q];
+                dot = fmaf(a.x, c.x, dot); dot = fmaf(a.y, c.y, dot); dot = fmaf(a.z, c.z, dot); dot = fmaf(a.w, c.w, dot);
+                p = fmaf(c.x, c.x, p); p = fmaf(c.y, c.y, p); p = fmaf(c.z, c.z, p); p = fmaf(c.w, c.w, p);
+            }
+            dot += d1; p += p1;
+        }
+        for (int o = tpr >> 1; o > 0; o >>= 1) {            // the tpr lanes of a row are adjacent in one warp
+            dot += __shfl_xor_sync(0xffffffffu, dot, o);
+            p += __shfl_xor_sync(0xffffffffu, p, o);
+        }
+        if (active) {
+            const float piv2 = Gs[k * ld + k] - p;
+            if (!(piv2 > 0.f)) {               // not positive definite (or NaN): torch raises here
+                ok = false;
+                if (i == k && sub == 0) { failed = 1; atomicMax(info, b + 1); }
+            } else if (sub == 0) {
+                const float rs = rsqrt_nr(piv2);
+                if (i == k) { mypiv = piv2 * rs; mylog = 0.5f * logf(piv2); }
+                else Lz[i * ld + k] = (Gs[i * ld + k] - dot) * rs;
+            }
+        }
+        __syncthreads();
+        // the diagonal is committed only now: chunks read during step k must see L[k][k] as zero
+        if (active && ok && i == k && sub == 0) Lz[k * ld + k] = mypiv;
+    }
+    const float ld_sum = block_sum(mylog, red);
+    const float off_sum = block_sum(off, red);
+    const float dia_sum = block_sum(dia, red);
+    if (t == 0) {
+        logdet[b] = failed ? nanf("") : 2.f * ld_sum;
+        l1_off[b] = off_sum;
+        l1_diag[b] = dia_sum;
+    }
+    float* Lb = L + (size_t)b * d * d;
+    if (vec) {
+        const int d4 = d >> 2;
+        for (int e = t; e < d * d4; e += kWideFwdThreads) {
+            const int r = e / d4, c = (e - r * d4) << 2;
+            *reinterpret_cast<float4*>(Lb + (size_t)r * d + c) = *reinterpret_cast<const float4*>(Lz + r * ld + c);
+        }
+    } else {
+        for (int e = t; e < d * d; e += kWideFwdThreads) {
+            const int r = e / d, c = e - r * d;
+            Lb[e] = Lz[r * ld + c];
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kWideBwdThreads)
+chol_wide_bwd_kernel(int d, int ld, int tpc, int vec, const float* __restrict__ L, const float* __restrict__ G,
+                     const float* __restrict__ g_logdet, const float* __restrict__ g_l1, int penalty,
+                     float* __restrict__ gG) {
+    extern __shared__ __align__(16) float smem[];
+    float* Ls = smem;                          // [d][ld]
+    float* Ws = smem + (size_t)d * ld;         // [d][ld]  W = L^{-1} (lower triangular, zero elsewhere incl. padding)
+    float* invd = Ws + (size_t)d * ld;         // [d]      1 / L[i][i]
+    const int b = blockIdx.x, t = threadIdx.x;
+    const float* Lb = L + (size_t)b * d * d;
+    if (vec) {
+        const int d4 = d >> 2;
+        for (int e = t; e < d * d4; e += kWideBwdThreads) {
+            const int r = e / d4, c = (e - r * d4) << 2;
+            *reinterpret_cast<float4*>(Ls + r * ld + c) = ldg4(Lb + (size_t)r * d + c);
+        }
+    } else {
+        for (int e = t; e < d * d; e += kWideBwdThreads) {
+            const int r = e / d, c = e - r * d;
+            Ls[r * ld + c] = __ldg(Lb + e);
+        }
+    }
+    for (int e = t; e < d * ld; e += kWideBwdThreads) Ws[e] = 0.f;
+    if (t < d) invd[t] = 1.f / __ldg(Lb + (size_t)t * d + t);
+    __syncthreads();
+    // column j of W by forward substitution, tpc lanes per column (adjacent lanes of one warp): they
+    // split the dot product W[i][j] = -(sum_{m<i} L[i][m] W[m][j]) / L[i][i] by m mod tpc and combine
+    // with xor shuffles -- a row step is a ~100-cycle chain instead of i dependent iterations.
+    {
+        const int j = t / tpc, sub = t - j * tpc;
+        const bool col = j < d;
+        if (col && sub == 0) Ws[j * ld + j] = invd[j];
+        const int m0 = (j / tpc) * tpc + sub;          // first m >= the aligned group of j (W[m][j] = 0 for m < j)
+        for (int i = 1; i < d; ++i) {
+            float a0 = 0.f, a1 = 0.f;
+            if (col && j < i) {
+                const float* ri = Ls + i * ld;
+                int m = m0;
+                for (; m + tpc < i; m += 2 * tpc) {
+                    a0 = fmaf(ri[m], Ws[m * ld + j], a0);
+                    a1 = fmaf(ri[m + tpc], Ws[(m + tpc) * ld + j], a1);
+                }
+                if (m < i) a0 = fmaf(ri[m], Ws[m * ld + j], a0);
+            }
+            float acc = a0 + a1;
+            for (int o = tpc >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (col && j < i && sub == 0) Ws[i * ld + j] = -acc * invd[i];
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    // G^{-1} = W^T W in 4x4 register tiles; tile (ty, tx) needs rows m >= max(4 ty, 4 tx) only
+    const float gl = __ldg(g_logdet + b);
+    const float g1 = (penalty != CMF_PENALTY_NONE && g_l1) ? __ldg(g_l1 + b) : 0.f;
+    const float* Gb = G + (size_t)b * d * d;
+    float* Ob = gG + (size_t)b * d * d;
+    const int nt = (d + 3) >> 2;
+    for (int tile = t; tile < nt * nt; tile += kWideBwdThreads) {
+        const int ty = tile / nt, tx = tile - ty * nt;
+        float acc[4][4] = {};
+        for (int m = 4 * max(ty, tx); m < d; ++m) {
+            const float4 a = *reinterpret_cast<const float4*>(Ws + m * ld + 4 * ty);
+            const float4 c = *reinterpret_cast<const float4*>(Ws + m * ld + 4 * tx);
+            const float av[4] = {a.x, a.y, a.z, a.w}, cv[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(av[p], cv[q], acc[p][q]);
+        }
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int i = 4 * ty + p;
+            if (i >= d) continue;
+            float out[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int j = 4 * tx + q;
+                out[q] = gl * acc[p][q];
+                const bool sel = penalty == CMF_PENALTY_OFFDIAG ? (i != j) : (penalty == CMF_PENALTY_DIAG ? (i == j) : false);
+                if (sel && j < d) {
+                    const float g = __ldg(Gb + (size_t)i * d + j);
+                    out[q] += g1 * (g > 0.f ? 1.f : (g < 0.f ? -1.f : 0.f));
+                }
+            }
+            if (vec) {
+                *reinterpret_cast<float4*>(Ob + (size_t)i * d + 4 * tx) = make_float4(out[0], out[1], out[2], out[3]);
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (4 * tx + q < d) Ob[(size_t)i * d + 4 * tx + q] = out[q];
+            }
+        }
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// d == 64 (the MNIST-shape latent): ONE WARP per sample, the matrix in registers.  Lane l owns rows
+// l and l + 32 (2 x 64 floats); the loops over k and j are fully unrolled so every register index
+// is static.  Right-looking: at step k the pivot is broadcast by one shuffle, the scaled column goes
+// through a 64-float shared buffer (two stores, 128-bit broadcast loads) and every lane updates the
+// trailing part of its two rows with independent FMAs.  ~80 warp instructions per step instead of
+// the ~600 the block-per-sample kernel spends on barriers, shuffles and loop control (measured:
+// that kernel is bound by instruction issue of its 8 warps, not by arithmetic).  Entries above the
+// diagonal carry garbage that is never read; the pivots decide positive definiteness exactly as
+// before.
+// ---------------------------------------------------------------------------------------------
+constexpr int kWarpD = 64;
+constexpr int kWarpCholThreads = 128;       // 4 samples per CTA
+
+__global__ void __launch_bounds__(kWarpCholThreads)
+chol_warp64_fwd_kernel(int B, const float* __restrict__ G, float* __restrict__ L,
+                       float* __restrict__ logdet, float* __restrict__ l1_off, float* __restrict__ l1_diag,
+                       int32_t* __restrict__ info) {
+    constexpr int D = kWarpD;
+    __shared__ __align__(16) float colbuf[kWarpCholThreads / 32][2][D];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x * (kWarpCholThreads / 32) + warp;
+    if (b >= B) return;                         // warp-uniform; no block-wide barrier below
+    const float* Gb = G + (size_t)b * D * D;
+    float a0[D], a1[D];
+#pragma unroll
+    for (int c = 0; c < D / 4; ++c) {
+        const float4 u = ldg4(Gb + (size_t)lane * D + 4 * c);
+        const float4 v = ldg4(Gb + (size_t)(lane + 32) * D + 4 * c);
+        a0[4 * c] = u.x; a0[4 * c + 1] = u.y; a0[4 * c + 2] = u.z; a0[4 * c + 3] = u.w;
+        a1[4 * c] = v.x; a1[4 * c + 1] = v.y; a1[4 * c + 2] = v.z; a1[4 * c + 3] = v.w;
+    }
+    float off = 0.f, dia = 0.f;
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        const float x0 = fabsf(a0[j]), x1 = fabsf(a1[j]);
+        if (j == lane) dia += x0; else off += x0;
+        if (j == lane + 32) dia += x1; else off += x1;
+    }
+    bool fail = false;
+#pragma unroll
+    for (int k = 0; k < D; ++k) {
+        const float akk = __shfl_sync(0xffffffffu, k < 32 ? a0[k] : a1[k], k & 31);
+        if (!(akk > 0.f)) fail = true;          // same value in every lane
+        const float rs = rsqrt_nr(akk);
+        const float l0 = a0[k] * rs, l1 = a1[k] * rs;
+        a0[k] = l0;
+        a1[k] = l1;
+        if (k + 1 < D) {
+            float* col = colbuf[warp][k & 1];
+            col[lane] = l0;
+            col[lane + 32] = l1;
+            __syncwarp();
+#pragma unroll
+            for (int g = (k + 1) / 4; g < D / 4; ++g) {
+                const float4 c = *reinterpret_cast<const float4*>(col + 4 * g);
+                const float cv[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int j = 4 * g + e;
+                    if (j > k) {
+                        a0[j] = fmaf(-l0, cv[e], a0[j]);
+                        a1[j] = fmaf(-l1, cv[e], a1[j]);
+                    }
+                }
+            }
+        }
+    }
+    // log det from the diagonal entries this lane owns
+    float d0 = 1.f, d1 = 1.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        if (j == lane) { d0 = a0[j]; d1 = a1[j + 32]; }
+    }
+    const float ld_sum = warp_sum(logf(d0) + logf(d1));
+    const float off_sum = warp_sum(off), dia_sum = warp_sum(dia);
+    if (lane == 0) {
+        if (fail) atomicMax(info, b + 1);
+        logdet[b] = fail ? nanf("") : 2.f * ld_sum;
+        l1_off[b] = off_sum;
+        l1_diag[b] = dia_sum;
+    }
+    float* Lb = L + (size_t)b * D * D;
+#pragma unroll
+    for (int c = 0; c < D / 4; ++c) {
+        float4 u, v;
+        u.x = 4 * c + 0 <= lane ? a0[4 * c + 0] : 0.f;
+        u.y = 4 * c + 1 <= lane ? a0[4 * c + 1] : 0.f;
+        u.z = 4 * c + 2 <= lane ? a0[4 * c + 2] : 0.f;
+        u.w = 4 * c + 3 <= lane ? a0[4 * c + 3] : 0.f;
+        v.x = 4 * c + 0 <= lane + 32 ? a1[4 * c + 0] : 0.f;
+        v.y = 4 * c + 1 <= lane + 32 ? a1[4 * c + 1] : 0.f;
+        v.z = 4 * c + 2 <= lane + 32 ? a1[4 * c + 2] : 0.f;
+        v.w = 4 * c + 3 <= lane + 32 ? a1[4 * c + 3] : 0.f;
+        *reinterpret_cast<float4*>(Lb + (size_t)lane * D + 4 * c) = u;
+        *reinterpret_cast<float4*>(Lb + (size_t)(lane + 32) * D + 4 * c) = v;
+    }
+}
+
 static int pick_tps(int d) {
     int t = 4;
     while (t < d) t <<= 1;
@@ -187,6 +525,28 @@ extern "C" int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float
     if (B == 0) return 0;
     CMF_REQUIRE(G && L && logdet && l1_off && l1_diag && info, "chol_fwd: null pointer");
     if (d > kCholMaxD) return chol_big_fwd_launch(B, d, G, L, logdet, l1_off, l1_diag, info, (cudaStream_t)stream);
+    if (d == kWarpD && aligned16(G) && aligned16(L)) {
+        chol_warp64_fwd_kernel<<<(unsigned)ceil_div(B, kWarpCholThreads / 32), kWarpCholThreads, 0, (cudaStream_t)stream>>>(
+            B, G, L, logdet, l1_off, l1_diag, info);
+        CMF_CHECK_LAUNCH();
+        return 0;
+    }
+    if (d >= kCholWideMinD) {
+        const int ld = wide_ld(d);
+        const int vec = (d % 4 == 0) && aligned16(G) && aligned16(L);
+        const size_t smem = ((size_t)2 * d * ld + 8) * sizeof(float);
+        int tpr = 8;
+        while (d * tpr > kWideFwdThreads) tpr >>= 1;
+        static bool wide_attr = false;
+        if (!wide_attr) {
+            cudaError_t e = cudaFuncSetAttribute(chol_wide_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) { set_error("chol_fwd attr: %s", cudaGetErrorString(e)); return (int)e; }
+            wide_attr = true;
+        }
+        chol_wide_fwd_kernel<<<(unsigned)B, kWideFwdThreads, smem, (cudaStream_t)stream>>>(d, ld, tpr, vec, G, L, logdet, l1_off, l1_diag, info);
+        CMF_CHECK_LAUNCH();
+        return 0;
+    }
     const int tps = pick_tps(d), spb = kCholThreads / tps;
     const size_t smem = ((size_t)spb * d * (d + 1) + kCholThreads + spb) * sizeof(float);
     static bool attr_set = false;
@@ -209,6 +569,22 @@ extern "C" int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
     if (B == 0) return 0;
     CMF_REQUIRE(L && G && g_logdet && g_G, "chol_bwd: null pointer");
     if (d > kCholMaxD) return chol_big_bwd_launch(B, d, L, G, g_logdet, g_l1, penalty, g_G, (cudaStream_t)stream);
+    if (d >= kCholWideMinD) {
+        const int ld = wide_ld(d);
+        const int vec = (d % 4 == 0) && aligned16(L) && aligned16(g_G);
+        const size_t smem = ((size_t)2 * d * ld + d) * sizeof(float);
+        int tpc = 8;
+        while (d * tpc > kWideBwdThreads) tpc >>= 1;
+        static bool wide_attr = false;
+        if (!wide_attr) {
+            cudaError_t e = cudaFuncSetAttribute(chol_wide_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) { set_error("chol_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
+            wide_attr = true;
+        }
+        chol_wide_bwd_kernel<<<(unsigned)B, kWideBwdThreads, smem, (cudaStream_t)stream>>>(d, ld, tpc, vec, L, G, g_logdet, g_l1, penalty, g_G);
+        CMF_CHECK_LAUNCH();
+        return 0;
+    }
     const int tps = pick_tps(d), spb = kCholThreads / tps;
     const size_t smem = (size_t)spb * 2 * d * (d + 1) * sizeof(float);
     static bool attr_set = false;

@@ -128,6 +128,115 @@ gram_bwd_kernel(int d, int n, int nx, const float* __restrict__ V, const float* 
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Adjoint for d <= 64 (the MNIST-shape latent): one CTA per (sample, group of 128-column chunks).
+// S + S^T (64 x 64, zero padded) is staged ONCE per CTA in shared memory; V chunks of 64 x 128
+// arrive by 16-byte cp.async into a double buffer while the previous chunk is multiplied.  A warp
+// owns 16 output columns and all 64 rows (8 x 4 register tile per thread: two broadcast-free 128-bit
+// loads of S and one of V per k, 32 FMAs), so the ragged last chunk (n = 392 = 3 x 128 + 8) costs
+// one warp, not a tile.  The generic kernel above re-reads S (transposed, uncoalesced) for every
+// 64 x 64 output tile and is bound by that: 101 us at B = 512, n = 392 against an FMA floor of 25.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSmallD = 64;
+constexpr int kChunkN = 128;
+constexpr int kALd = kSmallD + 4;        // 68: rows 16-byte aligned
+constexpr int kBLd = kChunkN + 4;        // 132
+constexpr size_t kSmallSmem = (size_t)(kSmallD * kALd + 2 * kSmallD * kBLd) * sizeof(float);
+
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kN>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kN) : "memory"); }
+
+// grid = (B, splits); CTA (b, s) handles chunks s, s + splits, ... of sample b
+__global__ void __launch_bounds__(256, 2)
+gram_bwd_small_kernel(int d, int n, const float* __restrict__ V, const float* __restrict__ gG, float* __restrict__ gV) {
+    extern __shared__ __align__(16) float sm[];
+    float* As = sm;                                   // [64][68]   As[k][m] = S[k][m] + S[m][k]
+    float* Bs = sm + kSmallD * kALd;                  // [2][64][132]
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const float* Vb = V + (size_t)b * d * n;
+    const float* Sb = gG + (size_t)b * d * d;
+    float* Ob = gV + (size_t)b * d * n;
+    const int nchunks = (n + kChunkN - 1) / kChunkN;
+
+    auto load_chunk = [&](int c, int buf) {           // V[0..d) x [c*128, c*128+128) -> Bs[buf]
+        float* dst = Bs + (size_t)buf * kSmallD * kBLd;
+        const int c0 = c * kChunkN;
+        for (int e = tid; e < d * (kChunkN / 4); e += 256) {
+            const int k = e >> 5, q = (e & 31) << 2;
+            if (c0 + q < n) cp_async16(dst + k * kBLd + q, Vb + (size_t)k * n + c0 + q);
+        }
+        cp_async_commit();
+    };
+
+    int c = blockIdx.y;
+    if (c < nchunks) load_chunk(c, 0);
+    // stage S raw into the second V buffer, then symmetrise into As (zero padded to 64 x 64)
+    {
+        float* T = Bs + (size_t)kSmallD * kBLd;       // [64][65]
+        float sv[kSmallD * kSmallD / 256];            // all 16 loads in flight before the first store
+#pragma unroll
+        for (int u = 0; u < kSmallD * kSmallD / 256; ++u) {
+            const int e = tid + 256 * u, r = e >> 6, q = e & 63;
+            sv[u] = (r < d && q < d) ? __ldg(Sb + (size_t)r * d + q) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < kSmallD * kSmallD / 256; ++u) {
+            const int e = tid + 256 * u;
+            T[(e >> 6) * 65 + (e & 63)] = sv[u];
+        }
+        __syncthreads();
+        for (int e = tid; e < kSmallD * kSmallD; e += 256) {
+            const int k = e >> 6, m = e & 63;
+            As[k * kALd + m] = T[k * 65 + m] + T[m * 65 + k];
+        }
+        __syncthreads();
+    }
+    const int warp = tid >> 5, lane = tid & 31;
+    const int mg = lane >> 2, cg = lane & 3;          // rows {4 mg .. +3} and {32 + 4 mg .. +3}; columns 16 warp + 4 cg .. +3
+    int buf = 0;
+    for (; c < nchunks; c += gridDim.y, buf ^= 1) {
+        const int cn = c + gridDim.y;
+        if (cn < nchunks) { load_chunk(cn, buf ^ 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+        __syncthreads();
+        const int col0 = c * kChunkN + 16 * warp;
+        if (col0 < n) {                               // warp-uniform: the ragged chunk runs on its live warps only
+            const float* Bc = Bs + (size_t)buf * kSmallD * kBLd + 16 * warp + 4 * cg;
+            float acc[8][4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+            for (int k = 0; k < d; ++k) {
+                const float4 a0 = *reinterpret_cast<const float4*>(As + k * kALd + 4 * mg);
+                const float4 a1 = *reinterpret_cast<const float4*>(As + k * kALd + 32 + 4 * mg);
+                const float4 v = *reinterpret_cast<const float4*>(Bc + k * kBLd);
+                const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+                const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], vv[j], acc[i][j]);
+            }
+            const int col = col0 + 4 * cg;
+            if (col < n) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int m = (i < 4 ? 4 * mg + i : 32 + 4 * mg + (i - 4));
+                    if (m < d) stcs4(Ob + (size_t)m * n + col, make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]));
+                }
+            }
+        }
+        __syncthreads();                              // everyone is done with Bs[buf] before it is refilled
+    }
+}
+
 // tensor-core path (gram_tc.cu)
 bool gram_tc_usable(int B, int d, int n, const float* V, const float* G);
 int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumulate, cudaStream_t stream);
@@ -185,6 +294,22 @@ extern "C" int cmf_gram_bwd_path(int B, int d, int n, const float* V, const floa
                     "gram_bwd: tensor-core path needs d >= 16, d %% 4 == 0, n >= 32, n %% 4 == 0 and 16-byte aligned V, g_G (d=%d n=%d)", d, n);
         // at d <= 64 the FP32 FMA kernel is as fast (HBM-bound either way); the tensor core wins above
         if (ok && (path == CMF_GRAM_TC || d > 64)) return gram_tc_bwd_launch(B, d, n, V, g_G, g_V, (cudaStream_t)stream);
+    }
+    if (d <= kSmallD && n % 4 == 0 && aligned16(V) && aligned16(g_V) && B <= 65535 * 32) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaError_t e = cudaFuncSetAttribute(gram_bwd_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallSmem);
+            if (e != cudaSuccess) { set_error("gram_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
+            attr_set = true;
+        }
+        // split a sample's chunks over several CTAs while the grid is below ~2 CTAs per SM
+        const int nchunks = (int)ceil_div(n, kChunkN);
+        int splits = 1;
+        while (splits < nchunks && (long long)B * splits < 2 * kNumSMs) ++splits;
+        dim3 grid((unsigned)B, (unsigned)splits);
+        gram_bwd_small_kernel<<<grid, 256, kSmallSmem, (cudaStream_t)stream>>>(d, n, V, g_G, g_V);
+        CMF_CHECK_LAUNCH();
+        return 0;
     }
     const int nx = (int)ceil_div(n, BT);
     CMF_REQUIRE((long long)B * nx < (1LL << 31), "gram_bwd: grid too large");

@@ -102,6 +102,16 @@ def test_gram_fwd_bwd(B, d, n):
     _close(K.gram_bwd(Vd, gG.float().to(DEV)), E.gram_bwd(V, gG), rtol=1e-5, what="g_V")
 
 
+@pytest.mark.parametrize("B,d,n", [(3, 64, 392), (600, 64, 8), (2, 64, 132), (5, 33, 256), (1, 17, 4), (7, 50, 520), (2, 6, 12)])
+def test_gram_bwd_small_d_kernel(B, d, n):
+    """d <= 64, n % 4 == 0: the staged-S kernel (ragged last 128-column chunk, chunk groups split over
+    CTAs when B is small, zero-padded S) against the fp64 contract"""
+    import cmf_b200.kernels as K
+    V, gG = _rand(B, d, n, seed=11), _rand(B, d, d, seed=12)
+    got = K.gram_bwd(V.float().to(DEV), gG.float().to(DEV), path="fma")
+    _close(got, E.gram_bwd(V, gG), rtol=1e-5, what="g_V small-d")
+
+
 TC_SHAPES = [(5, 64, 392), (50, 64, 784), (3, 128, 96), (4, 20, 40), (2, 256, 128), (3, 200, 36),
              (7, 16, 32), (1, 512, 64), (9, 48, 100), (2, 130, 260)]
 
@@ -164,7 +174,8 @@ def _spd(B, d, seed=0, cond=1e3):
     return G * scale.view(1, d, 1) * scale.view(1, 1, d) + 1e-6 * torch.eye(d, dtype=torch.float64)
 
 
-@pytest.mark.parametrize("B,d", [(1, 1), (7, 2), (33, 3), (100, 6), (17, 10), (5, 20), (9, 64), (3, 100), (2, 128),
+@pytest.mark.parametrize("B,d", [(1, 1), (7, 2), (33, 3), (100, 6), (17, 10), (5, 20), (4, 31), (6, 32), (5, 33), (3, 50),
+                                 (9, 64), (3, 100), (2, 127), (2, 128),
                                  (3, 129), (2, 200), (2, 256), (2, 512), (1, 1000)])
 def test_chol_logdet_fwd_bwd(B, d):
     import cmf_b200.kernels as K
@@ -194,6 +205,13 @@ def test_chol_reports_non_positive_definite():
     assert int(info.item()) == 5          # 1 + largest failing sample index
     *_, info = K.chol_logdet_fwd(_spd(6, 8).float().to(DEV))
     assert int(info.item()) == 0
+    # one-sample-per-CTA kernel (32 <= d <= 128): negative pivot late in sample 3, NaN in sample 1
+    G = _spd(5, 64)
+    G[3, 60, 60] = -1.0
+    G[1, 20, 5] = G[1, 5, 20] = float("nan")
+    _, ld, *_, info = K.chol_logdet_fwd(G.float().to(DEV))
+    assert int(info.item()) == 4
+    assert torch.isnan(ld[3]) and torch.isnan(ld[1]) and torch.isfinite(ld[[0, 2, 4]]).all()
     # panel-blocked kernel (d > 128): failure in a later panel of sample 2, NaN in sample 0
     G = _spd(4, 160)
     G[2, 150, 150] = -1.0
