@@ -132,7 +132,14 @@ __device__ __forceinline__ void finalize_store(float z, float e, float gx, float
 }
 
 // identity map, 128-bit path.  grid = (ceil(B*M/4 / kThreads), KC)
-__global__ void __launch_bounds__(kThreads)
+#ifndef CMF_CPL_BWD_MINB
+#define CMF_CPL_BWD_MINB 1
+#endif
+#ifndef CMF_CPL_BWD_UNROLL
+#define CMF_CPL_BWD_UNROLL 4
+#endif
+constexpr int kUnrollB = CMF_CPL_BWD_UNROLL;
+__global__ void __launch_bounds__(kThreads, CMF_CPL_BWD_MINB)
 coupling_bwd_vec4(int B, int d, int M, int kchunk,
                   const float* __restrict__ z_m, const float* __restrict__ V_m,
                   const float* __restrict__ st, const float* __restrict__ ST,
@@ -159,24 +166,24 @@ coupling_bwd_vec4(int B, int d, int M, int kchunk,
     float* ovp = g_Vin + ((size_t)b * d + k0) * M + j;
     float* otp = g_ST + ((size_t)b * d + k0) * 2 * M + j;
     int k = k0;
-    for (; k + kUnroll <= k1; k += kUnroll) {
-        float4 g[kUnroll], v[kUnroll], sd[kUnroll];
+    for (; k + kUnrollB <= k1; k += kUnrollB) {
+        float4 g[kUnrollB], v[kUnrollB], sd[kUnrollB];
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
+        for (int u = 0; u < kUnrollB; ++u) {
             g[u] = ldcs4(gp + (size_t)u * M);
             v[u] = ldcs4(vp + (size_t)u * M);
             sd[u] = ldcs4(sp + (size_t)u * 2 * M);
         }
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
+        for (int u = 0; u < kUnrollB; ++u) {
             A.x += sd[u].x * g[u].x; A.y += sd[u].y * g[u].y; A.z += sd[u].z * g[u].z; A.w += sd[u].w * g[u].w;
             C.x += v[u].x * g[u].x;  C.y += v[u].y * g[u].y;  C.z += v[u].z * g[u].z;  C.w += v[u].w * g[u].w;
             stcs4(ovp + (size_t)u * M, make_float4(e.x * g[u].x, e.y * g[u].y, e.z * g[u].z, e.w * g[u].w));
             stcs4(otp + (size_t)u * 2 * M, make_float4(-g[u].x, -g[u].y, -g[u].z, -g[u].w));
             stcs4(otp + (size_t)u * 2 * M + M, make_float4(ez.x * g[u].x, ez.y * g[u].y, ez.z * g[u].z, ez.w * g[u].w));
         }
-        gp += (size_t)kUnroll * M; vp += (size_t)kUnroll * M; sp += (size_t)kUnroll * 2 * M;
-        ovp += (size_t)kUnroll * M; otp += (size_t)kUnroll * 2 * M;
+        gp += (size_t)kUnrollB * M; vp += (size_t)kUnrollB * M; sp += (size_t)kUnrollB * 2 * M;
+        ovp += (size_t)kUnrollB * M; otp += (size_t)kUnrollB * 2 * M;
     }
     for (; k < k1; ++k) {
         const float4 g = ldcs4(gp), v = ldcs4(vp), sd = ldcs4(sp);

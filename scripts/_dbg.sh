@@ -1,2 +1,2 @@
 export PYTHONPATH=.
-timeout -k 10 900 python scripts/bench_cifar.py 2> /dev/null | tee gpurun_out/cifar_sweep.jsonl
+timeout -k 10 300 python bench.py --only scope_a 2>&1 | tail -2 | cut -c1-1200
