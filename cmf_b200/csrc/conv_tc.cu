@@ -457,7 +457,8 @@ extern "C" int cmf_conv3x3_c64_usable(int N, int H, int W) {
 
 static int conv_launch(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                        const float* mask_src, const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
-                       float* y, float* y2, cmf_stream_t stream) {
+                       float* y, float* y2, int drain_stages, cmf_stream_t stream) {
+    CMF_REQUIRE(drain_stages >= 1 && drain_stages <= 3, "conv3x3: drain_stages must be 1, 2 or 3 (got %d)", drain_stages);
     CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3: negative size");
     if (N == 0 || H == 0 || W == 0) return 0;
     CMF_REQUIRE(x && wsplit && y, "conv3x3: null pointer");
@@ -488,8 +489,10 @@ static int conv_launch(int N, int H, int W, const float* x, const float* wsplit,
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const long long npairs = ceil_div(P.total_tiles, kTiles);
     const unsigned grid = (unsigned)(npairs < sms ? npairs : sms);
-    static int seg = 0;
-    if (seg == 0) { const char* e = getenv("CMF_CONV_SEG"); seg = e ? atoi(e) : 1; if (seg < 1 || seg > 3) seg = 1; }
+    // CMF_CONV_SEG (debug): force one drain interval for every launch
+    static int seg_env = -1;
+    if (seg_env < 0) { const char* e = getenv("CMF_CONV_SEG"); seg_env = e ? atoi(e) : 0; if (seg_env < 0 || seg_env > 3) seg_env = 0; }
+    const int seg = seg_env ? seg_env : drain_stages;
 #define CMF_CONV_LAUNCH(PITCH, SEG)                                                                                   \
     do {                                                                                                               \
         static bool attr_set = false;                                                                                  \
@@ -516,13 +519,13 @@ extern "C" int cmf_debug_conv_prof(long long* host_out) {
 extern "C" int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                                      const float* mask_src, int mask_div, int mask_first, const float* res,
                                      float* y, float* y2, cmf_stream_t stream) {
-    return conv_launch(N, H, W, x, wsplit, bias, mask_src, nullptr, mask_div, mask_first, res, y, y2, stream);
+    return conv_launch(N, H, W, x, wsplit, bias, mask_src, nullptr, mask_div, mask_first, res, y, y2, 1, stream);
 }
 
 extern "C" int cmf_conv3x3_c64_fused_bits(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                                           const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
-                                          float* y, float* y2, cmf_stream_t stream) {
-    return conv_launch(N, H, W, x, wsplit, bias, nullptr, mask_bits, mask_div, mask_first, res, y, y2, stream);
+                                          float* y, float* y2, int drain_stages, cmf_stream_t stream) {
+    return conv_launch(N, H, W, x, wsplit, bias, nullptr, mask_bits, mask_div, mask_first, res, y, y2, drain_stages, stream);
 }
 
 extern "C" int cmf_relu_mask_pack(int N, int HW, const float* x, uint32_t* bits, cmf_stream_t stream) {

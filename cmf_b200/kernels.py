@@ -239,7 +239,8 @@ def relu_mask_pack(x: Tensor) -> Tensor:
 
 
 def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_src: Optional[Tensor] = None,
-                mask_div: int = 1, mask_first: bool = False, res: Optional[Tensor] = None, second: bool = False):
+                mask_div: int = 1, mask_first: bool = False, res: Optional[Tensor] = None, second: bool = False,
+                drain: int = 1):
     """x (N,64,H,W), wsplit from ``conv3x3_c64_prep`` -> y (N,64,H,W), with the fused epilogue of
     ``cmf_conv3x3_c64_fused``:  t = conv(x) + bias; if mask_first: t *= m; if res: t += res; y = t;
     ``second`` additionally returns y2 = t * m  (m = mask_src[n // mask_div] > 0).  ``mask_src`` is
@@ -266,10 +267,15 @@ def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_s
     y = torch.empty_like(x)
     y2 = torch.empty_like(x) if second else None
     with torch.cuda.device(x.device):
-        fn = lib.cmf_conv3x3_c64_fused_bits if packed else lib.cmf_conv3x3_c64_fused
-        _lib.check(fn(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src), int(mask_div),
-                      int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2), _stream()),
-                   "cmf_conv3x3_c64_fused")
+        if packed or mask_src is None:      # the extended entry point (drain interval); mask_bits may be NULL
+            _lib.check(lib.cmf_conv3x3_c64_fused_bits(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src),
+                                                      int(mask_div), int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2),
+                                                      int(drain), _stream()), "cmf_conv3x3_c64_fused_bits")
+        else:
+            assert drain == 1
+            _lib.check(lib.cmf_conv3x3_c64_fused(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src), int(mask_div),
+                                                 int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2), _stream()),
+                       "cmf_conv3x3_c64_fused")
     return (y, y2) if second else y
 
 

@@ -24,6 +24,10 @@ Tensor = torch.Tensor
 
 # CMF_CONV=cudnn keeps every conditioner convolution on the library path (A/B measurements)
 _TC_CONV = os.environ.get("CMF_CONV", "tc") != "cudnn"
+# K = 32 stages per FP32 drain in the data-gradient launches of the backward pass.  Forward values
+# pass through G^-1 (errors amplified by cond(G) ~ 5e3) and keep the per-stage drain; a gradient is
+# consumed as is, so 4e-7 instead of 2e-7 relative error buys 7 % of those launches.
+_BWD_DRAIN = 2
 
 
 def _conv3x3_pair(conv: nn.Conv2d, h: Tensor, Hv):
@@ -149,10 +153,10 @@ class _ResidualStackTangent(torch.autograd.Function):
             A0, A1 = saved[2 * k], saved[2 * k + 1]
             grads[4 * k + 3] = kernels.conv3x3_c64_wgrad(A1, g)
             gC1 = kernels.conv3x3_c64(g, kernels.conv3x3_c64_prep(w2s[k], True), None, mask_src=h1s[k], mask_div=d,
-                                      mask_first=True)
+                                      mask_first=True, drain=_BWD_DRAIN)
             grads[4 * k + 2] = kernels.conv3x3_c64_wgrad(A0, gC1)
             g = kernels.conv3x3_c64(gC1, kernels.conv3x3_c64_prep(w1s[k], True), None, mask_src=xs[k], mask_div=d,
-                                    mask_first=True, res=g)
+                                    mask_first=True, res=g, drain=_BWD_DRAIN)
         return (g, None, *grads)
 
 

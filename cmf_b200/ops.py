@@ -212,7 +212,7 @@ class _Conv3x3C64(Function):
         x, weight = ctx.saved_tensors
         g_y = g_y.contiguous()
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        g_x = kernels.conv3x3_c64(g_y, kernels.conv3x3_c64_prep(weight, True), None) if need_x else None
+        g_x = kernels.conv3x3_c64(g_y, kernels.conv3x3_c64_prep(weight, True), None, drain=2) if need_x else None   # a gradient: see networks._BWD_DRAIN
         g_w = None
         if need_w and kernels.conv3x3_c64_wgrad_usable(x.shape[0], x.shape[2], x.shape[3]):
             g_w = kernels.conv3x3_c64_wgrad(x, g_y)

@@ -147,7 +147,11 @@ int cmf_conv3x3_c64_fused(int N, int H, int W, const float* x, const float* wspl
 int cmf_relu_mask_pack(int N, int HW, const float* x, uint32_t* bits, cmf_stream_t stream);
 int cmf_conv3x3_c64_fused_bits(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                                const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
-                               float* y, float* y2, cmf_stream_t stream);
+                               float* y, float* y2, int drain_stages, cmf_stream_t stream);
+/* drain_stages = K = 32 stages accumulated on the tensor core (truncating FP32 adds) between two
+ * round-to-nearest drains into registers: 1 for everything that feeds the metric G (its inverse
+ * amplifies forward errors by cond(G) ~ 5e3), 2 for the data-gradient launches of the backward
+ * pass (a 4e-7 instead of 2e-7 relative error on a gradient; 7 % faster).  mask_bits may be NULL. */
 
 /* Weight gradient of the same convolution: g_w (64,64,3,3) (+)= sum_{n,p} g_y[n,co,p] x[n,ci,p+tap]
  * (what autograd derives for F.conv2d at cmf/trainer.py:216, aten::convolution_backward).

@@ -119,7 +119,7 @@ def _unpack_mask(bits, H, W):
     return b.permute(0, 2, 3, 1).reshape(N, 64, H, W).bool()
 
 
-def conv3x3_c64(x, wsplit, bias=None, mask_src=None, mask_div=1, mask_first=False, res=None, second=False):
+def conv3x3_c64(x, wsplit, bias=None, mask_src=None, mask_div=1, mask_first=False, res=None, second=False, drain=1):
     t = torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
     m = None
     if mask_src is not None:

@@ -155,6 +155,17 @@ def test_packed_relu_mask_is_the_same_mask(N, H, W, d):
             assert torch.equal(u, v)
 
 
+@pytest.mark.parametrize("drain", [2, 3])
+def test_longer_drain_interval_of_the_gradient_launches(drain):
+    """drain = 2 (used by the data-gradient launches): K = 64 per FP32 drain, still ~5e-7 of the output scale"""
+    x, w = _rand((5, 64, 28, 28), 60), _rand((64, 64, 3, 3), 61, 1 / 24)
+    got = K.conv3x3_c64(x, K.conv3x3_c64_prep(w, True), None, drain=drain)
+    ref = F.conv_transpose2d(x.double(), w.double(), padding=1)
+    assert _rel(got, ref) < 2e-6
+    with pytest.raises(_lib.CmfB200Error):
+        K.conv3x3_c64(x, K.conv3x3_c64_prep(w, True), None, drain=4)
+
+
 def test_residual_stack_tangent_matches_autograd():
     """the fused tangent node of a residual-block run vs the per-op autograd path (library convs)"""
     from cmf_b200 import networks as NW
