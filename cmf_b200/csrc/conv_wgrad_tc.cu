@@ -66,7 +66,8 @@ struct WgradParams {
     int N, H, W, HW;
     int tiles_per_image;
     long long total_tiles;
-    int tiles_per_cta;
+    int tiles_per_cta;                  // tiles per chunk
+    long long num_chunks;               // ceil(total_tiles / tiles_per_cta); CTA b walks chunks b, b + grid, ...
     int hl;
     float* partial;                     // [grid][9][64 ci][64 co]
 };
@@ -96,8 +97,16 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
     uint8_t* gylo = smem + 2 * kSub * kBBytes;              // [4][8 KB]
     uint8_t* xh = gylo + kSub * kBBytes;                    // [2][64 ci][kPitch px]
 
-    const long long tile_begin = (long long)blockIdx.x * P.tiles_per_cta;
-    const int nt = (int)min((long long)P.tiles_per_cta, P.total_tiles - tile_begin);
+    // PERSISTENT: a CTA walks chunks of tiles_per_cta tiles.  The accumulators are re-zeroed per chunk
+    // (the chunk bounds the truncating tensor-core accumulation) and the chunk's result is ADDED, in
+    // FP32 round-to-nearest, to this CTA's own partial in global memory -- 148 x 147 KB stays in L2,
+    // where one partial per chunk (1600 for the 28x28 tangent batch) cost 46 GB of DRAM traffic and
+    // 9 ms per step in the reduction kernel.  Every mbarrier phase is a function of the running tile
+    // counter gt (or staging counter ns), which all roles advance identically.
+    auto chunk_tiles = [&](long long ch, long long& tile_begin) {
+        tile_begin = ch * P.tiles_per_cta;
+        return (int)min((long long)P.tiles_per_cta, P.total_tiles - tile_begin);
+    };
 
     if (threadIdx.x == 0) {
         for (int b = 0; b < 2; ++b) { mbar_init(&x_full[b], 1); mbar_init(&g_full[b], 1); mbar_init(&tile_done[b], kIssuers); }
@@ -118,16 +127,21 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
-            for (int i = 0; i < nt; ++i) {
-                const int buf = i & 1;
-                const long long T = tile_begin + i;
-                const int img = (int)(T / P.tiles_per_image), p0 = (int)(T % P.tiles_per_image) * kTileM;
-                if (i >= 2) mbar_wait(&tile_done[buf], ((i >> 1) - 1) & 1);
-                mbar_arrive_expect_tx(&x_full[buf], (uint32_t)kXBytes);
-                tma_load_2d(xh + (size_t)buf * kXBytes, &tmx, &x_full[buf], p0 - P.hl, img * kC);
-                mbar_arrive_expect_tx(&g_full[buf], (uint32_t)(kSub * kBBytes));
-                for (int q = 0; q < kSub; ++q)
-                    tma_load_2d(gyhi + (size_t)(buf * kSub + q) * kBBytes, &tmg, &g_full[buf], p0 + 32 * q, img * kC);
+            int gt = 0;
+            for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x) {
+                long long tile_begin;
+                const int nt = chunk_tiles(ch, tile_begin);
+                for (int i = 0; i < nt; ++i, ++gt) {
+                    const int buf = gt & 1;
+                    const long long T = tile_begin + i;
+                    const int img = (int)(T / P.tiles_per_image), p0 = (int)(T % P.tiles_per_image) * kTileM;
+                    if (gt >= 2) mbar_wait(&tile_done[buf], ((gt >> 1) - 1) & 1);
+                    mbar_arrive_expect_tx(&x_full[buf], (uint32_t)kXBytes);
+                    tma_load_2d(xh + (size_t)buf * kXBytes, &tmx, &x_full[buf], p0 - P.hl, img * kC);
+                    mbar_arrive_expect_tx(&g_full[buf], (uint32_t)(kSub * kBBytes));
+                    for (int q = 0; q < kSub; ++q)
+                        tma_load_2d(gyhi + (size_t)(buf * kSub + q) * kBBytes, &tmg, &g_full[buf], p0 + 32 * q, img * kC);
+                }
             }
         }
     } else if (warp == 1 || (warp == kMmaWarp1 && kIssuers == 2)) {
@@ -141,17 +155,20 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
         constexpr int kPer = 4 / kIssuers;
         const uint32_t gyhi_addr = smem_u32(gyhi), gylo_addr = smem_u32(gylo);
-        mbar_wait(&acc_init, 0);
+        int ns = 0, gt = 0, r = 0;
+        for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x, ++r) {
+        long long tile_begin;
+        const int nt = chunk_tiles(ch, tile_begin);
+        mbar_wait(&acc_init, r & 1);            // the row workers have re-zeroed the accumulators for this chunk
         tc_fence_after();
-        int ns = 0;
-        for (int i = 0; i < nt; ++i) {
-            const int buf = i & 1;
+        for (int i = 0; i < nt; ++i, ++gt) {
+            const int buf = gt & 1;
             const int nq = live_subchunks(P.HW, (int)((tile_begin + i) % P.tiles_per_image) * kTileM);
             const int cnt = nq * kPairs;
             for (int n = 0; n < cnt; ++n, ++ns) {
                 const int q = n / kPairs, j = n - q * kPairs;
                 const int sb = ns % kStgBufs;
-                if (j == 0) mbar_wait(&b_ready[q], i & 1);
+                if (j == 0) mbar_wait(&b_ready[q], gt & 1);
                 mbar_wait(&st_full[sb], (ns / kStgBufs) & 1);
                 tc_fence_after();
                 if (elect_one()) {
@@ -174,12 +191,13 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
             // skipped sub-chunks: keep the b_ready / qdone phases in step (one per tile), and release
             // the tile's buffers only after the splitters are done rewriting ALL of its g_y boxes
             for (int q = nq; q < kSub; ++q) {
-                mbar_wait(&b_ready[q], i & 1);
+                mbar_wait(&b_ready[q], gt & 1);
                 if (elect_one()) umma_commit(&qdone[q]);
                 __syncwarp();
             }
             if (elect_one()) umma_commit(&tile_done[buf]);
             __syncwarp();
+        }
         }
     } else if (warp == kMmaWarp1) {
         // second issuer slot unused (kIssuers == 1)
@@ -187,11 +205,15 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         // ------------------------------------------------------------------ g_y splitters (64 threads)
         const int tid = threadIdx.x - 320;
         const uint32_t gyhi_addr = smem_u32(gyhi), gylo_addr = smem_u32(gylo);
-        for (int i = 0; i < nt; ++i) {
-            const int buf = i & 1;
-            mbar_wait(&g_full[buf], (i >> 1) & 1);
+        int gt = 0;
+        for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x) {
+        long long tile_begin;
+        const int nt = chunk_tiles(ch, tile_begin);
+        for (int i = 0; i < nt; ++i, ++gt) {
+            const int buf = gt & 1;
+            mbar_wait(&g_full[buf], (gt >> 1) & 1);
             for (int q = 0; q < kSub; ++q) {
-                if (i >= 1) mbar_wait(&qdone[q], (i - 1) & 1);      // remainder buffer q free again
+                if (gt >= 1) mbar_wait(&qdone[q], (gt - 1) & 1);      // remainder buffer q free again
                 const uint32_t src = gyhi_addr + (uint32_t)((buf * kSub + q) * kBBytes), dst = gylo_addr + (uint32_t)(q * kBBytes);
 #pragma unroll
                 for (int it = 0; it < kBBytes / 16 / 64; ++it) {
@@ -208,6 +230,7 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                 if (lane == 0) mbar_arrive(&b_ready[q]);
             }
         }
+        }
     } else {
         // ------------------------------------------------------------------ row workers (x operand)
         const int g = (warp - 2) >> 2;                    // this group stages n with n % 2 == g
@@ -216,6 +239,10 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         const int a = m >> 6, ci = m & 63;
         const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
         const uint32_t xrow_addr = smem_u32(xh) + (uint32_t)(ci * kPitch * 4);
+        int ns_base = 0, gt = 0, r = 0;                   // stagings / tiles / chunks before the current one
+        for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x, ++r) {
+        long long tile_begin;
+        const int nt = chunk_tiles(ch, tile_begin);
         {   // zero the five accumulators (group g: columns [160 g, 160 g + 160) of this warp's lane quarter)
             float zero[32];
 #pragma unroll
@@ -227,9 +254,8 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_init);
         }
-        int ns_base = 0;                                  // stagings of the tiles before this one
-        for (int i = 0; i < nt; ++i) {
-            const int buf = i & 1;
+        for (int i = 0; i < nt; ++i, ++gt) {
+            const int buf = gt & 1;
             const long long T = tile_begin + i;
             const int p0 = (int)(T % P.tiles_per_image) * kTileM;
             const int cnt = live_subchunks(P.HW, p0) * kPairs;
@@ -241,7 +267,7 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                 ml[q] = __ballot_sync(0xffffffffu, xx > 0);
                 mr[q] = __ballot_sync(0xffffffffu, xx + 1 < P.W);
             }
-            mbar_wait(&x_full[buf], (i >> 1) & 1);
+            mbar_wait(&x_full[buf], (gt >> 1) & 1);
             // group g stages the stagings whose GLOBAL index is congruent to g mod 2 (cnt may be odd)
             for (int n = (ns_base & 1) == g ? 0 : 1; n < cnt; n += 2) {
                 const int ns = ns_base + n;
@@ -296,8 +322,8 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
             ns_base += cnt;
         }
         // ------------------------------------------------------------------ epilogue: partial g_w
-        if (nt > 0) {
-            const int last = nt - 1;
+        {
+            const int last = gt - 1;                      // every chunk has at least one tile
             mbar_wait(&tile_done[last & 1], (last >> 1) & 1);
             tc_fence_after();
             float* out = P.partial + (size_t)blockIdx.x * (kTaps * kC * kC);
@@ -309,11 +335,25 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     tmem_ld_32x32(tmem_base + lane_addr + (uint32_t)(j * kC + 32 * h), v);
                     if (tap < kTaps) {
                         float4* dst = reinterpret_cast<float4*>(out + ((size_t)tap * kC + ci) * kC + 32 * h);
+                        if (r == 0) {
 #pragma unroll
-                        for (int e = 0; e < 8; ++e) dst[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                            for (int e = 0; e < 8; ++e) dst[e] = make_float4(v[4 * e], v[4 * e + 1], v[4 * e + 2], v[4 * e + 3]);
+                        } else {      // this thread wrote these words itself one chunk ago: plain read-add-write
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                const float4 o = dst[e];
+                                dst[e] = make_float4(o.x + v[4 * e], o.y + v[4 * e + 1], o.z + v[4 * e + 2], o.w + v[4 * e + 3]);
+                            }
+                        }
                     }
                 }
             }
+            // the re-zeroing of the next chunk touches accumulator columns another worker warp of the
+            // same lane quarter has just read: all 8 worker warps (256 threads) meet first
+            tc_fence_before();
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            tc_fence_after();
+        }
         }
     }
     tc_fence_before();
@@ -367,7 +407,7 @@ int wgrad_plan(int N, int H, int W, int* tiles_per_cta, long long* grid) {
     }
     if (T < 1) T = 1;
     *tiles_per_cta = (int)T;
-    *grid = ceil_div(total, T);
+    *grid = ceil_div(total, T);                         // number of chunks
     return 0;
 }
 
@@ -386,8 +426,9 @@ extern "C" int cmf_conv3x3_c64_wgrad_usable(int N, int H, int W) {
 
 extern "C" size_t cmf_conv3x3_c64_wgrad_workspace(int N, int H, int W) {
     if (N <= 0 || H <= 0 || W <= 0) return 0;
-    int T; long long grid;
-    wgrad_plan(N, H, W, &T, &grid);
+    int T; long long chunks;
+    wgrad_plan(N, H, W, &T, &chunks);
+    const long long grid = chunks < kNumSMs ? chunks : kNumSMs;      // persistent: one partial per CTA
     return (size_t)grid * kTaps * kC * kC * sizeof(float);
 }
 
@@ -409,8 +450,8 @@ extern "C" int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const 
     P.N = N; P.H = H; P.W = W; P.HW = H * W;
     P.tiles_per_image = (int)ceil_div(P.HW, kTileM);
     P.total_tiles = (long long)N * P.tiles_per_image;
-    long long grid;
-    wgrad_plan(N, H, W, &P.tiles_per_cta, &grid);
+    wgrad_plan(N, H, W, &P.tiles_per_cta, &P.num_chunks);
+    const long long grid = P.num_chunks < kNumSMs ? P.num_chunks : kNumSMs;
     P.hl = (W + 4) & ~3;
     P.partial = workspace;
     const int pitch = (kTileM + P.hl + W + 1 <= 196) ? 196 : 228;
