@@ -131,7 +131,11 @@ __global__ void relu_mask_pack_kernel(long long total, int hw, const float* __re
 // the first TMA round trip (a third of a one-pair CTA's life) are paid once per SM.
 // kSeg = stages (K = 32 each) accumulated on the tensor core between two drains of the accumulator
 // into the FP32 registers; kStages % kSeg == 0, so segments never straddle tile pairs.
-template <int kPitch, int kSeg>
+// kFloatMask: the epilogue may be given the mask as float activations (cmf_conv3x3_c64_fused); the
+// step itself only uses packed sign bits, and keeping the 64-load float path out of that
+// instantiation keeps its code small (the kernel is sensitive to instruction-cache footprint:
+// +20 KB of specialised epilogues once cost 10 % of every launch).
+template <int kPitch, int kSeg, bool kFloatMask>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -233,18 +237,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             }
             asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&a_full[t][c])) : "memory");
         };
-        load_halo(0, 0, 0);
-        load_halo(0, 0, 1);
-        int k = 0;
-        for (int it = 0; it < nit; ++it) {
-            mbar_wait(&halo_go, k & 1); ++k;
-            load_halo(it, 1, 0);
-            load_halo(it, 1, 1);
-            if (it + 1 < nit) {
-                mbar_wait(&halo_go, k & 1); ++k;
-                load_halo(it + 1, 0, 0);
-                load_halo(it + 1, 0, 1);
-            }
+        // load s of this CTA: chunk (s & 1) of pair (s >> 1); load 0 needs no permission, load s >= 1
+        // waits for the producer's (s - 1)-th signal.  One call site (code footprint).
+        for (int s = 0; s < 2 * nit; ++s) {
+            if (s >= 1) mbar_wait(&halo_go, (s - 1) & 1);
+#pragma unroll 1
+            for (int t = 0; t < kTiles; ++t) load_halo(s >> 1, s & 1, t);
         }
     } else if (warp == 1 || warp == kMmaWarp1) {
         // ------------------------------------------------------------------ MMA issuers, one warp per tile
@@ -351,29 +349,32 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 tc_fence_before();
             };
             load_stage(0);
-            for (int s = 0; s < kStages; ++s) {
+            // One extra trip: iteration kStages only drains the pair's last segment, so the drain has a
+            // single call site (the kernel is sensitive to its instruction-cache footprint).
+            for (int s = 0; s <= kStages; ++s) {
                 const int gs = gs0 + s;
-                const int b = gs & 1;
-                float hi[32], lo[32];
+                if (s < kStages) {
+                    const int b = gs & 1;
+                    float hi[32], lo[32];
 #pragma unroll
-                for (int c = 0; c < kChunkC; ++c) {
-                    hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & 0xFFFFE000u);   // TF32 head, round to nearest
-                    lo[c] = v[c] - hi[c];                                                       // exact signed remainder
+                    for (int c = 0; c < kChunkC; ++c) {
+                        hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & 0xFFFFE000u);   // TF32 head, round to nearest
+                        lo[c] = v[c] - hi[c];                                                       // exact signed remainder
+                    }
+                    if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
+                    tc_fence_after();
+                    const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64) + lane_addr;
+                    tmem_st_32x32(stg, hi);
+                    tmem_st_32x32(stg + 32, lo);
+                    if (s + 1 < kStages) load_stage(s + 1);
+                    tmem_st_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&at_full[t][b]);
                 }
-                if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
-                tc_fence_after();
-                const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64) + lane_addr;
-                tmem_st_32x32(stg, hi);
-                tmem_st_32x32(stg + 32, lo);
-                if (s + 1 < kStages) load_stage(s + 1);
-                tmem_st_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&at_full[t][b]);
-                // drain one stage late (the last one at its own stage), so the tensor pipe already works
-                // on the next stage in the other accumulator
-                if (s > 0 && (gs % kSeg) == 0) drain(gs - 1);
-                if (s == kStages - 1) drain(gs);
+                // drain one stage late, so the tensor pipe already works on the next stage in the other
+                // accumulator; the pair's last segment right after its own stage
+                if (s > 0 && ((gs % kSeg) == 0 || s == kStages)) drain(gs - 1);
             }
             if (valid) {
                 const long long o = (long long)im * kC * hw + p;
@@ -394,7 +395,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                         const uint2 mb = __ldg(P.mask_bits + (long long)(im / P.mask_div) * hw + p);
                         keep_bits[0] = mb.x;
                         keep_bits[1] = mb.y;
-                    } else if (ms) {
+                    } else if (kFloatMask && ms) {
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
                             float mv[32];
@@ -493,18 +494,21 @@ static int conv_launch(int N, int H, int W, const float* x, const float* wsplit,
     static int seg_env = -1;
     if (seg_env < 0) { const char* e = getenv("CMF_CONV_SEG"); seg_env = e ? atoi(e) : 0; if (seg_env < 0 || seg_env > 3) seg_env = 0; }
     const int seg = seg_env ? seg_env : drain_stages;
-#define CMF_CONV_LAUNCH(PITCH, SEG)                                                                                   \
+#define CMF_CONV_LAUNCH(PITCH, SEG, FM)                                                                                   \
     do {                                                                                                               \
         static bool attr_set = false;                                                                                  \
         if (!attr_set) {                                                                                               \
-            cudaError_t e = cudaFuncSetAttribute(conv3x3_tc_kernel<PITCH, SEG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
+            cudaError_t e = cudaFuncSetAttribute(conv3x3_tc_kernel<PITCH, SEG, FM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
             if (e != cudaSuccess) { set_error("conv3x3 attr: %s", cudaGetErrorString(e)); return (int)e; }           \
             attr_set = true;                                                                                           \
         }                                                                                                              \
-        conv3x3_tc_kernel<PITCH, SEG><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);                     \
+        conv3x3_tc_kernel<PITCH, SEG, FM><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);                 \
     } while (0)
-    if (pitch == 192) { if (seg == 1) CMF_CONV_LAUNCH(192, 1); else if (seg == 2) CMF_CONV_LAUNCH(192, 2); else CMF_CONV_LAUNCH(192, 3); }
-    else { if (seg == 1) CMF_CONV_LAUNCH(256, 1); else if (seg == 2) CMF_CONV_LAUNCH(256, 2); else CMF_CONV_LAUNCH(256, 3); }
+    if (P.mask_src) {          // float mask: rare (tests, external callers); per-stage drain only
+        CMF_REQUIRE(seg == 1, "conv3x3: a float mask_src needs drain_stages == 1");
+        if (pitch == 192) CMF_CONV_LAUNCH(192, 1, true); else CMF_CONV_LAUNCH(256, 1, true);
+    } else if (pitch == 192) { if (seg == 1) CMF_CONV_LAUNCH(192, 1, false); else if (seg == 2) CMF_CONV_LAUNCH(192, 2, false); else CMF_CONV_LAUNCH(192, 3, false); }
+    else { if (seg == 1) CMF_CONV_LAUNCH(256, 1, false); else if (seg == 2) CMF_CONV_LAUNCH(256, 2, false); else CMF_CONV_LAUNCH(256, 3, false); }
 #undef CMF_CONV_LAUNCH
     CMF_CHECK_LAUNCH();
     return 0;

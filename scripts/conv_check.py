@@ -34,7 +34,16 @@ def bench(N, H, W, iters=10):
     ws = K.conv3x3_c64_prep(w, False)
     flops = 2.0 * N * 64 * 64 * 9 * H * W
     res = {}
-    for name, fn in (("tc", lambda: K.conv3x3_c64(x, ws, None)), ("cudnn", lambda: F.conv2d(x, w, None, padding=1))):
+    d = 65 if N % 65 == 0 else 1
+    prim = torch.randn(N // d, 64, H, W, device=dev)
+    bits = K.relu_mask_pack(prim)
+    skip = torch.randn(N, 64, H, W, device=dev)
+    for name, fn in (("tc", lambda: K.conv3x3_c64(x, ws, None)),
+                     ("tc+mask", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=d, mask_first=True)),
+                     ("tc+mask+res", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=d, mask_first=True, res=skip)),
+                     ("tc+mask+res+y2", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=d, res=skip, second=True)),
+                     ("tc drain2", lambda: K.conv3x3_c64(x, ws, None, drain=2)),
+                     ("cudnn", lambda: F.conv2d(x, w, None, padding=1))):
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
@@ -46,7 +55,7 @@ def bench(N, H, W, iters=10):
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / iters
         res[name] = ms
-        print(f"  {name:6s} N={N} {H}x{W}: {ms:.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s", flush=True)
+        print(f"  {name:15s} N={N} {H}x{W}: {ms:.3f} ms  {flops / ms / 1e9:.1f} TFLOP/s", flush=True)
     return res
 
 
