@@ -77,6 +77,38 @@ def test_cuda_path_matches_oracle_on_fresh_inputs(name, batch):
         assert_close(p.grad, params[key].grad, RTOL, atol=RTOL * scale, what=key)
 
 
+@pytest.mark.parametrize("name,batch", [("sphere_gij_d3", 64), ("hepmass_gij_d10_warm", 17), ("img8_gij_d8", 4)])
+def test_eval_ood_entry_matches_oracle(name, batch):
+    """The eval / OOD entry (`non_square.py:52-53,119-124`: ``elbo(x, ood=True)`` -> per-sample
+    ``likelihood`` and ``reconstruction-error``) and ``extract_latent`` (`:55-62`), in eval mode,
+    against the fp64 oracle on the same weights and inputs."""
+    g = load_golden(name)
+    case = dict(CASES[name], batch=batch)
+    density = build_product(g, "cpu")
+    filled = fill_state_dict(density.state_dict(), salt=5, gain=1.2)
+    density.load_state_dict(filled)
+    density = density.cuda().eval()
+    x = make_input(case) * 0.8
+    top = strip_wrappers(density)
+    head, depth = find_head(top)
+    xh = x.cuda()
+    node = top
+    for _ in range(depth):                       # push x through the elementwise nodes above the head
+        xh = node.bijection.x_to_z(xh)["z"]
+        node = node.prior
+    with torch.no_grad():
+        out = head("elbo", xh, ood=True)
+        z = head("extract-latent", xh)
+    params = {(k[7:] if k.startswith("module.") else k): (v.double() if v.is_floating_point() else v) for k, v in filled.items()}
+    flow = O.OracleFlow(g["schema"], params, case["x_shape"])
+    with torch.no_grad():
+        ref = flow.elbo(x.double(), ood=True, training=False)
+    assert set(out) >= {"likelihood", "reconstruction-error"}
+    assert_close(out["likelihood"], ref["likelihood"], RTOL, atol=1e-4, what="ood likelihood")
+    assert_close(out["reconstruction-error"], ref["reconstruction-error"], RTOL, atol=1e-6, what="ood reconstruction error")
+    assert_close(z, ref["z"], RTOL, atol=1e-6, what="extract_latent")
+
+
 def test_mnist_shape_properties_full_batch():
     """B = 50 (the reference's image batch), D = 784, d = 64: properties that need no oracle run.
     (i) G symmetric PSD with log det == 2 sum log diag chol (torch), (ii) J columns reproduce a
