@@ -1,2 +1,2 @@
 export PYTHONPATH=.
-timeout -k 10 300 python -m pytest tests/test_parity_gpu.py -x -q -m gpu -k "ood" 2>&1 | tail -15
+timeout -k 10 600 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -5

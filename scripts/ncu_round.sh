@@ -6,9 +6,9 @@ set -x
 python bench.py --steps 3 --warmup 3 > gpurun_out/${R}_bench.json 2> gpurun_out/${R}_bench.err || exit 1
 CMF_NCU_RANGE=1 timeout 1500 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
     --log-file gpurun_out/${R}_launches_step.csv python bench.py --only step --steps 1 --warmup 2 > gpurun_out/ncu1.log 2>&1
-timeout 100 python scripts/_one_conv.py || exit 1
+timeout 100 python scripts/one_conv.py || exit 1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv3x3_tc_kernel -s 2 -c 1 -f \
-    -o gpurun_out/${R}_conv_fwd_tangent python scripts/_one_conv.py > gpurun_out/ncu2.log 2>&1
+    -o gpurun_out/${R}_conv_fwd_tangent python scripts/one_conv.py > gpurun_out/ncu2.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv3x3_wgrad_tc_kernel -s 2 -c 1 -f \
-    -o gpurun_out/${R}_conv_wgrad_tangent python scripts/_one_conv.py > gpurun_out/ncu3.log 2>&1
+    -o gpurun_out/${R}_conv_wgrad_tangent python scripts/one_conv.py > gpurun_out/ncu3.log 2>&1
 ls -la gpurun_out/ | tail -12
