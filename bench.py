@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=50, help="per-GPU batch (reference default: config/images.py:131)")
     ap.add_argument("--scope-a-batch", type=int, default=512)
+    ap.add_argument("--large-batch", type=int, default=128,
+                    help="second operating point reported beside the metric (N = 1 only; 0 disables)")
     ap.add_argument("--cpu-sample", type=int, default=1, help="samples per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--only", default=None, choices=[None, "scope_a", "step", "profile"],
@@ -457,6 +459,38 @@ def run_own_arm(args, cfg, schema):
     peak_mem = torch.cuda.max_memory_allocated() / 2 ** 30
     barrier()
 
+    # Beside the headline (the reference's default batch of 50 per GPU): the same step at a batch that
+    # fills the device (SURVEY 8d lists a larger per-GPU batch as the second operating point).  Not the
+    # metric; one GPU only; 1 warm-up + 2 timed steps.
+    large = None
+    if rank == 0 and world == 1 and args.large_batch > B:
+        try:
+            torch.cuda.empty_cache()
+            torch.cuda.reset_peak_memory_stats()
+            BL = args.large_batch
+            xl = torch.randint(0, 256, (BL, *WORKLOAD["x_shape"])).float()
+            xl = (xl + torch.rand_like(xl)).to(dev)
+
+            def step_large():
+                bucket.zero()
+                train_metrics(inner, xl, 0)["loss"].backward()
+            step_large()
+            torch.cuda.synchronize()
+            a, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(2):
+                step_large()
+            b2.record()
+            torch.cuda.synchronize()
+            ms_l = a.elapsed_time(b2) / 2
+            large = {"per_gpu_batch": BL, "ms_per_step": ms_l, "samples_per_s": BL / (ms_l * 1e-3),
+                     "peak_mem_gib": torch.cuda.max_memory_allocated() / 2 ** 30}
+            del xl
+            torch.cuda.empty_cache()
+        except Exception as e:                                  # e.g. out of memory on a smaller part: say so
+            large = {"per_gpu_batch": args.large_batch, "error": f"{type(e).__name__}: {str(e)[:120]}"}
+            torch.cuda.empty_cache()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         step, cores = cpu_step_fn(cfg, schema, args.cpu_sample)
@@ -514,6 +548,8 @@ def run_own_arm(args, cfg, schema):
                                  "algorithmic_bytes_per_step": cb_bytes},
             "peak_mem_gib": peak_mem,
         }
+        if large is not None:
+            line["large_batch"] = large
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
