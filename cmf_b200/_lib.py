@@ -26,6 +26,7 @@ SIGNATURES = {
     "cmf_gather_rows": (_i, [_ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_gram_fwd": (_i, [_i, _i, _i, _vp, _vp, _i, _vp]),
     "cmf_gram_fwd_path": (_i, [_i, _i, _i, _vp, _vp, _i, _i, _vp]),
+    "cmf_gram_fwd2": (_i, [_i, _i, _i, _vp, _i, _vp, _vp, _i, _vp]),
     "cmf_gram_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "cmf_gram_bwd_path": (_i, [_i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "cmf_chol_logdet_fwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

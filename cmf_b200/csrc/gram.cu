@@ -239,7 +239,8 @@ gram_bwd_small_kernel(int d, int n, const float* __restrict__ V, const float* __
 
 // tensor-core path (gram_tc.cu)
 bool gram_tc_usable(int B, int d, int n, const float* V, const float* G);
-int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumulate, cudaStream_t stream);
+int gram_tc_fwd_launch(int B, int d, int n, const float* V, int n2, const float* V2, float* G, int accumulate,
+                       cudaStream_t stream);
 bool gram_tc_bwd_usable(int B, int d, int n, const float* V, const float* gG, const float* gV);
 int gram_tc_bwd_launch(int B, int d, int n, const float* V, const float* gG, float* gV, cudaStream_t stream);
 
@@ -261,7 +262,7 @@ extern "C" int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, 
         const bool ok = gram_tc_usable(B, d, n, V, G);
         CMF_REQUIRE(ok || path == CMF_GRAM_AUTO,
                     "gram_fwd: tensor-core path needs d >= 16, n >= 32, n %% 4 == 0 and 16-byte aligned V (d=%d n=%d)", d, n);
-        if (ok) return gram_tc_fwd_launch(B, d, n, V, G, accumulate, (cudaStream_t)stream);
+        if (ok) return gram_tc_fwd_launch(B, d, n, V, 0, nullptr, G, accumulate, (cudaStream_t)stream);
     }
     if (n == 0) {
         if (!accumulate) {
@@ -276,6 +277,18 @@ extern "C" int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, 
     gram_fwd_kernel<<<(unsigned)(B * ntiles), kGemmThreads, 0, (cudaStream_t)stream>>>(d, n, ntiles, V, G, accumulate);
     CMF_CHECK_LAUNCH();
     return 0;
+}
+
+extern "C" int cmf_gram_fwd2(int B, int d, int n1, const float* V1, int n2, const float* V2, float* G, int accumulate,
+                             cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && d >= 0 && n1 >= 0 && n2 >= 0, "gram_fwd2: negative size");
+    if (B == 0 || d == 0) return 0;
+    CMF_REQUIRE(G && (n1 == 0 || V1) && (n2 == 0 || V2), "gram_fwd2: null pointer");
+    if (n1 > 0 && n2 > 0 && gram_tc_usable(B, d, n1, V1, G) && gram_tc_usable(B, d, n2, V2, G))
+        return gram_tc_fwd_launch(B, d, n1, V1, n2, V2, G, accumulate, (cudaStream_t)stream);
+    int rc = cmf_gram_fwd_path(B, d, n1, V1, G, accumulate, CMF_GRAM_AUTO, stream);
+    if (rc != 0) return rc;
+    return cmf_gram_fwd_path(B, d, n2, V2, G, 1, CMF_GRAM_AUTO, stream);
 }
 
 extern "C" int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream) {

@@ -34,6 +34,7 @@ constexpr int kGsLd = kTile + 1;      // padded row of the epilogue staging tile
 
 struct GramTcParams {
     int B, d, n;
+    int n2;         // columns of the optional second block (0: none)
     int S;          // samples per panel (d <= 128) or 0 (d > 128)
     int T;          // 128-row tiles per sample (d > 128)
     int ntiles;     // T (T+1) / 2
@@ -57,7 +58,8 @@ struct GramTcParams {
 // separate 2-deep ring that only spans split -> MMA.  After the K loop the ring is reused as a
 // 128 x 129 staging tile so that G leaves the SM in coalesced rows (and mirrored rows).
 __global__ void __launch_bounds__(kGramTcThreads, 1)
-gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const GramTcParams P) {
+gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap2,
+                   const GramTcParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages];
     __shared__ __align__(8) uint64_t split_bar[2], lo_free[2], hh_full[2], hh_free[2], done_bar;
@@ -82,7 +84,10 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const GramTcParams 
         rowB = b0 * P.d + tc * kTile;
         same = (tr == tc);
     }
-    const int nk = (P.n + kKc - 1) / kKc;
+    // K loop over the columns of the first block, then (n2 > 0) of a second block of the same
+    // samples: G = V1 V1^T + V2 V2^T in one accumulation, one launch (the two halves of J^T)
+    const int nk1 = (P.n + kKc - 1) / kKc;
+    const int nk = nk1 + (P.n2 + kKc - 1) / kKc;
     const int nst = P.nstages;
     uint8_t* lo_ring = smem + (size_t)nst * P.raw_bytes;      // 2 x raw_bytes
 
@@ -100,6 +105,7 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const GramTcParams 
         mbar_init(&done_bar, 1);
         mbar_fence_init();
         prefetch_tmap(&tmap);
+        if (P.n2 > 0) prefetch_tmap(&tmap2);
     }
     if (warp == 1) tmem_alloc<kTmemCols>(&tmem_base_smem);
     tc_fence_before();
@@ -117,8 +123,10 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const GramTcParams 
                 mbar_wait(&empty_bar[s], ph ^ 1u);
                 uint8_t* st = smem + (size_t)s * P.raw_bytes;
                 mbar_arrive_expect_tx(&full_bar[s], tx);
-                tma_load_2d(st, &tmap, &full_bar[s], kc * kKc, rowA);
-                if (!same) tma_load_2d(st + kTileBytes, &tmap, &full_bar[s], kc * kKc, rowB);
+                const CUtensorMap* tm = kc < nk1 ? &tmap : &tmap2;
+                const int col = (kc < nk1 ? kc : kc - nk1) * kKc;
+                tma_load_2d(st, tm, &full_bar[s], col, rowA);
+                if (!same) tma_load_2d(st + kTileBytes, tm, &full_bar[s], col, rowB);
             }
         }
     } else if (warp == 1) {
@@ -327,9 +335,10 @@ bool gram_tc_usable(int B, int d, int n, const float* V, const float* G) {
            (long long)B * d < (1LL << 31);
 }
 
-int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumulate, cudaStream_t stream) {
+int gram_tc_fwd_launch(int B, int d, int n, const float* V, int n2, const float* V2, float* G, int accumulate,
+                       cudaStream_t stream) {
     GramTcParams P{};
-    P.B = B; P.d = d; P.n = n; P.G = G; P.accumulate = accumulate;
+    P.B = B; P.d = d; P.n = n; P.n2 = n2; P.G = G; P.accumulate = accumulate;
     long long grid;
     if (d <= kTile) {
         P.S = kTile / d; P.T = 1; P.ntiles = 1;
@@ -346,6 +355,11 @@ int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumu
     CUtensorMap tmap;
     int rc = make_tmap_2d_f32(&tmap, V, (uint64_t)B * d, (uint64_t)n, (uint64_t)n, (uint32_t)P.box_rows, 0);
     if (rc != 0) return rc;
+    CUtensorMap tmap2 = tmap;
+    if (n2 > 0) {
+        rc = make_tmap_2d_f32(&tmap2, V2, (uint64_t)B * d, (uint64_t)n2, (uint64_t)n2, (uint32_t)P.box_rows, 0);
+        if (rc != 0) return rc;
+    }
     const size_t smem = (size_t)(P.nstages + 2) * P.raw_bytes + 1024;     // raw ring + 2-deep lo ring
     static bool attr_set = false;
     if (!attr_set) {
@@ -353,7 +367,7 @@ int gram_tc_fwd_launch(int B, int d, int n, const float* V, float* G, int accumu
         if (e != cudaSuccess) { set_error("gram_tc attr: %s", cudaGetErrorString(e)); return (int)e; }
         attr_set = true;
     }
-    gram_tc_fwd_kernel<<<(unsigned)grid, kGramTcThreads, smem, stream>>>(tmap, P);
+    gram_tc_fwd_kernel<<<(unsigned)grid, kGramTcThreads, smem, stream>>>(tmap, tmap2, P);
     CMF_CHECK_LAUNCH();
     return 0;
 }

@@ -119,6 +119,23 @@ def gram_fwd(V: Tensor, G: Optional[Tensor] = None, path: str = "auto") -> Tenso
     return G
 
 
+def gram_fwd2(V1: Tensor, V2: Tensor, G: Optional[Tensor] = None) -> Tensor:
+    """G (B,d,d) (+)= V1 V1^T + V2 V2^T for two blocks (B,d,n1), (B,d,n2) of the same samples: one launch,
+    one accumulation over n1 + n2 columns when both qualify for the tcgen05 kernel."""
+    lib = _lib.load()
+    V1, V2 = _req(V1, "V1"), _req(V2, "V2")
+    B, d, n1 = V1.shape
+    if V2.shape[:2] != (B, d):
+        raise ValueError(f"gram_fwd2: blocks disagree: {tuple(V1.shape)} vs {tuple(V2.shape)}")
+    acc = G is not None
+    if G is None:
+        G = torch.empty(B, d, d, dtype=torch.float32, device=V1.device)
+    with torch.cuda.device(V1.device):
+        _lib.check(lib.cmf_gram_fwd2(B, d, n1, _ptr(V1), V2.shape[2], _ptr(V2), _ptr(G), int(acc), _stream()),
+                   "cmf_gram_fwd2")
+    return G
+
+
 def gram_bwd(V: Tensor, g_G: Tensor, path: str = "auto") -> Tensor:
     lib = _lib.load()
     V, g_G = _req(V, "V"), _req(g_G, "g_G")

@@ -100,8 +100,14 @@ class _Gram(Function):
     @staticmethod
     def forward(ctx, *blocks):
         G = None
-        for V in blocks:
-            G = kernels.gram_fwd(V, G)
+        i = 0
+        while i < len(blocks):                      # pairs of blocks share one launch
+            if i + 1 < len(blocks):
+                G = kernels.gram_fwd2(blocks[i], blocks[i + 1], G)
+                i += 2
+            else:
+                G = kernels.gram_fwd(blocks[i], G)
+                i += 1
         ctx.save_for_backward(*blocks)
         return G
 

@@ -91,6 +91,13 @@ int cmf_gram_fwd(int B, int d, int n, const float* V, float* G, int accumulate, 
 int cmf_gram_fwd_path(int B, int d, int n, const float* V, float* G, int accumulate, int path,
                       cmf_stream_t stream);
 
+/* Two blocks of the same samples in one pass: G[b] (+)= V1[b] V1[b]^T + V2[b] V2[b]^T, the sum over
+ * the layer blocks of non_square.py:307-308 for the usual two-block split of J^T.  One launch with
+ * one accumulation over the n1 + n2 columns when both blocks qualify for the tensor-core kernel
+ * (each as in CMF_GRAM_TC); otherwise the same result from two cmf_gram_fwd calls. */
+int cmf_gram_fwd2(int B, int d, int n1, const float* V1, int n2, const float* V2, float* G, int accumulate,
+                  cmf_stream_t stream);
+
 /* Adjoint: g_V[b] = (g_G[b] + g_G[b]^T) V[b]   (B,d,n). */
 int cmf_gram_bwd(int B, int d, int n, const float* V, const float* g_G, float* g_V, cmf_stream_t stream);
 /* CMF_GRAM_TC here: D[n,j] = sum_k V[k,n] S[k,j] with V as the MN-major tcgen05 operand (TMA,

@@ -66,6 +66,10 @@ def gram_fwd(V, G=None):
     return G
 
 
+def gram_fwd2(V1, V2, G=None):
+    return gram_fwd(V2, gram_fwd(V1, G))
+
+
 def gram_bwd(V, g_G):
     return (g_G + g_G.transpose(1, 2)) @ V
 
@@ -142,6 +146,6 @@ def conv3x3_c64_wgrad(x, g_y):
                                                (False, True, False))[1]
 
 
-ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_bwd",
+ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

@@ -145,6 +145,24 @@ def test_gram_tc_matches_fp64_and_fma(B, d, n):
     _close(g_tc, K.gram_bwd(Vd, gG.float().to(DEV), path="fma"), rtol=1e-5, what="g_V tc vs fma")
 
 
+@pytest.mark.parametrize("B,d,n1,n2", [(5, 64, 392, 392), (3, 64, 392, 40), (2, 200, 36, 260), (9, 48, 100, 32),
+                                       (3, 64, 392, 8), (2, 6, 12, 20), (4, 130, 64, 64)])
+def test_gram_two_blocks_in_one_launch(B, d, n1, n2):
+    """cmf_gram_fwd2: G = V1 V1^T + V2 V2^T (non_square.py:307-308 over two layer blocks) -- one tcgen05
+    launch over the n1 + n2 columns when both qualify (ragged last K chunk of either block), the
+    two-call fallback otherwise; also in accumulate mode"""
+    import cmf_b200.kernels as K
+    V1, V2 = _rand(B, d, n1, seed=21), _rand(B, d, n2, seed=22)
+    ref = E.gram_fwd(V1) + E.gram_fwd(V2)
+    G = K.gram_fwd2(V1.float().to(DEV), V2.float().to(DEV))
+    _close(G, ref, rtol=2e-6 * max(1, (n1 + n2) ** 0.5), what="G two blocks")
+    assert torch.equal(G, G.transpose(1, 2)), "G must be bitwise symmetric"
+    G0 = _rand(B, d, d, seed=23)
+    G0 = G0 + G0.transpose(1, 2)
+    Ga = K.gram_fwd2(V1.float().to(DEV), V2.float().to(DEV), G0.float().to(DEV))
+    _close(Ga, ref + G0, rtol=1e-5, what="G two blocks, accumulate")
+
+
 def test_gram_tc_badly_scaled_columns():
     """Trained CMF models drive most G_kk toward zero (SURVEY 7 hard parts): tangent rows scaled by
     10^-k must keep fp32-level relative accuracy element-wise against |v_i||v_j|."""
