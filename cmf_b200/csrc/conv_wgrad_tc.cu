@@ -128,6 +128,9 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             int gt = 0;
+            // x and g_y stream through once (1.3 GB per tangent-batch launch); the per-CTA partials
+            // that are re-read between chunks should be what stays in L2
+            const uint64_t pol = l2_policy_evict_first();
             for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x) {
                 long long tile_begin;
                 const int nt = chunk_tiles(ch, tile_begin);
@@ -137,10 +140,10 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     const int img = (int)(T / P.tiles_per_image), p0 = (int)(T % P.tiles_per_image) * kTileM;
                     if (gt >= 2) mbar_wait(&tile_done[buf], ((gt >> 1) - 1) & 1);
                     mbar_arrive_expect_tx(&x_full[buf], (uint32_t)kXBytes);
-                    tma_load_2d(xh + (size_t)buf * kXBytes, &tmx, &x_full[buf], p0 - P.hl, img * kC);
+                    tma_load_2d_hint(xh + (size_t)buf * kXBytes, &tmx, &x_full[buf], p0 - P.hl, img * kC, pol);
                     mbar_arrive_expect_tx(&g_full[buf], (uint32_t)(kSub * kBBytes));
                     for (int q = 0; q < kSub; ++q)
-                        tma_load_2d(gyhi + (size_t)(buf * kSub + q) * kBBytes, &tmg, &g_full[buf], p0 + 32 * q, img * kC);
+                        tma_load_2d_hint(gyhi + (size_t)(buf * kSub + q) * kBBytes, &tmg, &g_full[buf], p0 + 32 * q, img * kC, pol);
                 }
             }
         }
