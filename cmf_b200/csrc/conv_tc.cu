@@ -344,7 +344,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     float u[32];
                     tmem_ld_32x32(acc + h * 32, u);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) accr[h * 32 + j] += u[j];
+                    for (int j = 0; j < 32; j += 2) fadd2(accr[h * 32 + j], accr[h * 32 + j + 1], u[j], u[j + 1]);
                 }
                 tc_fence_before();
             };

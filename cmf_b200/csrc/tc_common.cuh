@@ -79,6 +79,17 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ---------------------------------------------------------------- packed FP32 (FADD2 on sm_100a)
+// Two IEEE round-to-nearest additions in one issue slot: same bits as the scalar form.
+__device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) {
+    asm("{\n .reg .b64 x, y;\n mov.b64 x, {%0,%1};\n mov.b64 y, {%2,%3};\n add.rn.f32x2 x, x, y;\n mov.b64 {%0,%1}, x;\n}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void fsub2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+    asm("{\n .reg .b64 x, y;\n mov.b64 x, {%2,%3};\n mov.b64 y, {%4,%5};\n sub.rn.f32x2 x, x, y;\n mov.b64 {%0,%1}, x;\n}"
+        : "=f"(d0), "=f"(d1) : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
