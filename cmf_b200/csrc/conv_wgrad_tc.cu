@@ -305,8 +305,21 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         hi[k] = tf32_head_rn(v);                                                                  \
         lo[k] = v - hi[k];                                                                        \
     }
-                    if (off == 0) { CMF_WG_SPLIT(0) } else if (off == 1) { CMF_WG_SPLIT(1) }
-                    else if (off == 2) { CMF_WG_SPLIT(2) } else { CMF_WG_SPLIT(3) }
+                    // taps with dx = 0 (a third of the stagings; off is then P.W-dependent only) need no
+                    // column mask: 3 of the 6 per-element operations go away
+#define CMF_WG_SPLIT_NOMASK(OFF)                                                                  \
+    _Pragma("unroll") for (int k = 0; k < 32; ++k) {                                              \
+        hi[k] = tf32_head_rn(wv[k + OFF]);                                                        \
+        lo[k] = wv[k + OFF] - hi[k];                                                              \
+    }
+                    if (dx == 0) {
+                        if (off == 0) { CMF_WG_SPLIT_NOMASK(0) } else if (off == 1) { CMF_WG_SPLIT_NOMASK(1) }
+                        else if (off == 2) { CMF_WG_SPLIT_NOMASK(2) } else { CMF_WG_SPLIT_NOMASK(3) }
+                    } else {
+                        if (off == 0) { CMF_WG_SPLIT(0) } else if (off == 1) { CMF_WG_SPLIT(1) }
+                        else if (off == 2) { CMF_WG_SPLIT(2) } else { CMF_WG_SPLIT(3) }
+                    }
+#undef CMF_WG_SPLIT_NOMASK
 #undef CMF_WG_SPLIT
                 } else {
 #pragma unroll
