@@ -300,8 +300,7 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     const uint32_t mb = dx < 0 ? mlq : (dx > 0 ? mrq : 0xffffffffu);
 #define CMF_WG_SPLIT(OFF)                                                                         \
     _Pragma("unroll") for (int k = 0; k < 32; ++k) {                                              \
-        const uint32_t keep = (uint32_t)((int32_t)(mb << (31 - k)) >> 31);                        \
-        const float v = __uint_as_float(__float_as_uint(wv[k + OFF]) & keep);                     \
+        const float v = (mb & (1u << k)) ? wv[k + OFF] : 0.f;                                     \
         hi[k] = tf32_head_rn(v);                                                                  \
         lo[k] = v - hi[k];                                                                        \
     }
