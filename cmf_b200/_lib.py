@@ -42,6 +42,7 @@ SIGNATURES = {
     "cmf_conv3x3_c64_wgrad_usable": (_i, [_i, _i, _i]),
     "cmf_conv3x3_c64_wgrad_workspace": (_sz, [_i, _i, _i]),
     "cmf_conv3x3_c64_wgrad": (_i, [_i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
+    "cmf_conv3x3_c64_wgrad_det": (_i, [_i, _i, _i, _vp, _vp, _vp, _i, _vp, _i, _vp]),
 }
 
 _lib = None

@@ -80,7 +80,7 @@ __device__ __forceinline__ int live_subchunks(int hw, int p0) {
     return n < kSub ? n : kSub;
 }
 
-template <int kPitch>
+template <int kPitch, bool kDet>
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_constant__ CUtensorMap tmg, WgradParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -150,19 +150,24 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
     } else if (warp == 1 || (warp == kMmaWarp1 && kIssuers == 2)) {
         // ------------------------------------------------------------------ MMA issuers
         // A single thread's issue path costs ~50 cycles per tcgen05.mma (240 MMAs per tile would
-        // take 1.5x the tensor time), so TWO warps issue: both walk EVERY staging -- each sees every
-        // phase of st_full, which the parity waits require -- and issuer w takes the K-steps
-        // {2w, 2w+1} of it.  Both add into the same accumulator; the accumulators are zeroed by the
-        // row workers up front, so no MMA depends on being first.
+        // take 1.5x the tensor time), so TWO warps issue.  Both walk EVERY staging -- each sees every
+        // phase of st_full / b_ready, which the parity waits require, and both commit st_done.
+        //   default: issuer w takes the K-steps {2w, 2w+1} of every staging.  Both add into the same
+        //     accumulator (zeroed by the row workers up front, so no MMA depends on being first); the
+        //     relative order of the two MMA streams, hence the truncation pattern of the FP32
+        //     accumulate, depends on timing: results are reproducible to 1-3 ulp, not bitwise.
+        //   kDet: issuer w issues whole stagings, those of the accumulators j with j % 2 == w (tap
+        //     pairs 0, 2, 4 / 1, 3).  Every accumulator sees ONE in-order MMA stream -- bitwise
+        //     reproducible -- and the chunk's first MMA into it overwrites it (no zero-fill pass).
+        //     A staging is released after 12 serially issued MMAs instead of 6: ~9 % slower.
         const int w = warp == 1 ? 0 : 1;
         constexpr uint32_t idesc = umma_idesc_tf32(kTileM, kC);
-        constexpr int kPer = 4 / kIssuers;
         const uint32_t gyhi_addr = smem_u32(gyhi), gylo_addr = smem_u32(gylo);
         int ns = 0, gt = 0, r = 0;
         for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x, ++r) {
         long long tile_begin;
         const int nt = chunk_tiles(ch, tile_begin);
-        mbar_wait(&acc_init, r & 1);            // the row workers have re-zeroed the accumulators for this chunk
+        mbar_wait(&acc_init, r & 1);            // the row workers have read (and, !kDet, re-zeroed) the accumulators
         tc_fence_after();
         for (int i = 0; i < nt; ++i, ++gt) {
             const int buf = gt & 1;
@@ -171,6 +176,7 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
             for (int n = 0; n < cnt; ++n, ++ns) {
                 const int q = n / kPairs, j = n - q * kPairs;
                 const int sb = ns % kStgBufs;
+                const bool mine = !kDet || kIssuers == 1 || (j & 1) == w;
                 if (j == 0) mbar_wait(&b_ready[q], gt & 1);
                 mbar_wait(&st_full[sb], (ns / kStgBufs) & 1);
                 tc_fence_after();
@@ -179,12 +185,16 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)(sb * 64), a_lo = a_hi + 32;
                     const uint64_t dbh = umma_desc_sw128(gyhi_addr + (uint32_t)((buf * kSub + q) * kBBytes));
                     const uint64_t dbl = umma_desc_sw128(gylo_addr + (uint32_t)(q * kBBytes));
+                    if (mine) {
+                        constexpr int kPer = kDet ? 4 : 4 / kIssuers;
 #pragma unroll
-                    for (int kk = 0; kk < kPer; ++kk) {
-                        const int k = w * kPer + kk;
-                        umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, 1);
-                        umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
-                        umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
+                        for (int kk = 0; kk < kPer; ++kk) {
+                            const int k = kDet ? kk : w * kPer + kk;
+                            // kDet: the chunk's first MMA into accumulator j overwrites it (q = 0 of the first tile is always live)
+                            umma_tf32_ts(acc, a_hi + k * 8, dbl + 2 * k, idesc, kDet ? (i | q | k) != 0 : 1);
+                            umma_tf32_ts(acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                            umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
+                        }
                     }
                     umma_commit(&st_done[sb]);
                     if (j == kPairs - 1) umma_commit(&qdone[q]);
@@ -246,13 +256,17 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
         for (long long ch = blockIdx.x; ch < P.num_chunks; ch += gridDim.x, ++r) {
         long long tile_begin;
         const int nt = chunk_tiles(ch, tile_begin);
-        {   // zero the five accumulators (group g: columns [160 g, 160 g + 160) of this warp's lane quarter)
-            float zero[32];
+        {   // the accumulators are free (their previous contents have been read by every worker warp);
+            // shared-accumulator issue: zero the five accumulators (group g: columns [160 g, 160 g + 160)
+            // of this warp's lane quarter)
+            if (!kDet) {
+                float zero[32];
 #pragma unroll
-            for (int k = 0; k < 32; ++k) zero[k] = 0.f;
+                for (int k = 0; k < 32; ++k) zero[k] = 0.f;
 #pragma unroll
-            for (int c = 0; c < 5; ++c) tmem_st_32x32(tmem_base + lane_addr + (uint32_t)(g * 160 + c * 32), zero);
-            tmem_st_wait();
+                for (int c = 0; c < 5; ++c) tmem_st_32x32(tmem_base + lane_addr + (uint32_t)(g * 160 + c * 32), zero);
+                tmem_st_wait();
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_init);
@@ -449,6 +463,11 @@ extern "C" size_t cmf_conv3x3_c64_wgrad_workspace(int N, int H, int W) {
 
 extern "C" int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const float* g_y, float* workspace,
                                      int accumulate, float* g_w, cmf_stream_t stream) {
+    return cmf_conv3x3_c64_wgrad_det(N, H, W, x, g_y, workspace, accumulate, g_w, 0, stream);
+}
+
+extern "C" int cmf_conv3x3_c64_wgrad_det(int N, int H, int W, const float* x, const float* g_y, float* workspace,
+                                         int accumulate, float* g_w, int deterministic, cmf_stream_t stream) {
     CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3_wgrad: negative size");
     CMF_REQUIRE(g_w, "conv3x3_wgrad: null g_w");
     if (N == 0 || H == 0 || W == 0) {
@@ -478,14 +497,20 @@ extern "C" int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const 
     const size_t smem = (size_t)3 * kSub * kBBytes + (size_t)2 * kC * pitch * 4 + 1024;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv3x3_wgrad_tc_kernel<196>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(conv3x3_wgrad_tc_kernel<228>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaError_t e = cudaSuccess;
+        const void* fns[4] = {(const void*)conv3x3_wgrad_tc_kernel<196, false>, (const void*)conv3x3_wgrad_tc_kernel<228, false>,
+                              (const void*)conv3x3_wgrad_tc_kernel<196, true>, (const void*)conv3x3_wgrad_tc_kernel<228, true>};
+        for (int f = 0; f < 4 && e == cudaSuccess; ++f)
+            e = cudaFuncSetAttribute(fns[f], cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (e != cudaSuccess) { set_error("conv3x3_wgrad attr: %s", cudaGetErrorString(e)); return (int)e; }
         attr_set = true;
     }
-    if (pitch == 196) conv3x3_wgrad_tc_kernel<196><<<(unsigned)grid, kWgThreads, smem, (cudaStream_t)stream>>>(tmx, tmg, P);
-    else conv3x3_wgrad_tc_kernel<228><<<(unsigned)grid, kWgThreads, smem, (cudaStream_t)stream>>>(tmx, tmg, P);
+    const dim3 g((unsigned)grid), b(kWgThreads);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (pitch == 196 && !deterministic) conv3x3_wgrad_tc_kernel<196, false><<<g, b, smem, st>>>(tmx, tmg, P);
+    else if (pitch == 196) conv3x3_wgrad_tc_kernel<196, true><<<g, b, smem, st>>>(tmx, tmg, P);
+    else if (!deterministic) conv3x3_wgrad_tc_kernel<228, false><<<g, b, smem, st>>>(tmx, tmg, P);
+    else conv3x3_wgrad_tc_kernel<228, true><<<g, b, smem, st>>>(tmx, tmg, P);
     CMF_CHECK_LAUNCH();
     conv_wgrad_reduce_kernel<<<(kTaps * kC * kC + 255) / 256, 256, 0, (cudaStream_t)stream>>>(workspace, (int)grid, accumulate, g_w);
     CMF_CHECK_LAUNCH();

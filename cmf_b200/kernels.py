@@ -300,16 +300,21 @@ def conv3x3_c64_wgrad_usable(N: int, H: int, W: int) -> bool:
     return bool(_lib.load().cmf_conv3x3_c64_wgrad_usable(int(N), int(H), int(W)))
 
 
-def conv3x3_c64_wgrad(x: Tensor, g_y: Tensor) -> Tensor:
-    """x, g_y (N,64,H,W) -> g_w (64,64,3,3) = weight gradient of ``conv2d(x, w, padding=1)``."""
+def conv3x3_c64_wgrad(x: Tensor, g_y: Tensor, deterministic: Optional[bool] = None) -> Tensor:
+    """x, g_y (N,64,H,W) -> g_w (64,64,3,3) = weight gradient of ``conv2d(x, w, padding=1)``.
+    ``deterministic``: bitwise run-to-run reproducible accumulation order (~9 % slower); None follows
+    ``torch.are_deterministic_algorithms_enabled()`` like aten's own convolution_backward."""
     lib = _lib.load()
     x, g_y = _req(x, "x"), _req(g_y, "g_y")
     N, C, H, W = x.shape
     assert C == 64 and g_y.shape == x.shape
+    if deterministic is None:
+        deterministic = torch.are_deterministic_algorithms_enabled()
     g_w = torch.empty(64, 64, 3, 3, dtype=torch.float32, device=x.device)
     nbytes = lib.cmf_conv3x3_c64_wgrad_workspace(N, H, W)
     ws = torch.empty(max(nbytes // 4, 1), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
-        _lib.check(lib.cmf_conv3x3_c64_wgrad(N, H, W, _ptr(x), _ptr(g_y), _ptr(ws), 0, _ptr(g_w), _stream()),
+        _lib.check(lib.cmf_conv3x3_c64_wgrad_det(N, H, W, _ptr(x), _ptr(g_y), _ptr(ws), 0, _ptr(g_w),
+                                                 int(bool(deterministic)), _stream()),
                    "cmf_conv3x3_c64_wgrad")
     return g_w

@@ -169,6 +169,14 @@ int cmf_conv3x3_c64_wgrad_usable(int N, int H, int W);
 size_t cmf_conv3x3_c64_wgrad_workspace(int N, int H, int W);
 int cmf_conv3x3_c64_wgrad(int N, int H, int W, const float* x, const float* g_y, float* workspace,
                           int accumulate, float* g_w, cmf_stream_t stream);
+/* Same with the reproducibility of the result chosen by the caller (what
+ * torch.use_deterministic_algorithms selects for aten::convolution_backward):
+ *   deterministic = 0  two MMA issuers share each accumulator; the order of their truncating FP32
+ *                      accumulations depends on timing: same inputs reproduce to 1-3 ulp (the
+ *                      default above; accuracy against FP64 is the same in both modes)
+ *   deterministic = 1  one in-order MMA stream per accumulator: bitwise reproducible, ~9 % slower */
+int cmf_conv3x3_c64_wgrad_det(int N, int H, int W, const float* x, const float* g_y, float* workspace,
+                              int accumulate, float* g_w, int deterministic, cmf_stream_t stream);
 
 /* Rational-quadratic spline coupling, inverse direction (z -> x), primal + d tangent columns.
  * Arithmetic of gitmodules/nsf/nde/transforms/splines/rational_quadratic.py:13-52,96-112 (linear

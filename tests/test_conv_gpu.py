@@ -191,6 +191,33 @@ def test_residual_stack_tangent_matches_autograd():
         assert _rel(a, b.double()) < 2e-5
 
 
+@pytest.mark.parametrize("N,H,W", [(1, 4, 8), (40, 28, 28), (330, 14, 14), (600, 28, 28)])
+def test_run_to_run_reproducibility(N, H, W):
+    """Forward / data gradient: fixed accumulation order (FP32 drains per segment), same bits every launch.
+    Weight gradient: bitwise with deterministic=True (one in-order MMA stream per accumulator, per-CTA
+    partials added chunk by chunk, fixed-order reduction), also when the persistent CTAs walk several
+    chunks; the default (two issuers sharing an accumulator) reproduces to a few ulp of the result's
+    scale and has the same accuracy against FP64."""
+    x, gy, w = _rand((N, 64, H, W), 31), _rand((N, 64, H, W), 32), _rand((64, 64, 3, 3), 33, 1 / 24)
+    ws, wt = K.conv3x3_c64_prep(w, False), K.conv3x3_c64_prep(w, True)
+    y0, gx0 = K.conv3x3_c64(x, ws), K.conv3x3_c64(gy, wt, drain=2)
+    gw_det, gw_fast = K.conv3x3_c64_wgrad(x, gy, deterministic=True), K.conv3x3_c64_wgrad(x, gy, deterministic=False)
+    ref = torch.ops.aten.convolution_backward(gy.double(), x.double(), w.double(), None, (1, 1), (1, 1), (1, 1), False,
+                                              (0, 0), 1, (False, True, False))[1]
+    assert _rel(gw_det, ref) < 2e-5 and _rel(gw_fast, ref) < 2e-5     # measured 2e-6 (N = 40) .. 1.1e-5 (N = 3200)
+    for _ in range(5):
+        assert torch.equal(K.conv3x3_c64(x, ws), y0)
+        assert torch.equal(K.conv3x3_c64(gy, wt, drain=2), gx0)
+        assert torch.equal(K.conv3x3_c64_wgrad(x, gy, deterministic=True), gw_det)
+        assert _rel(K.conv3x3_c64_wgrad(x, gy, deterministic=False), gw_fast.double()) < 2e-6
+    with torch.random.fork_rng():
+        torch.use_deterministic_algorithms(True)
+        try:
+            assert torch.equal(K.conv3x3_c64_wgrad(x, gy), gw_det)      # None follows torch's global switch
+        finally:
+            torch.use_deterministic_algorithms(False)
+
+
 def test_unsupported_shapes_are_rejected():
     assert not K.conv3x3_c64_usable(1, 7, 7)        # H*W % 4 != 0: TMA row stride not 16-byte aligned
     assert not K.conv3x3_c64_usable(1, 64, 64)      # halo box wider than 256 pixels
