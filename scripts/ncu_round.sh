@@ -1,6 +1,6 @@
 #!/bin/bash
 # plain run first (must exit 0), then the launch list of one step, then full captures of the two conv kernels
-R=${1:-r01e}
+R=${1:-r01f}
 export PYTHONPATH=.
 set -x
 python bench.py --steps 3 --warmup 3 > gpurun_out/${R}_bench.json 2> gpurun_out/${R}_bench.err || exit 1
