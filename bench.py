@@ -531,9 +531,9 @@ def run_own_arm(args, cfg, schema):
                          "bound": "tensor", "achieved": conv["conv3x3_tc_kernel"]["tflops"],
                          "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
                          "frac": conv["conv3x3_tc_kernel"]["tflops"] / peaks["bf16_tflops"],
-                         "traffic": 1260242176, "peak_source": peak_kind,
+                         "traffic": 1260095232, "peak_source": peak_kind,
                          "traffic_note": "dram read+write of ONE launch on the tangent batch (3250x64x28x28) from ncu "
-                                         "--set full (profiles/r01d_conv_fwd_tangent_raw.csv); algorithmic 1304.6 MB",
+                                         "--set full (profiles/r01f_conv_fwd_tangent_raw.csv); algorithmic 1304.6 MB",
                          "note": "FP32-accurate 3xTF32: kind::tf32 runs at half the bf16 rate and each product "
                                  "takes 3 MMAs, so the ceiling of this arithmetic is 1/6 of the bf16 peak",
                          "frac_of_3xtf32_ceiling": 6.0 * conv["conv3x3_tc_kernel"]["tflops"] / peaks["bf16_tflops"],
