@@ -331,8 +331,13 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 if (tap == 0) mbar_wait(&a_full[t][chunk], it & 1);
                 const uint32_t src = row_addr + (uint32_t)((chunk * kHaloElems + dy * P.W + dx) * 4);
                 const bool ok = (okbits >> tap) & 1u;
+                if (__all_sync(0xffffffffu, ok)) {      // interior rows: no zero-fill, no predicates
 #pragma unroll
-                for (int c = 0; c < kChunkC; ++c) v[c] = ok ? ld_shared_f32(src + (uint32_t)(c * kPitch * 4)) : 0.f;
+                    for (int c = 0; c < kChunkC; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
+                } else {
+#pragma unroll
+                    for (int c = 0; c < kChunkC; ++c) v[c] = ok ? ld_shared_f32(src + (uint32_t)(c * kPitch * 4)) : 0.f;
+                }
             };
             // drain the accumulator of the segment that ended with global stage e into the FP32 registers
             auto drain = [&](int e) {
