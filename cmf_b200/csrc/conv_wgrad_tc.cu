@@ -313,17 +313,20 @@ conv3x3_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmx, const __grid_co
                     for (int qq = 1; qq < kSub; ++qq) { if (q == qq) { mlq = ml[qq]; mrq = mr[qq]; } }
                     const uint32_t mb = dx < 0 ? mlq : (dx > 0 ? mrq : 0xffffffffu);
 #define CMF_WG_SPLIT(OFF)                                                                         \
-    _Pragma("unroll") for (int k = 0; k < 32; ++k) {                                              \
-        const float v = (mb & (1u << k)) ? wv[k + OFF] : 0.f;                                     \
-        hi[k] = tf32_head_rn(v);                                                                  \
-        lo[k] = v - hi[k];                                                                        \
+    _Pragma("unroll") for (int k = 0; k < 32; k += 2) {                                           \
+        const float v0 = (mb & (1u << k)) ? wv[k + OFF] : 0.f;                                    \
+        const float v1 = (mb & (2u << k)) ? wv[k + 1 + OFF] : 0.f;                                \
+        hi[k] = tf32_head_rn(v0);                                                                 \
+        hi[k + 1] = tf32_head_rn(v1);                                                             \
+        fsub2(lo[k], lo[k + 1], v0, v1, hi[k], hi[k + 1]);                                        \
     }
                     // taps with dx = 0 (a third of the stagings; off is then P.W-dependent only) need no
                     // column mask: 3 of the 6 per-element operations go away
 #define CMF_WG_SPLIT_NOMASK(OFF)                                                                  \
-    _Pragma("unroll") for (int k = 0; k < 32; ++k) {                                              \
+    _Pragma("unroll") for (int k = 0; k < 32; k += 2) {                                           \
         hi[k] = tf32_head_rn(wv[k + OFF]);                                                        \
-        lo[k] = wv[k + OFF] - hi[k];                                                              \
+        hi[k + 1] = tf32_head_rn(wv[k + 1 + OFF]);                                                \
+        fsub2(lo[k], lo[k + 1], wv[k + OFF], wv[k + 1 + OFF], hi[k], hi[k + 1]);                  \
     }
                     if (dx == 0) {
                         if (off == 0) { CMF_WG_SPLIT_NOMASK(0) } else if (off == 1) { CMF_WG_SPLIT_NOMASK(1) }
