@@ -43,6 +43,7 @@ def bench(N, H, W, iters=10):
                      ("tc+mask+res", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=d, mask_first=True, res=skip)),
                      ("tc+mask+res+y2", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=d, res=skip, second=True)),
                      ("tc drain2", lambda: K.conv3x3_c64(x, ws, None, drain=2)),
+                     ("tc drain3", lambda: K.conv3x3_c64(x, ws, None, drain=3)),
                      ("cudnn", lambda: F.conv2d(x, w, None, padding=1))):
         for _ in range(3):
             fn()
