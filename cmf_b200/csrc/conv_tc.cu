@@ -363,7 +363,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     float hi[32], lo[32];
 #pragma unroll
                     for (int c = 0; c < kChunkC; ++c) {
-                        hi[c] = __uint_as_float((__float_as_uint(v[c]) + 0x1000u) & 0xFFFFE000u);   // TF32 head, round to nearest
+                        // TF32 head: round to nearest where the result feeds the metric (kSeg == 1); the
+                        // gradient launches (kSeg >= 2) truncate -- one operation less, the remainder then
+                        // loses 2 of its 13 bits in the tensor core (2^-21 |x| instead of 2^-22)
+                        hi[c] = __uint_as_float((__float_as_uint(v[c]) + (kSeg == 1 ? 0x1000u : 0u)) & 0xFFFFE000u);
                         lo[c] = v[c] - hi[c];                                                       // exact signed remainder
                     }
                     if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
