@@ -23,6 +23,9 @@ SIGNATURES = {
     "cmf_coupling_jvp_bwd_workspace": (_sz, [_i, _i, _i, _i]),
     "cmf_coupling_jvp_bwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                   _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "cmf_coupling_jvp_bwd_static_max_bytes": (_sz, []),
+    "cmf_coupling_jvp_bwd_static": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                                         _vp, _vp, _vp, _vp, _vp]),
     "cmf_gather_rows": (_i, [_ll, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_gram_fwd": (_i, [_i, _i, _i, _vp, _vp, _i, _vp]),
     "cmf_gram_fwd_path": (_i, [_i, _i, _i, _vp, _vp, _i, _i, _vp]),

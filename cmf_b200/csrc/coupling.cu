@@ -8,6 +8,8 @@
 // from registers for every column; consecutive lanes touch consecutive 16-byte words of every
 // stream (fully coalesced).  The mapped (checkerboard / permuted) variant does the same with
 // 32-bit accesses, reading conditioner outputs through the int32 index map.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cmf {
@@ -406,4 +408,73 @@ extern "C" int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
         CMF_CHECK_LAUNCH();
     }
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of cmf_coupling_jvp_bwd (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture,
+// tight serving loops).  The tangent-chunk partials (A, C) live in a file-scope device array of a
+// fixed, modest size that every GPU loading this library holds until exit.  All calls share it:
+// calls that overlap on the GPU (two streams, two host threads) race on it.  Nothing in it has to
+// start at zero -- every partial that coupling_bwd_finalize reads is written by the same call's
+// first kernel -- so the contents left by the previous call are simply overwritten.
+// ------------------------------------------------------------------------------------------------
+namespace cmf {
+constexpr size_t kStaticScratchBytes = CMF_COUPLING_BWD_STATIC_MAX_BYTES;
+static __device__ __align__(256) float g_coupling_bwd_scratch[kStaticScratchBytes / sizeof(float)];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_scratch_mu;
+static float* g_scratch_ptr[kMaxDevices] = {};
+
+// Device address of the scratch array on the CURRENT device.  In host code the symbol's name is only
+// a host-side stand-in; the address a kernel may use comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static int static_scratch(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        set_error("coupling_bwd_static: cudaGetDevice: %s", cudaGetErrorString(e));
+        return (int)e;
+    }
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("coupling_bwd_static: device ordinal %d out of range (max %d)", dev, kMaxDevices - 1);
+        return -1;
+    }
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    if (g_scratch_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_coupling_bwd_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("coupling_bwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : -1;
+        }
+        g_scratch_ptr[dev] = p;
+    }
+    *out = g_scratch_ptr[dev];
+    return 0;
+}
+}  // namespace cmf
+
+extern "C" size_t cmf_coupling_jvp_bwd_static_max_bytes(void) { return kStaticScratchBytes; }
+
+extern "C" int cmf_coupling_jvp_bwd_static(int B, int d, int M, int Q,
+                                           const float* z_m, const float* V_m,
+                                           const float* st, const float* ST,
+                                           const int32_t* map, const int32_t* inv,
+                                           const float* g_x, const float* g_V,
+                                           float* g_z, float* g_Vin, float* g_st, float* g_ST,
+                                           cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && d >= 0 && M >= 0 && Q >= M, "coupling_bwd_static: bad sizes B=%d d=%d M=%d Q=%d", B, d, M, Q);
+    const size_t need = cmf_coupling_jvp_bwd_workspace(B, d, M, Q);
+    CMF_REQUIRE(need <= kStaticScratchBytes,
+                "coupling_bwd_static: B=%d d=%d M=%d Q=%d needs %zu bytes of scratch, the static array holds %zu "
+                "(use cmf_coupling_jvp_bwd with a caller-provided workspace)", B, d, M, Q, need, kStaticScratchBytes);
+    float* ws = nullptr;
+    if (need > 0) {
+        const int rc = static_scratch(&ws);
+        if (rc != 0) return rc;
+    }
+    return cmf_coupling_jvp_bwd(B, d, M, Q, z_m, V_m, st, ST, map, inv, g_x, g_V, g_z, g_Vin, g_st, g_ST,
+                                ws, need > 0 ? kStaticScratchBytes : 0, stream);
 }

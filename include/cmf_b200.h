@@ -67,6 +67,26 @@ int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
                          float* g_z, float* g_Vin, float* g_st, float* g_ST,
                          void* workspace, size_t workspace_bytes, cmf_stream_t stream);
 
+/* Allocation-free variant of cmf_coupling_jvp_bwd.  It has NO counterpart in the reference: it was
+ * added for callers that cannot call cudaMalloc (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results
+ * as cmf_coupling_jvp_bwd minus the workspace: the tangent-chunk partials live in a file-scope
+ * `static __device__` array of CMF_COUPLING_BWD_STATIC_MAX_BYTES that every GPU loading the library
+ * holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine).  Sizes whose cmf_coupling_jvp_bwd_workspace(B,d,M,Q) exceeds the array are rejected
+ * (return < 0, cmf_last_error_string says how many bytes were needed).  ALL calls share the one
+ * array per GPU and it keeps the previous call's contents (nothing in it needs to start at zero:
+ * every partial read is written first by the same call): calls that overlap on the GPU -- two
+ * streams, two host threads -- race.  The MNIST-shape layer (B=50, d=64, M=Q=392) needs 2.4 MiB. */
+#define CMF_COUPLING_BWD_STATIC_MAX_BYTES (4u << 20)
+size_t cmf_coupling_jvp_bwd_static_max_bytes(void);
+int cmf_coupling_jvp_bwd_static(int B, int d, int M, int Q,
+                                const float* z_m, const float* V_m,
+                                const float* st, const float* ST, const int32_t* map, const int32_t* inv,
+                                const float* g_x, const float* g_V,
+                                float* g_z, float* g_Vin, float* g_st, float* g_ST,
+                                cmf_stream_t stream);
+
 /* Index maps folded into addressing: out[r, i] = idx[i] < 0 ? 0 : cat(in0, in1)[r, idx[i]].
  * Replaces the zero-pad / permute / squeeze / split copies of non_square.py:397-410,
  * split.py:26-30,50-52, reshaping.py:28-29,102-114 and the mask*z products of acl.py:54.
