@@ -53,6 +53,7 @@ def get_config(dataset: str, model: str = "non-square", use_baseline: bool = Fal
             "regularization_param": 1, "log_jacobian_method": "cholesky", "latent_dimension": 2,
             "likelihood_warmup": False, "likelihood_warmup_start": 500, "likelihood_warmup_end": 1000,
             "prior": "affine",
+            "vis_log_prob_min": -3, "vis_log_prob_max": -1,      # plotting only (config/two_d.py); carried for key parity
         }
     elif group == "tabular":
         d, bs = TABULAR[dataset]
@@ -66,6 +67,9 @@ def get_config(dataset: str, model: str = "non-square", use_baseline: bool = Fal
             "hutchinson_distribution": "normal", "hutchinson_samples": 1, "latent_dimension": d,
             "likelihood_warmup": True, "likelihood_warmup_start": 25, "likelihood_warmup_end": 50,
             "prior": "realnvp", "prior_num_density_layers": 5, "prior_hidden_channels": [32] * 2,
+            # not on the hot path (batch norm is off, FID is evaluation); carried so the dict equals the reference's
+            "prior_batch_norm": False, "batch_norm_use_running_averages": False, "batch_norm_apply_affine": True,
+            "smaller_realnvp": False, "use_fid": True, "num_fid_samples": 10000,
         }
     else:
         cfg = {
@@ -81,6 +85,10 @@ def get_config(dataset: str, model: str = "non-square", use_baseline: bool = Fal
             "prior": "realnvp", "prior_num_density_layers": 10, "prior_hidden_channels": [32] * 4,
             "logit_tf_lambda": 1e-6 if dataset in ("mnist", "fashion-mnist") else 0.05,
             "logit_tf_scale": 256,
+            # not on the hot path; carried so the dict equals the reference's (config/images.py:120-178)
+            "prior_batch_norm": False, "batch_norm_use_running_averages": True, "batch_norm_momentum": 0.1,
+            "batch_norm_apply_affine": True, "test_metric": False, "use_fid": True, "num_fid_samples": 10000,
+            "fid_dims": 2048,
         }
     return {"model": model, "dataset": dataset, **_HEAD_COMMON, **cfg}
 

@@ -549,11 +549,11 @@ extern "C" int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float
     }
     const int tps = pick_tps(d), spb = kCholThreads / tps;
     const size_t smem = ((size_t)spb * d * (d + 1) + kCholThreads + spb) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(chol_logdet_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) { set_error("chol_fwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     chol_logdet_fwd_kernel<<<(unsigned)ceil_div(B, spb), kCholThreads, smem, (cudaStream_t)stream>>>(
         B, d, tps, G, L, logdet, l1_off, l1_diag, info);
@@ -587,11 +587,11 @@ extern "C" int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
     }
     const int tps = pick_tps(d), spb = kCholThreads / tps;
     const size_t smem = (size_t)spb * 2 * d * (d + 1) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(chol_logdet_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) { set_error("chol_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     chol_logdet_bwd_kernel<<<(unsigned)ceil_div(B, spb), kCholThreads, smem, (cudaStream_t)stream>>>(
         B, d, tps, L, G, g_logdet, g_l1, penalty, g_G);

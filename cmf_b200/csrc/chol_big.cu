@@ -286,11 +286,11 @@ using namespace cmf;
 int chol_big_fwd_launch(int B, int d, const float* G, float* L, float* logdet, float* l1_off, float* l1_diag,
                         int32_t* info, cudaStream_t stream) {
     const size_t smem = ((size_t)kNb * kPld + (size_t)max(d - kNb, 1) * kPld) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(chol_big_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) { set_error("chol_big_fwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     chol_big_fwd_kernel<<<(unsigned)B, kBigThreads, smem, stream>>>(d, G, L, logdet, l1_off, l1_diag, info);
     CMF_CHECK_LAUNCH();
@@ -300,11 +300,11 @@ int chol_big_fwd_launch(int B, int d, const float* G, float* L, float* logdet, f
 int chol_big_bwd_launch(int B, int d, const float* L, const float* G, const float* g_logdet, const float* g_l1,
                         int penalty, float* g_G, cudaStream_t stream) {
     const size_t smem = ((size_t)2 * kNb * kPld + (size_t)d * kPld) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(chol_big_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) { set_error("chol_big_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     dim3 grid((unsigned)B, (unsigned)ceil_div(d, kNb));
     chol_big_bwd_kernel<<<grid, kBigThreads, smem, stream>>>(d, L, G, g_logdet, g_l1, penalty, g_G);

@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+
 #include "../../include/cmf_b200.h"
 
 namespace cmf {
@@ -43,6 +45,21 @@ __device__ __forceinline__ float warp_sum(float v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
+
+// "already configured on this device" flag: function attributes (the opt-in to > 48 KB of dynamic
+// shared memory) are per device, so one process launching on a second GPU must set them there too.
+struct DeviceOnce {
+    std::atomic<unsigned long long> mask{0};
+    static int current() { int d = -1; cudaGetDevice(&d); return d; }
+    bool done() const {
+        const int d = current();
+        return d >= 0 && d < 64 && ((mask.load(std::memory_order_acquire) >> d) & 1ull);
+    }
+    void mark() {
+        const int d = current();
+        if (d >= 0 && d < 64) mask.fetch_or(1ull << d, std::memory_order_release);
+    }
+};
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -504,11 +504,11 @@ static int conv_launch(int N, int H, int W, const float* x, const float* wsplit,
     const int seg = seg_env ? seg_env : drain_stages;
 #define CMF_CONV_LAUNCH(PITCH, SEG, FM)                                                                                   \
     do {                                                                                                               \
-        static bool attr_set = false;                                                                                  \
-        if (!attr_set) {                                                                                               \
+        static DeviceOnce attr_set;                                                                                  \
+        if (!attr_set.done()) {                                                                                               \
             cudaError_t e = cudaFuncSetAttribute(conv3x3_tc_kernel<PITCH, SEG, FM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
             if (e != cudaSuccess) { set_error("conv3x3 attr: %s", cudaGetErrorString(e)); return (int)e; }           \
-            attr_set = true;                                                                                           \
+            attr_set.mark();                                                                                           \
         }                                                                                                              \
         conv3x3_tc_kernel<PITCH, SEG, FM><<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(tmw, P);                 \
     } while (0)

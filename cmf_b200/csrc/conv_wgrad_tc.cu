@@ -505,15 +505,15 @@ extern "C" int cmf_conv3x3_c64_wgrad_det(int N, int H, int W, const float* x, co
     rc = make_tmap_2d_f32(&tmg, g_y, (uint64_t)N * kC, (uint64_t)P.HW, (uint64_t)P.HW, kC, 0);
     if (rc != 0) return rc;
     const size_t smem = (size_t)3 * kSub * kBBytes + (size_t)2 * kC * pitch * 4 + 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaSuccess;
         const void* fns[4] = {(const void*)conv3x3_wgrad_tc_kernel<196, false>, (const void*)conv3x3_wgrad_tc_kernel<228, false>,
                               (const void*)conv3x3_wgrad_tc_kernel<196, true>, (const void*)conv3x3_wgrad_tc_kernel<228, true>};
         for (int f = 0; f < 4 && e == cudaSuccess; ++f)
             e = cudaFuncSetAttribute(fns[f], cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
         if (e != cudaSuccess) { set_error("conv3x3_wgrad attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     const dim3 g((unsigned)grid), b(kWgThreads);
     cudaStream_t st = (cudaStream_t)stream;

@@ -309,11 +309,11 @@ extern "C" int cmf_gram_bwd_path(int B, int d, int n, const float* V, const floa
         if (ok && (path == CMF_GRAM_TC || d > 64)) return gram_tc_bwd_launch(B, d, n, V, g_G, g_V, (cudaStream_t)stream);
     }
     if (d <= kSmallD && n % 4 == 0 && aligned16(V) && aligned16(g_V) && B <= 65535 * 32) {
-        static bool attr_set = false;
-        if (!attr_set) {
+        static DeviceOnce attr_set;
+        if (!attr_set.done()) {
             cudaError_t e = cudaFuncSetAttribute(gram_bwd_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallSmem);
             if (e != cudaSuccess) { set_error("gram_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-            attr_set = true;
+            attr_set.mark();
         }
         // split a sample's chunks over several CTAs while the grid is below ~2 CTAs per SM
         const int nchunks = (int)ceil_div(n, kChunkN);

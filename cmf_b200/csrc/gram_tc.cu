@@ -361,11 +361,11 @@ int gram_tc_fwd_launch(int B, int d, int n, const float* V, int n2, const float*
         if (rc != 0) return rc;
     }
     const size_t smem = (size_t)(P.nstages + 2) * P.raw_bytes + 1024;     // raw ring + 2-deep lo ring
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(gram_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) { set_error("gram_tc attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     gram_tc_fwd_kernel<<<(unsigned)grid, kGramTcThreads, smem, stream>>>(tmap, tmap2, P);
     CMF_CHECK_LAUNCH();
@@ -581,11 +581,11 @@ int gram_tc_bwd_launch(int B, int d, int n, const float* V, const float* gG, flo
     rc = make_tmap_2d_plain_f32(&tmapY, gG, (uint64_t)B * d, (uint64_t)d, (uint64_t)d, (uint32_t)P.N, 32);
     if (rc != 0) return rc;
     const size_t smem = (size_t)P.nstages * P.stage_bytes + 1024;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static DeviceOnce attr_set;
+    if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(gram_tc_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) { set_error("gram_tc_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-        attr_set = true;
+        attr_set.mark();
     }
     gram_tc_bwd_kernel<<<(unsigned)grid, kBwdThreads, smem, stream>>>(tmap, tmapX, tmapY, P);
     CMF_CHECK_LAUNCH();

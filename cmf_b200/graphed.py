@@ -71,6 +71,10 @@ class GraphedTrainStep:
         graph, static_x, static_loss, infos, _ = entry
         static_x.copy_(x)
         graph.replay()
+        for p in self.bucket.params:                  # the replay wrote bucket.flat: an optimizer's
+            if p.grad is None:                        # zero_grad(set_to_none=True) must not hide it
+                self.bucket.sync_aliases_after_replay()
+                break
         if infos and int(torch.stack([i.view(()) for i in infos]).max().item()):
             self.eager_fallbacks += 1                 # not PD: eager path replays the retry loop
             return self._eager(x, epoch)

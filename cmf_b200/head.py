@@ -17,6 +17,7 @@ import torch
 from . import ops
 from .cg import linear_cg_batched
 from .densities import Density
+from .networks import library_convs
 from .program import LayerProgram
 
 Tensor = torch.Tensor
@@ -204,7 +205,14 @@ class FusedNonSquareHeadDensity(Density):
             blocks, _ = self.program.run(lat, vec.unsqueeze(1).contiguous())
             with torch.enable_grad():
                 lat_p = lat if lat.requires_grad else lat.detach().requires_grad_(True)
-                prim, _ = self.program.run(lat_p, None)
+                if create_graph:
+                    # this VJP is differentiated again by loss.backward(): the primal coupling / gather
+                    # ops record their adjoints (ops._CouplingPrimalVJP); the conditioner convolutions
+                    # take the library path, which autograd can differentiate twice
+                    with library_convs():
+                        prim, _ = self.program.run(lat_p, None)
+                else:
+                    prim, _ = self.program.run(lat_p, None)
                 outs = [xb for _, xb, _ in prim]
                 cots = [Vb[:, 0] for _, _, Vb in blocks]
                 (res,) = torch.autograd.grad(outs, lat_p, cots, create_graph=create_graph)

@@ -30,12 +30,31 @@ _TC_CONV = os.environ.get("CMF_CONV", "tc") != "cudnn"
 _BWD_DRAIN = 2
 
 
+class library_convs:
+    """Inside this context every conditioner convolution is the library call ``F.conv2d`` (which
+    autograd can differentiate twice).  Used for the primal run whose VJP is itself differentiated
+    (`non_square.py:199`, ``create_graph=True`` of hutch_with_cg): the tcgen05 convolution ops carry
+    first-order adjoints only."""
+    depth = 0
+
+    def __enter__(self):
+        library_convs.depth += 1
+
+    def __exit__(self, *exc):
+        library_convs.depth -= 1
+        return False
+
+
+def _tc_conv_enabled() -> bool:
+    return _TC_CONV and library_convs.depth == 0
+
+
 def _conv3x3_pair(conv: nn.Conv2d, h: Tensor, Hv):
     """``conv(h)`` and the bias-free tangent push ``conv.weight * Hv`` (`jvp_layers.py:49-64`).
     64 -> 64 channel 3x3 convolutions run on the tcgen05 kernel (weights pre-split once for both
     calls); other shapes are library calls."""
     from . import kernels, ops
-    if _TC_CONV and ops.conv3x3_c64_usable(h, conv.weight):
+    if _tc_conv_enabled() and ops.conv3x3_c64_usable(h, conv.weight):
         ws = kernels.conv3x3_c64_prep(conv.weight.detach(), False)
         y = ops.conv3x3_c64(h, conv.weight, conv.bias, ws)
         if Hv is not None and ops.conv3x3_c64_usable(Hv, conv.weight):
@@ -164,7 +183,7 @@ def _residual_stack_jvp(blocks, h: Tensor, Hv: Tensor, d: int):
     """primal (autograd, per block) + tangents (one fused node) through consecutive residual blocks"""
     from . import kernels
     N, _, H, W = Hv.shape
-    fused = (_TC_CONV and all(b.conv1.weight.shape == (64, 64, 3, 3) for b in blocks) and Hv.shape[1] == 64
+    fused = (_tc_conv_enabled() and all(b.conv1.weight.shape == (64, 64, 3, 3) for b in blocks) and Hv.shape[1] == 64
              and kernels.conv3x3_c64_usable(N, H, W) and kernels.conv3x3_c64_wgrad_usable(N, H, W))
     if not fused:
         for b in blocks:

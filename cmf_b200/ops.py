@@ -2,9 +2,13 @@
 C ABI).  These are the only places the hot path touches the GPU outside the conditioner
 networks' library calls.
 
-Only first-order adjoints are needed: the reference's "double backward" is one reverse pass over
-a graph whose nodes are JVPs (`trainer.py:216`, `non_square.py:298-311`), and each op here is one
-such node with an explicit adjoint w.r.t. primal *and* tangent inputs.
+The exact (cholesky) path needs first-order adjoints only: the reference's "double backward" is one
+reverse pass over a graph whose nodes are JVPs (`trainer.py:216`, `non_square.py:298-311`), and
+each op here is one such node with an explicit adjoint w.r.t. primal *and* tangent inputs.
+``hutch_with_cg`` additionally differentiates a VJP (`non_square.py:199`,
+``autograd_F.vjp(..., create_graph=True)`` over a PRIMAL-only run): the primal coupling and the
+gather ops therefore issue their adjoints as differentiable nodes when the backward pass itself is
+being recorded (``torch.is_grad_enabled()`` inside ``backward``).
 """
 from __future__ import annotations
 
@@ -58,10 +62,60 @@ class _CouplingJVP(Function):
     def backward(ctx, g_x, g_V):
         z_m, V_m, st, ST = ctx.saved_tensors
         map_, inv = ctx.maps
+        if V_m is None and torch.is_grad_enabled():
+            # autograd.grad(..., create_graph=True) over a primal-only run: the VJP J^T u of
+            # `non_square.py:190-201` (hutch_with_cg) must itself carry a graph
+            g_z, g_st = _CouplingPrimalVJP.apply(z_m, st, g_x, map_, inv)
+            return g_z, None, g_st, None, None, None
         if V_m is not None and g_V is None:
             g_V = torch.zeros_like(V_m)
         g_z, g_Vin, g_st, g_ST = kernels.coupling_jvp_bwd(z_m, V_m, st, ST, map_, inv, g_x, g_V)
         return g_z, g_Vin, g_st, g_ST, None, None
+
+
+class _CouplingPrimalVJP(Function):
+    """The primal coupling's VJP as a differentiable node: (z_m, st, g_x) -> (g_z, g_st) by the
+    adjoint kernel with d = 0,
+
+        e = exp(-s);   g_z = e g_x;   g_t = -g_x;   g_s = -z e g_x,
+
+    and ITS adjoint (the "double backward" the reference gets from autograd when
+    `non_square.py:199` calls ``autograd_F.vjp(..., create_graph=True)``): with cotangents
+    (a, b_t, b_s) of (g_z, g_t, g_s),
+
+        d/dg_x = a e - b_t - b_s z e;   d/dz = -b_s e g_x;   d/ds = e g_x (b_s z - a);   d/dt = 0.
+
+    Primal-sized elementwise work (B x M, no tangent factor), issued as torch ops on the device."""
+
+    @staticmethod
+    def forward(ctx, z_m, st, g_x, map_, inv):
+        if g_x is None:
+            g_x = torch.zeros_like(z_m)
+        g_z, _, g_st, _ = kernels.coupling_jvp_bwd(z_m, None, st, None, map_, inv, g_x, None)
+        ctx.save_for_backward(z_m, st, g_x)
+        ctx.map = map_
+        return g_z, g_st
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, a, b):
+        z, st, gx = ctx.saved_tensors
+        Q = st.shape[1] // 2
+        q = None if ctx.map is None else ctx.map.long()
+        pick = (lambda t: t) if q is None else (lambda t: t.index_select(1, q))
+        e = torch.exp(-pick(st[:, Q:]))
+        a = torch.zeros_like(z) if a is None else a
+        b = torch.zeros_like(st) if b is None else b
+        bt, bs = pick(b[:, :Q]), pick(b[:, Q:])
+        g_gx = a * e - bt - bs * z * e
+        g_z = -bs * e * gx
+        g_s = e * gx * (bs * z - a)
+        g_st = torch.zeros_like(st)
+        if q is None:
+            g_st[:, Q:] = g_s
+        else:
+            g_st[:, Q:].index_copy_(1, q, g_s)
+        return g_z, g_st, g_gx, None, None
 
 
 def coupling_jvp(z_m: Tensor, V_m: Optional[Tensor], st: Tensor, ST: Optional[Tensor],
@@ -79,11 +133,23 @@ class _GatherRows(Function):
     def forward(ctx, in0, in1, idx, inv0, inv1):
         ctx.inv = (inv0, inv1)
         ctx.has1 = in1 is not None
+        ctx.idx, ctx.n0 = idx, in0.shape[-1]
         return kernels.gather_rows(in0, in1, idx)
 
     @staticmethod
     def backward(ctx, g):
         inv0, inv1 = ctx.inv
+        if torch.is_grad_enabled():
+            # create_graph=True (the VJP of hutch_with_cg, `non_square.py:199`): a gather's adjoint is a
+            # gather, so it is issued through the differentiable op with the roles of the maps swapped
+            idx, n0 = ctx.idx, ctx.n0
+            neg = torch.full_like(idx, -1)
+            g0 = g1 = None
+            if ctx.needs_input_grad[0]:
+                g0 = _GatherRows.apply(g.contiguous(), None, inv0, torch.where((idx >= 0) & (idx < n0), idx, neg), None)
+            if ctx.has1 and ctx.needs_input_grad[1]:
+                g1 = _GatherRows.apply(g.contiguous(), None, inv1, torch.where(idx >= n0, idx - n0, neg), None)
+            return g0, g1, None, None, None
         g0 = kernels.gather_rows(g, None, inv0) if ctx.needs_input_grad[0] else None
         g1 = kernels.gather_rows(g, None, inv1) if (ctx.has1 and ctx.needs_input_grad[1]) else None
         return g0, g1, None, None, None

@@ -67,8 +67,42 @@ class GradientBucket:
     def zero(self):
         self.flat.zero_()
 
+    def sync_aliases(self) -> int:
+        """Make every ``p.grad`` a view of ``flat`` again and return how many had to be repaired.
+
+        ``torch.optim.Optimizer.zero_grad()`` defaults to ``set_to_none=True`` (torch >= 2.0; the
+        reference's step `cmf/trainer.py:211` calls it), after which backward allocates fresh
+        ``.grad`` tensors that no longer alias the bucket.  A fresh gradient is copied into its
+        slice, a missing one (parameter that received no gradient) zeroes it, and the view is put
+        back -- so a reduction never ships stale data.  Steps that clear gradients with
+        :meth:`zero` or ``zero_grad(set_to_none=False)`` never pay this copy."""
+        repaired, off = 0, 0
+        for p in self.params:
+            n = p.numel()
+            view = self.flat[off:off + n].view_as(p)
+            off += n
+            if p.grad is None:
+                view.zero_()
+            elif p.grad.data_ptr() == view.data_ptr():
+                continue
+            else:
+                view.copy_(p.grad)
+            p.grad = view
+            repaired += 1
+        return repaired
+
+    def sync_aliases_after_replay(self) -> None:
+        """After a CUDA-graph replay the gradients ARE in ``flat`` (the captured kernels wrote there):
+        only the views are put back, nothing is copied or zeroed."""
+        off = 0
+        for p in self.params:
+            n = p.numel()
+            p.grad = self.flat[off:off + n].view_as(p)
+            off += n
+
     def allreduce(self, async_op: bool = False):
         """sum over ranks, then divide by the world size (mean of per-rank mean-losses)."""
+        self.sync_aliases()
         world = _world()
         if world == 1:
             return None

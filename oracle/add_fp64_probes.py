@@ -31,7 +31,8 @@ def main(argv):
         params = fill_state_dict(O.init_params(g["schema"], g["case"]["x_shape"]))
         params = {k: (v.double().requires_grad_(True) if v.is_floating_point() else v) for k, v in params.items()}
         flow = O.OracleFlow(g["schema"], params, g["case"]["x_shape"])
-        loss = O.train_loss(flow, g["config"], make_input(CASES[name]).double(), g["case"]["epoch"])
+        kw = {"hutchinson_eps": g["hutch_eps"].double()} if "hutch_eps" in g else {}
+        loss = O.train_loss(flow, g["config"], make_input(CASES[name]).double(), g["case"]["epoch"], **kw)
         loss.backward()
         g["loss_fp64"] = loss.detach().clone()
         g["grads_fp64"] = {k: grad_probe(k, v.grad) for k, v in params.items()

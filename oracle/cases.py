@@ -51,6 +51,27 @@ CASES = {
     "img8c3_gij_d16": dict(dataset="cifar10", x_shape=(3, 8, 8), batch=4, epoch=60, data="pixels",
                            overrides=dict(g_ij_loss=True, latent_dimension=16, g_hidden_channels=[8, 8],
                                           prior_num_density_layers=2, **COMMON)),
+    # image architecture with the SHIPPED hidden width of 64 (config/images.py:137) at reduced size 1x12x12:
+    # a second reference-pinned case (besides the slow full MNIST shape) that reaches the tcgen05
+    # conditioner convolutions (64 -> 64 channels) -- 12x12 checkerboard layers, 6x6 split-channel layers
+    "img12_c64_gij_d16": dict(dataset="mnist", x_shape=(1, 12, 12), batch=3, epoch=60, data="pixels",
+                              overrides=dict(g_ij_loss=True, latent_dimension=16, g_hidden_channels=[64, 64],
+                                             prior_num_density_layers=2, **COMMON)),
+    # log_jacobian_method=hutch_with_cg (the image-config default, config/images.py:148) with the Hutchinson
+    # probes injected (``hutch=True``: gen_golden.py replaces torch.randn inside the reference's draw,
+    # non_square.py:206, by the deterministic tensor of ``hutch_eps``).  With g_ij_loss the reference
+    # takes the penalty over a broadcast of J^T J eps (non_square.py:98-99,258) -- reproduced as is.
+    "hepmass_hutch_d10": dict(dataset="hepmass", x_shape=(21,), batch=12, epoch=60, data="uniform", hutch=True,
+                              overrides=dict(g_ij_loss=True, latent_dimension=10, log_jacobian_method="hutch_with_cg",
+                                             hutchinson_samples=1)),
+    # two probes per sample, plain ELBO (the penalty's masked_select cannot broadcast for m = 2)
+    "hepmass_hutch_m2_plain": dict(dataset="hepmass", x_shape=(21,), batch=8, epoch=60, data="uniform", hutch=True,
+                                   overrides=dict(latent_dimension=10, log_jacobian_method="hutch_with_cg",
+                                                  hutchinson_samples=2)),
+    # image architecture, method left at the image default (hutch_with_cg)
+    "img8_hutch_d8": dict(dataset="mnist", x_shape=(1, 8, 8), batch=4, epoch=60, data="pixels", hutch=True,
+                          overrides=dict(g_ij_loss=True, latent_dimension=8, g_hidden_channels=[8, 8],
+                                         prior_num_density_layers=2, log_jacobian_method="hutch_with_cg")),
     # BASELINE.json configs[4] (CIFAR-shape latent sweep) at reduced size: 3x16x16 -> d=160 > 128,
     # the regime of the panel-blocked Cholesky and the multi-tile tcgen05 Gram
     "img16c3_gij_d160": dict(dataset="cifar10", x_shape=(3, 16, 16), batch=2, epoch=60, data="pixels",
@@ -70,6 +91,11 @@ def make_input(case: dict) -> torch.Tensor:
     if case["data"] == "pixels":      # de-quantised pixel values in [0, 256): the noise of
         return (u + 1.0) * 127.9 + 0.05   # wrapper.py:27-30 is folded into the fixture
     return u
+
+
+def hutch_eps(name: str, shape) -> torch.Tensor:
+    """The injected Hutchinson probes of a ``hutch=True`` case: (B, d, m), roughly unit variance."""
+    return det_tensor("hutch/" + name, shape, 1.7, salt=9)
 
 
 def grad_probe(name: str, grad: torch.Tensor) -> dict:

@@ -179,8 +179,8 @@ class _Layer:
 
 def _checkerboard_mask(c: int, h: int, w: int, reverse: bool, like: Tensor) -> Tensor:
     """`acl.py:68-78`: 1 where (row+col) is odd, flipped by reverse_mask."""
-    ii = torch.arange(h).view(h, 1)
-    jj = torch.arange(w).view(1, w)
+    ii = torch.arange(h, device=like.device).view(h, 1)
+    jj = torch.arange(w, device=like.device).view(1, w)
     m = ((ii + jj) % 2 == 1).to(like.dtype).expand(c, h, w)
     return 1 - m if reverse else m
 
@@ -302,9 +302,9 @@ class _Elementwise(_Layer):
     def x_to_z(self, x):
         n = x[0].numel()
         if self.kind == "scalar-mult":        # math.py:70-88
-            return self.value * x, torch.full((x.shape[0], 1), n * math.log(abs(self.value)), dtype=x.dtype)
+            return self.value * x, torch.full((x.shape[0], 1), n * math.log(abs(self.value)), dtype=x.dtype, device=x.device)
         if self.kind == "scalar-add":         # math.py:91-105
-            return x + self.value, torch.zeros((x.shape[0], 1), dtype=x.dtype)
+            return x + self.value, torch.zeros((x.shape[0], 1), dtype=x.dtype, device=x.device)
         xc = x.clamp(1e-7, 1 - 1e-7)          # logit, math.py:41-53
         lj = (-torch.log(xc) - torch.log(1 - xc)).flatten(1).sum(1, keepdim=True)
         return torch.log(x) - torch.log(1 - x), lj
@@ -337,7 +337,7 @@ class _Tail(_Layer):
         return x.flatten(1)[:, self.perm][:, self.mask], None
 
     def z_to_x(self, z):
-        padded = torch.zeros(z.shape[0], self.n, dtype=z.dtype)
+        padded = torch.zeros(z.shape[0], self.n, dtype=z.dtype, device=z.device)
         padded[:, : self.d] = z
         return padded[:, self.inv_perm].view(z.shape[0], *self.x_shape)
 
@@ -489,7 +489,7 @@ class OracleFlow:
     def exact_log_det(self, z: Tensor):
         gram, recon, jac = self.full_jac_transpose_jac(z)
         eps, attempts = 1e-6, 1
-        eye = torch.eye(self.d, dtype=gram.dtype).expand(z.shape[0], self.d, self.d)
+        eye = torch.eye(self.d, dtype=gram.dtype, device=gram.device).expand(z.shape[0], self.d, self.d)
         while True:
             try:
                 chol = torch.linalg.cholesky(gram)
@@ -548,7 +548,7 @@ class OracleFlow:
             if add_diagonal_metric_reg:                               # non_square.py:87-92
                 l1 = torch.diagonal(gram, dim1=-2, dim2=-1).abs().sum(1, keepdim=True)
             elif add_offdiagonal_metric_reg:                          # non_square.py:95-100
-                off = ~torch.eye(gram.shape[1], dtype=torch.bool)
+                off = ~torch.eye(gram.shape[1], dtype=torch.bool, device=gram.device)
                 l1 = gram.masked_select(off).view(gram.shape[0], -1).abs().sum(1, keepdim=True)
             else:
                 l1 = 0
@@ -626,20 +626,28 @@ def loss_weights(config: dict, epoch: int):
 
 
 def train_loss(flow: OracleFlow, config: dict, x: Tensor, epoch: int = 0, **kw) -> Tensor:
+    return -elbo_per_sample(flow, config, x, epoch, **kw).mean()
+
+
+def elbo_kwargs(config: dict, epoch: int) -> dict:
+    """the keyword arguments the loss closure passes to ``density.elbo`` (`non_square_helpers.py:99-123`)"""
     lw, add_rec = loss_weights(config, epoch)
     if config["g_kk_loss"]:
         assert not config["g_ij_loss"]
-        extra = dict(likelihood_wt=lw * config["elbo_regularization_param"],
-                     metric_wt=lw * config["metric_regularization_param"],
-                     add_diagonal_metric_reg=add_rec, add_offdiagonal_metric_reg=False)
-    elif config["g_ij_loss"]:
+        return dict(likelihood_wt=lw * config["elbo_regularization_param"],
+                    metric_wt=lw * config["metric_regularization_param"], add_reconstruction=add_rec,
+                    add_diagonal_metric_reg=add_rec, add_offdiagonal_metric_reg=False)
+    if config["g_ij_loss"]:
         assert config["latent_dimension"] != 1
-        extra = dict(likelihood_wt=lw * config["elbo_regularization_param"],
-                     metric_wt=lw * config["metric_regularization_param"],
-                     add_diagonal_metric_reg=False, add_offdiagonal_metric_reg=add_rec)
-    else:
-        extra = dict(likelihood_wt=lw)
-    return -flow.elbo(x, add_reconstruction=add_rec, **extra, **kw)["elbo"].mean()
+        return dict(likelihood_wt=lw * config["elbo_regularization_param"],
+                    metric_wt=lw * config["metric_regularization_param"], add_reconstruction=add_rec,
+                    add_diagonal_metric_reg=False, add_offdiagonal_metric_reg=add_rec)
+    return dict(likelihood_wt=lw, add_reconstruction=add_rec)
+
+
+def elbo_per_sample(flow: OracleFlow, config: dict, x: Tensor, epoch: int = 0, **kw) -> Tensor:
+    """(B, 1): what the loss closure averages"""
+    return flow.elbo(x, **elbo_kwargs(config, epoch), **kw)["elbo"]
 
 
 # --------------------------------------------------------------------------------------

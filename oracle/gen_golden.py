@@ -51,6 +51,32 @@ def jsonable(obj):
     return json.loads(json.dumps(obj, default=str))
 
 
+class inject_hutchinson:
+    """For ``hutch=True`` cases: while active, ``torch.randn`` (the reference's only draw inside
+    ``_approx_log_det_jac_and_reconstruction``, non_square.py:206) returns the deterministic probes
+    of ``cases.hutch_eps`` and records them.  The reference itself is not modified."""
+
+    def __init__(self, name, case):
+        self.name, self.on, self.drawn = name, bool(case.get("hutch")), []
+
+    def __enter__(self):
+        if self.on:
+            from cases import hutch_eps
+            self._orig = torch.randn
+
+            def fake(*shape, **kw):
+                eps = hutch_eps(self.name, shape)
+                self.drawn.append(eps)
+                return eps
+            torch.randn = fake
+        return self.drawn
+
+    def __exit__(self, *exc):
+        if self.on:
+            torch.randn = self._orig
+        return False
+
+
 def run_case(name, case, api):
     from cases import make_input, grad_probe
     from detfill import fill_state_dict
@@ -76,7 +102,8 @@ def run_case(name, case, api):
 
     train_metrics = get_train_metrics(cfg)[0]
     t0 = time.time()
-    loss = train_metrics(top, x.clone(), case["epoch"])["loss"]
+    with inject_hutchinson(name, case) as drawn:
+        loss = train_metrics(top, x.clone(), case["epoch"])["loss"]
     loss.backward()
     dt = time.time() - t0
 
@@ -104,6 +131,13 @@ def run_case(name, case, api):
         off = ~torch.eye(gram.shape[1], dtype=torch.bool)
         out["l1_offdiag"] = gram.masked_select(off).view(gram.shape[0], -1).abs().sum(1, keepdim=True)
         out["l1_diag"] = torch.diagonal(gram, dim1=-2, dim2=-1).abs().sum(1, keepdim=True)
+    if case.get("hutch"):
+        assert len(drawn) == 1, "the reference draws its probes exactly once per elbo call"
+        out["hutch_eps"] = drawn[0].clone()
+        # the estimator's own outputs (non_square.py:203-258), no graph; same injected probes
+        with torch.no_grad(), inject_hutchinson(name, case):
+            est, recon, jtj_eps = head._approx_log_det_jac_and_reconstruction(z)
+        out.update(hutch_estimate=est.clone(), hutch_jtj_eps=jtj_eps.clone())
     return out
 
 

@@ -28,3 +28,22 @@ def pytest_collection_modifyitems(config, items):
 
 def load_golden(name):
     return torch.load(os.path.join(GOLDEN_DIR, name + ".pt"), weights_only=False)
+
+
+def pytest_terminal_summary(terminalreporter):
+    """measured parity deviations (tests/helpers.record), so they land in the GPU box's test log"""
+    try:
+        from helpers import DEVIATIONS
+    except Exception:
+        return
+    if not DEVIATIONS:
+        return
+    terminalreporter.write_sep("-", "measured parity deviations (max relative; bound)")
+    seen = set()
+    for case, what, dev, bound in DEVIATIONS:
+        key = (case, what)
+        if key in seen:
+            continue
+        seen.add(key)
+        flag = "" if dev <= bound else "   <-- over"
+        terminalreporter.write_line(f"{case:28s} {what:72s} {dev:9.2e}  ({bound:.1e}){flag}")

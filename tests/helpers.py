@@ -36,6 +36,10 @@ def run_loss(golden, density, device="cpu"):
     name = golden["name"]
     x = make_input(CASES[name]).to(device)
     train_metrics = get_non_square_train_metrics(golden["config"])[0]
+    if "hutch_eps" in golden:          # the probes the reference was given (oracle/gen_golden.py)
+        head, _ = find_head(strip_wrappers(density))
+        eps = golden["hutch_eps"]
+        head._draw_hutchinson = lambda shape, dev, dtype: eps.to(device=dev, dtype=dtype)
     loss = train_metrics(strip_wrappers(density), x, golden["case"]["epoch"])["loss"]
     loss.backward()
     grads = {}
@@ -53,10 +57,20 @@ def assert_close(a, b, rtol, atol=0.0, what=""):
     assert err <= rtol * scale + atol, f"{what}: max err {err:.3e} vs scale {scale:.3e} (rtol {rtol})"
 
 
+# (case, what, measured max relative deviation, bound): printed by conftest.pytest_terminal_summary so the
+# numbers land in the test log of the GPU box, pass or fail
+DEVIATIONS = []
+
+
+def record(case, what, dev, bound):
+    DEVIATIONS.append((case, what, float(dev), float(bound)))
+
+
 def reference_rounding_noise(golden):
     """Worst relative deviation of the reference's own fp32 gradients from an fp64 evaluation of
     the same algorithm (oracle/add_fp64_probes.py).  ~1e-7 for the well-conditioned flat configs,
-    1.6e-4 for MNIST-shape d=64 where cond(G) ~ 5e3..8e3 amplifies fp32 rounding in G^{-1}."""
+    1.6e-4 for MNIST-shape d=64 where cond(G) ~ 5e3..8e3 amplifies fp32 rounding in G^{-1}.
+    Reported next to the measured deviations; it does not widen any tolerance."""
     if "grads_fp64" not in golden:
         return 0.0
     worst = 0.0
@@ -67,16 +81,34 @@ def reference_rounding_noise(golden):
 
 
 def check_against_golden(golden, loss, grads, rtol):
-    """loss and every parameter gradient within ``rtol`` relative of the reference's -- or within
-    3x the reference's own fp32 rounding error against fp64 when that is larger (an fp32 result
-    cannot be asked to agree with another fp32 result more closely than either agrees with the
-    exact value)."""
-    rtol = max(rtol, 3.0 * reference_rounding_noise(golden))
+    """loss and every parameter gradient within ``rtol`` (north_star: 1e-4) relative of the
+    reference's own fp32 values -- asserted as is for every case, the ill-conditioned MNIST shape
+    included.  The deviation from the fp64 evaluation of the same algorithm (``grads_fp64``) is a
+    second, separately reported bound: there the product may not be further from the exact value than
+    the north-star band plus the reference's own fp32 error."""
+    name = golden["name"]
     assert_close(loss, golden["loss"], rtol, what="loss")
+    record(name, "loss vs reference fp32", abs(float(loss) - float(golden["loss"])) / max(abs(float(golden["loss"])), 1e-30), rtol)
     assert set(golden["grads"]) == set(grads), "parameters receiving gradients differ from the reference"
+    worst_norm = worst_head = worst64 = 0.0
+    for k, probe in golden["grads"].items():
+        mine = grad_probe(k, grads[k])
+        tol = rtol * max(probe["norm"], 1e-12)
+        worst_norm = max(worst_norm, abs(mine["norm"] - probe["norm"]) / max(probe["norm"], 1e-12))
+        worst_head = max(worst_head, float((mine["head"].double() - probe["head"].double()).abs().max()) / max(probe["norm"], 1e-12))
+        if k in golden.get("grads_fp64", {}):
+            p64 = golden["grads_fp64"][k]
+            worst64 = max(worst64, abs(mine["norm"] - p64["norm"]) / max(p64["norm"], 1e-12))
+    record(name, "grad norms vs reference fp32", worst_norm, rtol)
+    record(name, "grad entries vs reference fp32 (of the norm)", worst_head, 2 * rtol)
+    noise = reference_rounding_noise(golden)
+    if "grads_fp64" in golden:
+        record(name, f"grad norms vs fp64 oracle (reference's own fp32 error: {noise:.2e})", worst64, rtol + noise)
     for k, probe in golden["grads"].items():
         mine = grad_probe(k, grads[k])
         tol = rtol * max(probe["norm"], 1e-12)
         assert abs(mine["norm"] - probe["norm"]) <= tol, f"{k}: norm {mine['norm']} vs {probe['norm']}"
         assert abs(mine["dot"] - probe["dot"]) <= 8 * tol, f"{k}: dot {mine['dot']} vs {probe['dot']}"
         assert_close(mine["head"], probe["head"], rtol, atol=tol, what=k)
+    if "grads_fp64" in golden:
+        assert worst64 <= rtol + noise, f"gradient norms {worst64:.2e} from the fp64 oracle (allowed {rtol + noise:.2e})"

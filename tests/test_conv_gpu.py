@@ -60,6 +60,40 @@ def test_weight_gradient(N, H, W):
     assert _rel(K.conv3x3_c64_wgrad(x, gy), gw.double()) < 2e-6
 
 
+@pytest.mark.parametrize("H,W", [(28, 28), (14, 14)])
+def test_benchmarked_tangent_batch(H, W):
+    """N = 3200 = B * d of the benchmarked step (B = 50, d = 64): 148 persistent CTAs each walking
+    ~66 (28x28) / ~17 (14x14) tile pairs, weight-gradient chunks of T = 14 / 15 tiles -- forward, data
+    gradient (both drain intervals) and weight gradient (both modes) against FP64 on the device."""
+    N = 3200
+    x, gy, w = _rand((N, 64, H, W), 41), _rand((N, 64, H, W), 42), _rand((64, 64, 3, 3), 43, 1 / 24)
+    b = _rand((64,), 44)
+    devs = {}
+    ref = torch.empty(N, 64, H, W, dtype=torch.float64, device=DEV)
+    for i in range(0, N, 400):                                  # FP64 reference in slices (memory)
+        ref[i:i + 400] = F.conv2d(x[i:i + 400].double(), w.double(), b.double(), padding=1)
+    devs["fwd"] = _rel(K.conv3x3_c64(x, K.conv3x3_c64_prep(w, False), b), ref)
+    for i in range(0, N, 400):
+        ref[i:i + 400] = F.conv_transpose2d(gy[i:i + 400].double(), w.double(), padding=1)
+    wt = K.conv3x3_c64_prep(w, True)
+    devs["dgrad drain 1"] = _rel(K.conv3x3_c64(gy, wt, None), ref)
+    devs["dgrad drain 2"] = _rel(K.conv3x3_c64(gy, wt, None, drain=2), ref)
+    del ref
+    gw_ref = torch.zeros(64, 64, 3, 3, dtype=torch.float64, device=DEV)
+    for i in range(0, N, 400):
+        gw_ref += _wgrad_ref(x[i:i + 400], gy[i:i + 400])
+    devs["wgrad"] = _rel(K.conv3x3_c64_wgrad(x, gy, deterministic=False), gw_ref)
+    devs["wgrad deterministic"] = _rel(K.conv3x3_c64_wgrad(x, gy, deterministic=True), gw_ref)
+    try:
+        from helpers import record
+        for k, v in devs.items():
+            record(f"conv3x3 N=3200 {H}x{W}", k + " vs FP64", v, 2e-5 if k.startswith("wgrad") else 2e-6)
+    except ImportError:
+        pass
+    assert devs["fwd"] < 2e-6 and devs["dgrad drain 1"] < 2e-6 and devs["dgrad drain 2"] < 2e-6, devs
+    assert devs["wgrad"] < 2e-5 and devs["wgrad deterministic"] < 2e-5, devs
+
+
 def test_weight_gradient_same_sign_terms():
     """all-positive terms: the longest truncating accumulation (T = 14 tiles per CTA)"""
     x, gy = _rand((64, 64, 28, 28), 22).abs(), _rand((64, 64, 28, 28), 23).abs()

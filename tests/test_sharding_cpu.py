@@ -32,6 +32,20 @@ def _worker(rank, world, port, name, out_dir):
     loss = get_non_square_train_metrics(g["config"])[0](strip_wrappers(density), x, g["case"]["epoch"])["loss"]
     loss.backward()
     loss = allreduce_gradients(bucket, loss)
+    first = bucket.flat.clone()
+    # a second step the way the reference's trainer runs it (`cmf/trainer.py:211-222`): a real optimizer
+    # whose zero_grad() drops the .grad tensors (set_to_none=True is torch's default) -- the bucket must
+    # pick the fresh gradients up again, not reduce its stale buffer
+    opt = torch.optim.SGD(density.parameters(), lr=0.0)
+    opt.zero_grad()
+    assert all(p.grad is None for p in density.parameters())
+    loss2 = get_non_square_train_metrics(g["config"])[0](strip_wrappers(density), x, g["case"]["epoch"])["loss"]
+    loss2.backward()
+    assert bucket.sync_aliases() > 0 and bucket.sync_aliases() == 0
+    allreduce_gradients(bucket, loss2)
+    opt.step()
+    assert torch.allclose(bucket.flat, first, rtol=1e-6, atol=1e-12), "second step (after zero_grad) reduced stale gradients"
+    assert all(p.grad is not None and p.grad.data_ptr() >= bucket.flat.data_ptr() for p in bucket.params)
     if rank == 0:
         torch.save({"loss": loss, "flat": bucket.flat.clone(),
                     "names": [n for n, p in density.named_parameters() if p.requires_grad]},
