@@ -17,10 +17,17 @@ call `cmf/trainer.py:213-216` makes -- followed by the flat-bucket gradient all-
   scope_a    the replaced kernels alone (coupling fwd/bwd over the 10 layers, Gram fwd/bwd,
              Cholesky/log-det/penalty fwd/bwd) on synthetic conditioner outputs resident in HBM,
              against their algorithmic bytes (8.76 MB/sample) -- explains `value`
-  roofline   the dominant hand-written kernel (coupling adjoint), algorithmic bytes / CUDA-event
-             time inside the scope_a region, against the measured HBM copy bandwidth
+  roofline   the dominant kernel of the step, the tcgen05 conditioner convolution: algorithmic
+             FLOPs / CUDA-event time of its launches inside one step, against the FP32-accurate
+             3xTF32 ceiling = (TF32 matmul throughput measured on this box at start-up) / 3
+  roofline_scope_a  the coupling adjoint (HBM-bound), algorithmic bytes / CUDA-event time against the
+             measured HBM copy bandwidth
   cpu_baseline  the CPU oracle (a port of the reference's algorithm, oracle/cmf_oracle.py) timed
              on this box's host cores on a bounded sample of the same workload
+  device_baseline  the same oracle port run on this GPU (fp32, TF32 off, the reference's own
+             one-column-at-a-time schedule): the like-for-like device number BASELINE.md asks for
+  other_configs  the other BASELINE.json config shapes (sphere, sinusoid-1-6, power-shape,
+             hepmass-shape, CIFAR-shape d=64) through the same public API, sharded the same way
 """
 from __future__ import annotations
 
@@ -56,7 +63,9 @@ def parse_args():
     ap.add_argument("--scope-a-batch", type=int, default=512)
     ap.add_argument("--large-batch", type=int, default=128,
                     help="second operating point reported beside the metric (N = 1 only; 0 disables)")
-    ap.add_argument("--cpu-sample", type=int, default=1, help="samples per CPU-baseline step")
+    ap.add_argument("--cpu-sample", type=int, default=2, help="samples per CPU-baseline / reference-arm step")
+    ap.add_argument("--no-other-configs", action="store_true")
+    ap.add_argument("--no-device-baseline", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--only", default=None, choices=[None, "scope_a", "step", "profile"],
                     help="profiling aid: run only the kernels-only region / only the full step (no JSON contract)")
@@ -154,8 +163,10 @@ def run_reference_arm(args, cfg, schema):
         "impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "MNIST-shape 1x28x28 -> d=64, non-square cholesky + g_ij_loss",
-                   "batch": args.cpu_sample, "l2": "n/a (host)"},
+        "config": {"workload": "MNIST-shape 1x28x28 -> d=64, non-square cholesky + g_ij_loss (BASELINE configs[3])",
+                   "batch": args.cpu_sample, "l2": "n/a (host)",
+                   "bounded_sample": f"each step is {args.cpu_sample} sample(s) of the workload whose GPU arm runs {args.batch} per step, so that "
+                                     "warm-up + timed steps end within minutes on the host cores; samples/s is per-sample work either way"},
         "cpu_baseline": {"value": val, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -332,6 +343,188 @@ def scope_a(head, B, steps, warmup, dev):
 
 
 # ------------------------------------------------------------------------------------------------
+# The ceiling of the convolution kernels: TF32 tensor-core throughput MEASURED on this box
+# ------------------------------------------------------------------------------------------------
+def measure_tf32_peak(dev, seconds=1.5):
+    """torch.matmul (cuBLAS) fp32 inputs with TF32 allowed, 8192^3: best of 10 (burst) and back to
+    back for ``seconds`` (sustained) -- the same recipe MEASURED_PEAKS.json uses for bf16.  A 3xTF32
+    (FP32-accurate) product costs three such MMAs, so its ceiling is a third of this."""
+    n = 8192
+    a = torch.randn(n, n, device=dev)
+    b = torch.randn(n, n, device=dev)
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        for _ in range(3):
+            a @ b
+        torch.cuda.synchronize()
+        best = 0.0
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); a @ b; e1.record()
+            torch.cuda.synchronize()
+            best = max(best, 2.0 * n ** 3 / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+        iters = max(10, int(seconds / (2.0 * n ** 3 / (best * 1e12))))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        sustained = 2.0 * n ** 3 * iters / (e0.elapsed_time(e1) * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    del a, b
+    return {"tf32_tflops": best, "tf32_tflops_sustained": sustained,
+            "how": f"torch.matmul fp32 with TF32 allowed, {n}^3: best of 10 (burst), {iters} back to back (sustained), CUDA events"}
+
+
+def conv_roofline(conv, tf32, peaks, peak_kind):
+    """`roofline` of the JSON line.  ``achieved`` = algorithmic FLOPs (2 * N * 64 * 64 * 9 * H * W per
+    launch, every launch of one step) / the CUDA-event time of those launches; ``peak`` = the ceiling of
+    FP32-accurate 3xTF32 arithmetic = measured TF32 matmul throughput / 3 (sustained figure: the kernel
+    is timed inside a long step).  ``traffic`` = dram bytes of ONE launch on the tangent batch from the
+    ncu --set full capture named in ``traffic_source`` (a citation of a capture of this code, not a
+    measurement of this run), or null when no capture of the current kernels is committed."""
+    k = conv["conv3x3_tc_kernel"]
+    peak = tf32["tf32_tflops_sustained"] / 3.0
+    out = {"kernel": f"conv3x3_tc_kernel ({k['launches']} launches/step, {k['ms_per_step']:.0f} ms of the step)",
+           "bound": "tensor", "achieved": k["tflops"], "peak": peak, "unit": "TFLOP/s", "frac": k["tflops"] / peak,
+           "peak_source": "measured in this run: " + tf32["how"] + "; / 3 for the three MMAs of a 3xTF32 product",
+           "peak_burst": tf32["tf32_tflops"] / 3.0, "frac_of_burst_peak": 3.0 * k["tflops"] / tf32["tf32_tflops"],
+           "tf32_tflops_measured": tf32["tf32_tflops"], "tf32_tflops_sustained_measured": tf32["tf32_tflops_sustained"],
+           "bf16_derived_ceiling": {"value": peaks["bf16_tflops"] / 6.0, "source": peak_kind + " bf16 peak / 6 (kind::tf32 at half the bf16 rate, 3 MMAs)",
+                                    "frac": 6.0 * k["tflops"] / peaks["bf16_tflops"]},
+           "algorithmic_flops_per_step": k["algorithmic_flops_per_step"],
+           "full_size_launches": {v: d for v, d in k["by_variant"].items() if not v.startswith("N=50 ")}}
+    tpath = os.path.join(ROOT, "profiles", "conv_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            t = json.load(f)
+        out.update(traffic=t["dram_bytes_per_launch"], traffic_source=t["source"], traffic_algorithmic=t.get("algorithmic_bytes_per_launch"))
+    else:
+        out.update(traffic=None, traffic_source="no ncu --set full capture of the current kernel is committed")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# Device baseline: the reference's algorithm (oracle port, plain torch) on this GPU
+# ------------------------------------------------------------------------------------------------
+def device_baseline(cfg, schema, batch, dev, chunk=10):
+    """One fwd+bwd of the oracle port on ``batch`` MNIST-shape samples on the GPU in fp32 with TF32
+    off -- the reference's own schedule (one tangent column per pass, conditioner primal recomputed
+    per column, cuDNN/cuBLAS/cuSOLVER library calls).  Run ``chunk`` samples at a time: its autograd
+    graph keeps ~4.4 GB of activations per sample alive.  One warm-up chunk (cuDNN autotune), then
+    the timed pass.  bench.py may execute oracle/ here as the checker's baseline, never as the product."""
+    import cmf_oracle as O
+    from detfill import fill_state_dict, det_tensor
+    params = fill_state_dict(O.init_params(schema, WORKLOAD["x_shape"]))
+    params = {k: v.to(dev) for k, v in params.items()}
+    params = {k: (v.requires_grad_(True) if v.is_floating_point() else v) for k, v in params.items()}
+    flow = O.OracleFlow(schema, params, WORKLOAD["x_shape"])
+    x = ((det_tensor("bench/x", (batch, *WORKLOAD["x_shape"]), 1.0, salt=5) + 1.0) * 127.9 + 0.05).to(dev)
+
+    def one_pass(n):
+        for i in range(0, n, chunk):
+            (O.train_loss(flow, cfg, x[i:i + chunk], epoch=0) * (min(chunk, n - i) / n)).backward()
+    one_pass(min(chunk, batch))
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    one_pass(batch)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    return {"value": batch / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms, "batch": batch, "chunk": chunk,
+            "kind": "port", "dtype": "f32", "tf32": False,
+            "what": "oracle port of the reference algorithm (one tangent column per pass, torch library kernels) on this "
+                    "GPU, same workload and batch, one timed fwd+bwd after a warm-up chunk"}
+
+
+# ------------------------------------------------------------------------------------------------
+# The other BASELINE.json config shapes, through the same public API
+# ------------------------------------------------------------------------------------------------
+OTHER_CONFIGS = [
+    # name, dataset key, x_shape, per-GPU batch (reference defaults: two_d.py:77, tabular.py:290-296, images.py:131), overrides
+    ("sphere d=3 (configs[0])", "sphere", (3,), 1000, dict(g_ij_loss=True, latent_dimension=3)),
+    ("sinusoid-1-6 d=6 (configs[1])", "sinusoid-1-6", (6,), 1000, dict(g_ij_loss=True, latent_dimension=6, hutchinson_samples=1,
+                                                                    g_ij_global_loss=True)),
+    ("power-shape D=6 d=6 (configs[2]; d=10 > D is not runnable in the reference)", "power", (6,), 5000,
+     dict(g_ij_loss=True, latent_dimension=6)),
+    ("hepmass-shape D=21 d=10 (configs[2] stand-in)", "hepmass", (21,), 750, dict(g_ij_loss=True, latent_dimension=10)),
+    ("CIFAR-shape 3x32x32 d=64 (configs[4])", "cifar10", (3, 32, 32), 48, dict(g_ij_loss=True, latent_dimension=64)),
+]
+
+
+def run_other_configs(dev, rank, world, barrier):
+    """ms/step and whole-job samples/s of each shape: loss + backward + gradient all-reduce on a
+    batch resident in HBM, every rank its own shard (weak scaling), max over ranks.  The flat shapes
+    are launch-bound, so they run as one CUDA graph (cmf_b200.graphed); the image shape runs eagerly."""
+    import torch.distributed as dist
+    from cmf_b200.config import get_config, get_schema
+    from cmf_b200.factory import get_density
+    from cmf_b200.graphed import GraphedTrainStep
+    from cmf_b200.non_square_helpers import get_non_square_train_metrics
+    from cmf_b200.parallel import GradientBucket, allreduce_gradients
+    out = []
+    for name, ds, x_shape, B, ov in OTHER_CONFIGS:
+        try:
+            cfg = {**get_config(ds), **ov, "log_jacobian_method": "cholesky", "likelihood_warmup": False}
+            torch.manual_seed(0)
+            density = get_density(get_schema(cfg), x_shape)
+            with torch.no_grad():
+                for p in density.parameters():
+                    p.add_(0.05 * float(p.std() if p.numel() > 1 else 1.0) * torch.randn_like(p))
+            density = density.to(dev).train()
+            bucket = GradientBucket(density.parameters())
+            tm = get_non_square_train_metrics(cfg)[0]
+            torch.manual_seed(1234 + rank)
+            image = len(x_shape) == 3
+            if image:
+                x = torch.randint(0, 256, (B, *x_shape)).float()
+                x = (x + torch.rand_like(x)).to(dev)
+                inner = density.module.density
+            else:
+                x = torch.randn(B, *x_shape)
+                if ds == "sphere":
+                    x = x / x.norm(dim=1, keepdim=True)
+                x = x.to(dev)
+                inner = density.module
+            graphed = None if image else GraphedTrainStep(inner, tm, bucket)
+
+            def step():
+                if graphed is not None:
+                    graphed(x, 0)
+                else:
+                    bucket.zero()
+                    tm(inner, x, 0)["loss"].backward()
+                allreduce_gradients(bucket)
+            iters, warm = (3, 2) if image else (50, 5)
+            for _ in range(warm):
+                step()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                step()
+            e1.record()
+            barrier()
+            ms = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            ms = float(ms)
+            out.append({"workload": name, "per_gpu_batch": B, "ms_per_step": ms, "samples_per_s": world * B / (ms * 1e-3),
+                        "timing": "eager" if image else "cuda-graph replay",
+                        "eager_fallbacks": 0 if graphed is None else graphed.eager_fallbacks})
+            del density, bucket, graphed, x
+            torch.cuda.empty_cache()
+        except Exception as e:                                  # report, never hide
+            out.append({"workload": name, "error": f"{type(e).__name__}: {str(e)[:160]}"})
+            torch.cuda.empty_cache()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # own arm
 # ------------------------------------------------------------------------------------------------
 def run_own_arm(args, cfg, schema):
@@ -440,6 +633,7 @@ def run_own_arm(args, cfg, schema):
         ms, launches = timed(step_resident, args.steps, args.warmup)
         print(json.dumps({"ms_per_step": ms / args.steps, "gpu_launches": launches}), flush=True)
         return
+    tf32 = measure_tf32_peak(dev) if rank == 0 else None
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -447,6 +641,32 @@ def run_own_arm(args, cfg, schema):
     ms_e2e, _ = timed(step_e2e, args.steps, 1)
     value = world * B * args.steps / (ms * 1e-3)
     e2e = world * B * args.steps / (ms_e2e * 1e-3)
+
+    # where the N > 1 step spends its time: device time up to the end of backward vs. the time from
+    # there to the end of the gradient all-reduce (transfer + waiting for the slowest rank), per rank
+    breakdown = None
+    if world > 1:
+        comp, wait = [], []
+        for _ in range(3):
+            barrier()
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            bucket.zero()
+            e0.record()
+            loss = train_metrics(inner, x_dev, 0)["loss"]
+            loss.backward()
+            e1.record()
+            allreduce_gradients(bucket)
+            e2.record()
+            torch.cuda.synchronize()
+            comp.append(e0.elapsed_time(e1)); wait.append(e1.elapsed_time(e2))
+        t = torch.tensor([sum(comp) / 3, sum(wait) / 3], device=dev)
+        gathered = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(gathered, t)
+        if rank == 0:
+            cs, ws = [float(g[0]) for g in gathered], [float(g[1]) for g in gathered]
+            breakdown = {"compute_ms_per_rank": [round(c, 2) for c in cs], "allreduce_wait_ms_per_rank": [round(w, 2) for w in ws],
+                         "compute_ms_max": max(cs), "compute_ms_min": min(cs), "allreduce_bytes": int(bucket.flat.numel() * 4),
+                         "note": "steps start at a barrier; wait = all-reduce transfer + waiting for the slowest rank's backward"}
 
     sa = None
     conv = conv_kernel_times(step_resident, dev)      # a full step incl. the gradient all-reduce: EVERY rank runs it
@@ -488,6 +708,19 @@ def run_own_arm(args, cfg, schema):
             large = {"per_gpu_batch": args.large_batch, "error": f"{type(e).__name__}: {str(e)[:120]}"}
             torch.cuda.empty_cache()
 
+    others = None if args.no_other_configs else run_other_configs(dev, rank, world, barrier)
+
+    dev_base = None
+    if rank == 0 and world == 1 and not args.no_device_baseline:
+        try:
+            del x_dev
+            density.zero_grad(set_to_none=True)
+            torch.cuda.empty_cache()
+            dev_base = device_baseline(cfg, schema, B, dev)
+        except Exception as e:
+            dev_base = {"error": f"{type(e).__name__}: {str(e)[:160]}"}
+        torch.cuda.empty_cache()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         step, cores = cpu_step_fn(cfg, schema, args.cpu_sample)
@@ -495,8 +728,8 @@ def run_own_arm(args, cfg, schema):
         step()
         dt = time.perf_counter() - t0
         cpu = {"value": args.cpu_sample / dt, "unit": "samples/s", "cores": cores, "kind": "port",
-               "sample": f"1 step of {args.cpu_sample} MNIST-shape sample(s), d=64, fp32 fwd+bwd, oracle port of the "
-                         f"reference algorithm on torch CPU with {cores} threads ({dt:.1f} s)"}
+               "sample": f"1 step of {args.cpu_sample} MNIST-shape sample(s) (the GPU step is {B}), d=64, fp32 fwd+bwd, oracle port "
+                         f"of the reference algorithm on torch CPU with {cores} threads ({dt:.1f} s)"}
 
     if rank == 0:
         peaks, peak_kind = measured_peaks()
@@ -526,18 +759,7 @@ def run_own_arm(args, cfg, schema):
                         "frac_of_hbm": scope_gbs / peaks["hbm_gbs"], "class_ms_per_step": sa["class_ms"],
                         "launches_per_step": sa["launches_per_class"]},
             # dominant kernel of the step: the tcgen05 conditioner convolution (forward + data gradient)
-            "roofline": {"kernel": f"conv3x3_tc_kernel ({conv['conv3x3_tc_kernel']['launches']} launches/step, "
-                                   f"{conv['conv3x3_tc_kernel']['ms_per_step']:.0f} ms of the step)",
-                         "bound": "tensor", "achieved": conv["conv3x3_tc_kernel"]["tflops"],
-                         "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
-                         "frac": conv["conv3x3_tc_kernel"]["tflops"] / peaks["bf16_tflops"],
-                         "traffic": 1260095232, "peak_source": peak_kind,
-                         "traffic_note": "dram read+write of ONE launch on the tangent batch (3250x64x28x28) from ncu "
-                                         "--set full (profiles/r01f_conv_fwd_tangent_raw.csv); algorithmic 1304.6 MB",
-                         "note": "FP32-accurate 3xTF32: kind::tf32 runs at half the bf16 rate and each product "
-                                 "takes 3 MMAs, so the ceiling of this arithmetic is 1/6 of the bf16 peak",
-                         "frac_of_3xtf32_ceiling": 6.0 * conv["conv3x3_tc_kernel"]["tflops"] / peaks["bf16_tflops"],
-                         "algorithmic_flops_per_step": conv["conv3x3_tc_kernel"]["algorithmic_flops_per_step"]},
+            "roofline": conv_roofline(conv, tf32, peaks, peak_kind),
             "conv_kernels": conv,
             "roofline_scope_a": {"kernel": "coupling_bwd_{vec4,map} (10 launches/step)", "bound": "hbm",
                                  "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
@@ -545,8 +767,14 @@ def run_own_arm(args, cfg, schema):
                                  "algorithmic_bytes_per_step": cb_bytes},
             "peak_mem_gib": peak_mem,
         }
+        if breakdown is not None:
+            line["scaling_breakdown"] = breakdown
         if large is not None:
             line["large_batch"] = large
+        if others is not None:
+            line["other_configs"] = others
+        if dev_base is not None:
+            line["device_baseline"] = dev_base
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)

