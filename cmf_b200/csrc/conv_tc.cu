@@ -78,6 +78,8 @@ struct ConvParams {
     const float* mask_src;             // (N / mask_div, 64, H, W) pre-ReLU primal activations, or null
     const uint2* mask_bits;            // (N / mask_div, H*W) packed signs of the same (cmf_relu_mask_pack), or null
     int mask_div;
+    int tail;                          // joint batch: images [tail, N) are the PRIMAL images of samples 0 .. N - tail - 1
+                                       // (mask row im - tail, and the only images that get the bias); 0 = no tail
     int mask_first;
     const float* res;                  // (N, 64, H, W) or null
     float* y;
@@ -386,11 +388,15 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             }
             if (valid) {
                 const long long o = (long long)im * kC * hw + p;
+                // joint batch: tangent images first (mask row im / mask_div, no bias), then the primal images
+                const bool in_tail = P.tail > 0 && im >= P.tail;
+                const int mrow = in_tail ? im - P.tail : im / P.mask_div;
+                const float* bias = (P.tail == 0 || in_tail) ? P.bias : nullptr;
                 if (!P.mask_src && !P.mask_bits && !P.res) {
 #pragma unroll
-                    for (int j = 0; j < kC; ++j) P.y[o + (long long)j * hw] = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                    for (int j = 0; j < kC; ++j) P.y[o + (long long)j * hw] = accr[j] + (bias ? __ldg(bias + j) : 0.f);
                 } else {
-                    const float* ms = P.mask_src ? P.mask_src + (long long)(im / P.mask_div) * kC * hw + p : nullptr;
+                    const float* ms = P.mask_src ? P.mask_src + (long long)mrow * kC * hw + p : nullptr;
                     const float* rs = P.res ? P.res + o : nullptr;
                     float* y1 = P.y + o;
                     float* y2 = P.y2 ? P.y2 + o : nullptr;
@@ -400,7 +406,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     // mask values, packed into two words, then the skip connection 32 channels at a time
                     uint32_t keep_bits[2] = {0xffffffffu, 0xffffffffu};
                     if (P.mask_bits) {       // one 8-byte load instead of 64 strided ones
-                        const uint2 mb = __ldg(P.mask_bits + (long long)(im / P.mask_div) * hw + p);
+                        const uint2 mb = __ldg(P.mask_bits + (long long)mrow * hw + p);
                         keep_bits[0] = mb.x;
                         keep_bits[1] = mb.y;
                     } else if (kFloatMask && ms) {
@@ -423,7 +429,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
 #pragma unroll
                         for (int e = 0; e < 32; ++e) {
                             const int j = 32 * h + e;
-                            float v2 = accr[j] + (P.bias ? __ldg(P.bias + j) : 0.f);
+                            float v2 = accr[j] + (bias ? __ldg(bias + j) : 0.f);
                             const bool keep = (keep_bits[h] >> e) & 1u;
                             if (mask_first && !keep) v2 = 0.f;
                             v2 += rv[e];
@@ -466,7 +472,7 @@ extern "C" int cmf_conv3x3_c64_usable(int N, int H, int W) {
 
 static int conv_launch(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                        const float* mask_src, const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
-                       float* y, float* y2, int drain_stages, cmf_stream_t stream) {
+                       float* y, float* y2, int drain_stages, cmf_stream_t stream, int tail = 0) {
     CMF_REQUIRE(drain_stages >= 1 && drain_stages <= 3, "conv3x3: drain_stages must be 1, 2 or 3 (got %d)", drain_stages);
     CMF_REQUIRE(N >= 0 && H >= 0 && W >= 0, "conv3x3: negative size");
     if (N == 0 || H == 0 || W == 0) return 0;
@@ -480,7 +486,10 @@ static int conv_launch(int N, int H, int W, const float* x, const float* wsplit,
     P.x = x;
     P.hl = (W + 4) & ~3;
     const bool masked = mask_src || mask_bits;
-    CMF_REQUIRE(!masked || (mask_div >= 1 && N % mask_div == 0), "conv3x3: mask_div must divide N");
+    CMF_REQUIRE(tail >= 0 && tail <= N, "conv3x3: tail must lie in [0, N]");
+    CMF_REQUIRE(!masked || (mask_div >= 1 && (tail > 0 ? tail : N) % mask_div == 0), "conv3x3: mask_div must divide the tangent images");
+    CMF_REQUIRE(tail == 0 || !masked || tail / mask_div == N - tail, "conv3x3: joint batch needs tail / mask_div == N - tail primal images");
+    P.tail = tail;
     CMF_REQUIRE(!y2 || masked, "conv3x3: second output needs a mask source");
     CMF_REQUIRE(!mask_bits || (reinterpret_cast<uintptr_t>(mask_bits) & 7u) == 0, "conv3x3: mask_bits must be 8-byte aligned");
     P.bias = bias; P.y = y; P.y2 = y2;
@@ -538,6 +547,13 @@ extern "C" int cmf_conv3x3_c64_fused_bits(int N, int H, int W, const float* x, c
                                           const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
                                           float* y, float* y2, int drain_stages, cmf_stream_t stream) {
     return conv_launch(N, H, W, x, wsplit, bias, nullptr, mask_bits, mask_div, mask_first, res, y, y2, drain_stages, stream);
+}
+
+extern "C" int cmf_conv3x3_c64_joint(int N, int Nt, int H, int W, const float* x, const float* wsplit, const float* bias,
+                                     const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
+                                     float* y, float* y2, int drain_stages, cmf_stream_t stream) {
+    CMF_REQUIRE(Nt > 0 && Nt < N, "conv3x3_joint: need 0 < Nt < N (Nt tangent images, then N - Nt primal images)");
+    return conv_launch(N, H, W, x, wsplit, bias, nullptr, mask_bits, mask_div, mask_first, res, y, y2, drain_stages, stream, Nt);
 }
 
 extern "C" int cmf_relu_mask_pack(int N, int HW, const float* x, uint32_t* bits, cmf_stream_t stream) {

@@ -257,12 +257,15 @@ def relu_mask_pack(x: Tensor) -> Tensor:
 
 def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_src: Optional[Tensor] = None,
                 mask_div: int = 1, mask_first: bool = False, res: Optional[Tensor] = None, second: bool = False,
-                drain: int = 1):
+                drain: int = 1, tail: int = 0, out: Optional[Tensor] = None, out2: Optional[Tensor] = None):
     """x (N,64,H,W), wsplit from ``conv3x3_c64_prep`` -> y (N,64,H,W), with the fused epilogue of
     ``cmf_conv3x3_c64_fused``:  t = conv(x) + bias; if mask_first: t *= m; if res: t += res; y = t;
     ``second`` additionally returns y2 = t * m  (m = mask_src[n // mask_div] > 0).  ``mask_src`` is
     either the float activations (N // mask_div, 64, H, W) or their packed signs from
-    ``relu_mask_pack`` (int32, (N // mask_div, H*W, 2))."""
+    ``relu_mask_pack`` (int32, (N // mask_div, H*W, 2)).
+    ``tail`` = Nt > 0 selects the joint batch of ``cmf_conv3x3_c64_joint``: images [0, Nt) are tangents
+    (mask row n // mask_div, no bias), images [Nt, N) the primal images of samples 0 .. N - Nt - 1
+    (mask row n - Nt, bias).  ``out`` / ``out2``: write into these (contiguous, same shape as x)."""
     lib = _lib.load()
     x, wsplit = _req(x, "x"), _req(wsplit, "wsplit")
     N, C, H, W = x.shape
@@ -270,21 +273,31 @@ def conv3x3_c64(x: Tensor, wsplit: Tensor, bias: Optional[Tensor] = None, mask_s
     if bias is not None:
         bias = _req(bias, "bias")
         assert bias.numel() == 64
+    n_rows = (N - tail) if tail else (N // mask_div if mask_src is not None else 0)
     packed = mask_src is not None and mask_src.dtype == torch.int32
     if packed:
         assert mask_src.is_cuda and mask_src.is_contiguous()
-        assert N % mask_div == 0 and tuple(mask_src.shape) == (N // mask_div, H * W, 2), (mask_src.shape, x.shape, mask_div)
+        assert (tail or N) % mask_div == 0 and tuple(mask_src.shape) == (n_rows, H * W, 2), (mask_src.shape, x.shape, mask_div, tail)
     elif mask_src is not None:
+        assert not tail, "the joint batch takes packed masks"
         mask_src = _req(mask_src, "mask_src")
         assert N % mask_div == 0 and tuple(mask_src.shape) == (N // mask_div, 64, H, W), (mask_src.shape, x.shape, mask_div)
     if res is not None:
         res = _req(res, "res")
         assert res.shape == x.shape
     assert not second or mask_src is not None
-    y = torch.empty_like(x)
-    y2 = torch.empty_like(x) if second else None
+    for o in (out, out2):
+        if o is not None:
+            assert o.is_cuda and o.dtype == torch.float32 and o.is_contiguous() and o.shape == x.shape
+    y = torch.empty_like(x) if out is None else out
+    y2 = (torch.empty_like(x) if out2 is None else out2) if second else None
     with torch.cuda.device(x.device):
-        if packed or mask_src is None:      # the extended entry point (drain interval); mask_bits may be NULL
+        if tail:
+            assert mask_src is None or tail // mask_div == N - tail
+            _lib.check(lib.cmf_conv3x3_c64_joint(N, int(tail), H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src),
+                                                 int(mask_div), int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2),
+                                                 int(drain), _stream()), "cmf_conv3x3_c64_joint")
+        elif packed or mask_src is None:      # the extended entry point (drain interval); mask_bits may be NULL
             _lib.check(lib.cmf_conv3x3_c64_fused_bits(N, H, W, _ptr(x), _ptr(wsplit), _ptr(bias), _ptr(mask_src),
                                                       int(mask_div), int(bool(mask_first)), _ptr(res), _ptr(y), _ptr(y2),
                                                       int(drain), _stream()), "cmf_conv3x3_c64_fused_bits")

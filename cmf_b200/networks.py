@@ -179,24 +179,101 @@ class _ResidualStackTangent(torch.autograd.Function):
         return (g, None, *grads)
 
 
+class _ResidualStackJoint(torch.autograd.Function):
+    """Primal AND tangents through a run of residual blocks as ONE autograd node on the tcgen05
+    convolution kernels (`networks.py:62-79` of the reference applied per block, for the primal and
+    for every tangent column).  Per block, with m0 = (x > 0), m1 = (h1 > 0) taken from the primal:
+
+        primal   :  h1 = conv1(m0 x) + b1;      x' = conv2(m1 h1) + b2 + x
+        tangents :  C1 = conv1(m0 V);           V' = conv2(m1 C1) + V
+
+    Both rows have the same structure, so every saved activation is ONE buffer of B*d + B images
+    (tangent images first, the B primal images last) and the backward pass runs each data-gradient
+    and each weight-gradient launch once on that joint batch (`cmf_conv3x3_c64_joint`): the weight
+    gradient of a convolution is the sum of its primal and tangent uses, which is exactly what one
+    launch over the concatenated images accumulates.  That removes the 2/3 of the N = B launches that
+    the separate primal autograd convolutions used to issue (they fill a third of the SMs).
+    In the forward pass the tangent launch of a convolution needs the primal result of the SAME
+    convolution (its relu-JVP mask), so the primal still runs one small launch ahead.
+    The masks come from the primal activations and are not differentiated (the reference's relu JVP,
+    `jvp_layers.py:38-46`, is piecewise constant in them)."""
+
+    @staticmethod
+    def forward(ctx, h, V, d, *tensors):
+        from . import kernels
+        K = len(tensors) // 4
+        B, Nt = h.shape[0], V.shape[0]
+        shape = (Nt + B, *h.shape[1:])
+        x, S = h.contiguous(), V.contiguous()
+        new = lambda: torch.empty(shape, dtype=h.dtype, device=h.device)
+        xb = kernels.relu_mask_pack(x)
+        A0 = new()
+        torch.clamp_min(x, 0, out=A0[Nt:])
+        torch.mul(S.view(B, d, *S.shape[1:]), _bcast((x > 0).to(S.dtype)), out=A0[:Nt].view(B, d, *S.shape[1:]))
+        xbits, hbits, saved = [], [], []
+        for k in range(K):
+            w1, b1, w2, b2 = tensors[4 * k:4 * k + 4]
+            ws1, ws2 = kernels.conv3x3_c64_prep(w1, False), kernels.conv3x3_c64_prep(w2, False)
+            h1 = kernels.conv3x3_c64(A0[Nt:], ws1, b1)                                   # primal, one launch ahead
+            hb = kernels.relu_mask_pack(h1)
+            A1 = new()
+            torch.clamp_min(h1, 0, out=A1[Nt:])
+            kernels.conv3x3_c64(A0[:Nt], ws1, None, mask_src=hb, mask_div=d, mask_first=True, out=A1[:Nt])
+            x = kernels.conv3x3_c64(A1[Nt:], ws2, b2, res=x)
+            xbits.append(xb); hbits.append(hb); saved += [A0, A1]
+            if k + 1 < K:
+                xb = kernels.relu_mask_pack(x)
+                A0 = new()
+                torch.clamp_min(x, 0, out=A0[Nt:])
+                S, _ = kernels.conv3x3_c64(A1[:Nt], ws2, None, mask_src=xb, mask_div=d, res=S, second=True, out2=A0[:Nt])
+            else:
+                S = kernels.conv3x3_c64(A1[:Nt], ws2, None, res=S)
+        ctx.d, ctx.K, ctx.Nt = d, K, Nt
+        ctx.save_for_backward(*xbits, *hbits, *tensors[0::4], *tensors[2::4], *saved)
+        return x, S
+
+    @staticmethod
+    def backward(ctx, g_h, g_S):
+        from . import kernels
+        K, d, Nt = ctx.K, ctx.d, ctx.Nt
+        t = ctx.saved_tensors
+        xbits, hbits, w1s, w2s, saved = t[:K], t[K:2 * K], t[2 * K:3 * K], t[3 * K:4 * K], t[4 * K:]
+        g = torch.empty_like(saved[0])
+        for part, src in ((g[:Nt], g_S), (g[Nt:], g_h)):
+            if src is None:
+                part.zero_()
+            else:
+                part.copy_(src)
+        grads = [None] * (4 * K)
+        for k in reversed(range(K)):
+            A0, A1 = saved[2 * k], saved[2 * k + 1]
+            grads[4 * k + 2] = kernels.conv3x3_c64_wgrad(A1, g)
+            grads[4 * k + 3] = g[Nt:].sum(dim=(0, 2, 3))
+            gC1 = kernels.conv3x3_c64(g, kernels.conv3x3_c64_prep(w2s[k], True), None, mask_src=hbits[k], mask_div=d,
+                                      mask_first=True, drain=_BWD_DRAIN, tail=Nt)
+            grads[4 * k + 0] = kernels.conv3x3_c64_wgrad(A0, gC1)
+            grads[4 * k + 1] = gC1[Nt:].sum(dim=(0, 2, 3))
+            g = kernels.conv3x3_c64(gC1, kernels.conv3x3_c64_prep(w1s[k], True), None, mask_src=xbits[k], mask_div=d,
+                                    mask_first=True, res=g, drain=_BWD_DRAIN, tail=Nt)
+        return (g[Nt:], g[:Nt], None, *grads)
+
+
 def _residual_stack_jvp(blocks, h: Tensor, Hv: Tensor, d: int):
-    """primal (autograd, per block) + tangents (one fused node) through consecutive residual blocks"""
+    """primal + tangents through consecutive residual blocks: one joint autograd node on the tcgen05
+    kernels when the shapes qualify, the per-block library path otherwise"""
     from . import kernels
     N, _, H, W = Hv.shape
     fused = (_tc_conv_enabled() and all(b.conv1.weight.shape == (64, 64, 3, 3) for b in blocks) and Hv.shape[1] == 64
-             and kernels.conv3x3_c64_usable(N, H, W) and kernels.conv3x3_c64_wgrad_usable(N, H, W))
+             and h.dtype == torch.float32 and N == h.shape[0] * d
+             and kernels.conv3x3_c64_usable(N + h.shape[0], H, W) and kernels.conv3x3_c64_wgrad_usable(N + h.shape[0], H, W))
     if not fused:
         for b in blocks:
             h, Hv = b.jvp_batched(h, Hv, d)
         return h, Hv
     args = []
     for b in blocks:
-        x_in = h
-        h1, _ = _conv3x3_pair(b.conv1, torch.relu(x_in), None)
-        h2, _ = _conv3x3_pair(b.conv2, torch.relu(h1), None)
-        h = h2 + x_in
-        args += [x_in.detach(), h1.detach(), b.conv1.weight, b.conv2.weight]
-    return h, _ResidualStackTangent.apply(Hv, d, *args)
+        args += [b.conv1.weight, b.conv1.bias, b.conv2.weight, b.conv2.bias]
+    return _ResidualStackJoint.apply(h, Hv, d, *args)
 
 
 def _mask_rows(V: Tensor, keep: Tensor, d: int) -> Tensor:

@@ -175,6 +175,15 @@ int cmf_relu_mask_pack(int N, int HW, const float* x, uint32_t* bits, cmf_stream
 int cmf_conv3x3_c64_fused_bits(int N, int H, int W, const float* x, const float* wsplit, const float* bias,
                                const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
                                float* y, float* y2, int drain_stages, cmf_stream_t stream);
+/* Joint batch (one launch for the tangents AND the primal of a residual-block convolution in the
+ * backward pass, where nothing orders them): images [0, Nt) are tangent images -- image n belongs to
+ * sample n / mask_div and gets no bias -- and images [Nt, N) are the primal images of samples
+ * 0 .. N - Nt - 1 (Nt / mask_div == N - Nt), which read mask row n - Nt and are the only ones that get
+ * `bias`.  Everything else as cmf_conv3x3_c64_fused_bits.  Replaces the separate aten::convolution_backward
+ * calls autograd issues for the primal and the tangent use of one weight (networks.py:62-79). */
+int cmf_conv3x3_c64_joint(int N, int Nt, int H, int W, const float* x, const float* wsplit, const float* bias,
+                          const uint32_t* mask_bits, int mask_div, int mask_first, const float* res,
+                          float* y, float* y2, int drain_stages, cmf_stream_t stream);
 /* drain_stages = K = 32 stages accumulated on the tensor core (truncating FP32 adds) between two
  * round-to-nearest drains into registers: 1 for everything that feeds the metric G (its inverse
  * amplifies forward errors by cond(G) ~ 5e3), 2 for the data-gradient launches of the backward

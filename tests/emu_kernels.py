@@ -123,17 +123,34 @@ def _unpack_mask(bits, H, W):
     return b.permute(0, 2, 3, 1).reshape(N, 64, H, W).bool()
 
 
-def conv3x3_c64(x, wsplit, bias=None, mask_src=None, mask_div=1, mask_first=False, res=None, second=False, drain=1):
-    t = torch.nn.functional.conv2d(x, wsplit, bias, padding=1)
+def conv3x3_c64(x, wsplit, bias=None, mask_src=None, mask_div=1, mask_first=False, res=None, second=False, drain=1,
+                tail=0, out=None, out2=None):
+    N = x.shape[0]
+    t = torch.nn.functional.conv2d(x, wsplit, None, padding=1)
+    if bias is not None:
+        if tail:
+            t[tail:] = t[tail:] + bias.view(1, -1, 1, 1)
+        else:
+            t = t + bias.view(1, -1, 1, 1)
     m = None
     if mask_src is not None:
         keep = _unpack_mask(mask_src, *x.shape[2:]) if mask_src.dtype == torch.int32 else mask_src > 0
-        m = keep.to(t.dtype).repeat_interleave(mask_div, dim=0)
+        keep = keep.to(t.dtype)
+        m = torch.cat((keep.repeat_interleave(mask_div, dim=0), keep)) if tail else keep.repeat_interleave(mask_div, dim=0)
     if mask_first:
         t = t * m
     if res is not None:
         t = t + res
-    return (t, t * m) if second else t
+    if out is not None:
+        out.copy_(t)
+        t = out
+    if second:
+        t2 = t * m
+        if out2 is not None:
+            out2.copy_(t2)
+            t2 = out2
+        return t, t2
+    return t
 
 
 def conv3x3_c64_wgrad_usable(N, H, W):
