@@ -81,6 +81,18 @@ class Squeeze2dBijection(ReshapingBijection):
         return z.reshape(-1, c, f, f, h // f, w // f).permute(0, 1, 4, 2, 5, 3).reshape(-1, c, h, w)
 
 
+class RandomChannelwisePermutationBijection(ReshapingBijection):
+    """`reshaping.py:32-44` (the schema's ``rand-channel-perm`` between ``nsf-c`` layers)."""
+
+    def __init__(self, x_shape):
+        super().__init__(x_shape, x_shape)
+        self.register_buffer("permutation", torch.randperm(x_shape[0]))
+        self.register_buffer("inverse_permutation", torch.argsort(self.permutation))
+
+    def reshape_x(self, x): return x[:, self.permutation]
+    def reshape_z(self, z): return z[:, self.inverse_permutation]
+
+
 # ---- elementwise preprocessing above the head (`math.py:9-105`) -------------------------------
 class ScalarMultiplicationBijection(Bijection):
     def __init__(self, x_shape, value):
@@ -261,3 +273,100 @@ class AlternatingChannelwiseAffineCouplingBijection(ChannelwiseAffineCouplingBij
         out[:, ::2] = a
         out[:, 1::2] = b
         return out
+
+
+# ---- rational-quadratic spline coupling (`bijections/nsf.py:45-84`) -----------------------------
+class _UnconditionalRQ(nn.Module):
+    """Parameters of nsf's ``PiecewiseRationalQuadraticCDF`` on the identity features
+    (`gitmodules/nsf/nde/transforms/nonlinearities.py:337-369`, linear tails, random init)."""
+
+    def __init__(self, features: int, num_bins: int):
+        super().__init__()
+        self.unnormalized_widths = nn.Parameter(torch.rand(features, num_bins))
+        self.unnormalized_heights = nn.Parameter(torch.rand(features, num_bins))
+        self.unnormalized_derivatives = nn.Parameter(torch.rand(features, num_bins - 1))
+
+
+class _RQCouplingFlow(nn.Module):
+    """Container with the attribute names of nsf's ``PiecewiseRationalQuadraticCouplingTransform``
+    (`gitmodules/nsf/nde/transforms/coupling.py:14-57,399-431`) so state-dict keys match."""
+
+    def __init__(self, features: int, even: bool, net_factory, num_bins: int):
+        super().__init__()
+        mask = torch.zeros(features, dtype=torch.uint8)
+        mask[(0 if even else 1)::2] += 1                      # utils/torchutils.py:87-98
+        idx = torch.arange(features)
+        self.register_buffer("identity_features", idx[mask <= 0])
+        self.register_buffer("transform_features", idx[mask > 0])
+        n_id, n_tr = int(self.identity_features.numel()), int(self.transform_features.numel())
+        self.transform_net = net_factory(n_id, n_tr * (3 * num_bins - 1))
+        self.unconditional_transform = _UnconditionalRQ(n_id, num_bins)
+
+
+class CoupledRationalQuadraticSplineBijection(Bijection):
+    """``nsf-c`` layer (`bijections/nsf.py:45-84`): alternating binary mask, ResidualNet conditioner,
+    linear tails, ``apply_unconditional_transform=True`` (the identity features go through a spline
+    with free parameters).  ``x_to_z`` / ``z_to_x`` here are plain torch on the reference's knot
+    arithmetic; the z -> x push WITH tangents -- which the reference does not have at all
+    -- is compiled into the layer program (``cmf_b200.program.RqsStep``) and runs on
+    ``cmf_rqs_coupling_jvp_fwd/bwd``."""
+
+    def __init__(self, num_input_channels: int, num_hidden_layers: int, num_hidden_channels: int, num_bins: int,
+                 tail_bound: float, dropout_probability: float, reverse_mask: bool):
+        from .splines import ResidualNet
+        super().__init__((num_input_channels,), (num_input_channels,))
+        self.num_bins, self.tail_bound = num_bins, float(tail_bound)
+        self.flow = _RQCouplingFlow(
+            num_input_channels, reverse_mask,
+            lambda n_in, n_out: ResidualNet(n_in, n_out, num_hidden_channels, num_hidden_layers, dropout_probability),
+            num_bins)
+
+    # -- knot tables ---------------------------------------------------------------------------
+    def unconditional_tables(self, batch: int):
+        """(cw, ch, dv), each (batch, n_id, K+1): the free-parameter spline of the identity half"""
+        from .splines import knot_tables
+        u = self.flow.unconditional_transform
+        params = torch.cat((u.unnormalized_widths, u.unnormalized_heights, u.unnormalized_derivatives), dim=-1)
+        cw, ch, dv, _, _, _ = knot_tables(params.unsqueeze(0), None, self.num_bins, self.tail_bound)
+        exp = lambda t: t.expand(batch, *t.shape[1:]).contiguous()
+        return exp(cw), exp(ch), exp(dv)
+
+    def conditional_tables(self, x_id: Tensor, V_id):
+        """knot tables of the transformed half (and their tangents) from the conditioner"""
+        from .splines import knot_tables
+        net = self.flow.transform_net
+        p, P = net.jvp_batched(x_id, V_id)
+        B, M = x_id.shape[0], int(self.flow.transform_features.numel())
+        p = p.view(B, M, 3 * self.num_bins - 1)
+        if P is not None:
+            P = P.view(B, P.shape[1], M, 3 * self.num_bins - 1)
+        return knot_tables(p, P, self.num_bins, self.tail_bound, hidden_features=net.hidden_features)
+
+    # -- encode pass / sampling (plain torch) ---------------------------------------------------
+    def _x_to_z(self, x, **kw):
+        from .splines import rq_spline_from_tables
+        f = self.flow
+        x_id, x_tr = x[:, f.identity_features], x[:, f.transform_features]
+        cw, ch, dv, _, _, _ = self.conditional_tables(x_id, None)              # coupling.py:74-81
+        z_tr, lad = rq_spline_from_tables(x_tr, cw, ch, dv, False, self.tail_bound)
+        z_id, lad_id = rq_spline_from_tables(x_id, *self.unconditional_tables(x.shape[0]), False, self.tail_bound)
+        z = torch.empty_like(x)
+        z[:, f.identity_features] = z_id
+        z[:, f.transform_features] = z_tr
+        return {"z": z, "log-jac": (lad.sum(1) + lad_id.sum(1)).view(-1, 1)}
+
+    def _z_to_x(self, z, **kw):
+        from .splines import rq_spline_from_tables
+        f = self.flow
+        z_id, z_tr = z[:, f.identity_features], z[:, f.transform_features]
+        x_id, lad_id = rq_spline_from_tables(z_id, *self.unconditional_tables(z.shape[0]), True, self.tail_bound)
+        cw, ch, dv, _, _, _ = self.conditional_tables(x_id, None)              # coupling.py:103-114
+        x_tr, lad = rq_spline_from_tables(z_tr, cw, ch, dv, True, self.tail_bound)
+        x = torch.empty_like(z)
+        x[:, f.identity_features] = x_id
+        x[:, f.transform_features] = x_tr
+        return {"x": x, "log-jac": (lad.sum(1) + lad_id.sum(1)).view(-1, 1)}
+
+    def partition(self):
+        f = self.flow
+        return f.identity_features, f.transform_features

@@ -145,6 +145,20 @@ def get_schema(config: Dict) -> List[dict]:
     elif ty == "multiscale-realnvp":
         body = _multiscale_realnvp(config["g_hidden_channels"], config.get("resnet_batchnorm", True),
                                    config.get("ignore_batch_effects", False), config.get("smaller_realnvp", False))
+    elif ty == "nsf":
+        # config/schemas.py:152-162,586-626 with the `normalise` entries already removed (:22).  Only the
+        # coupling variant can carry tangents; the reference itself has no spline _jvp at all.
+        if config["autoregressive"] or config.get("use_linear", True):
+            raise ValueError("schema_type nsf on the non-square JVP stack needs autoregressive=False and "
+                             "use_linear=False (nsf-ar and LU-linear layers have no JVP rule)")
+        body = [{"type": "flatten"}]
+        for i in range(config["num_density_layers"]):
+            body += [{"type": "rand-channel-perm"},
+                     {"type": "nsf-c", "num_hidden_channels": config["num_hidden_channels"],
+                      "num_hidden_layers": config["num_hidden_layers"], "num_bins": config["num_bins"],
+                      "tail_bound": config["tail_bound"], "activation": "relu",
+                      "dropout_probability": config["dropout_probability"], "reverse_mask": i % 2 == 0}]
+        body.append({"type": "rand-channel-perm"})
     else:
         raise ValueError(f"schema_type {ty} has no JVP path in the reference")
 

@@ -82,6 +82,19 @@ def get_bijection(layer: dict, x_shape):
         return bj.ScalarAdditionBijection(x_shape, layer["value"])
     if ty == "affine":
         return bj.AffineBijection(x_shape, layer["per_channel"])
+    if ty == "rand-channel-perm":                       # factory.py:291-292
+        return bj.RandomChannelwisePermutationBijection(x_shape)
+    if ty == "nsf-c":                                   # factory.py:316-327
+        assert len(x_shape) == 1
+        if layer["activation"] != "relu":
+            raise ValueError("nsf-c: only the relu conditioner (config/schemas.py:608) is built")
+        return bj.CoupledRationalQuadraticSplineBijection(
+            num_input_channels=x_shape[0], num_hidden_layers=layer["num_hidden_layers"],
+            num_hidden_channels=layer["num_hidden_channels"], num_bins=layer["num_bins"], tail_bound=layer["tail_bound"],
+            dropout_probability=layer["dropout_probability"], reverse_mask=layer["reverse_mask"])
+    if ty in ("nsf-ar", "linear"):
+        raise ValueError(f"layer type {ty} has no JVP rule (autoregressive splines / LU linear layers cannot sit on "
+                         "the non-square JVP stack; use autoregressive=False, use_linear=False)")
     raise ValueError(f"Invalid layer type {ty} for the non-square path")
 
 

@@ -27,7 +27,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .bijections import AffineCouplingBijection, ReshapingBijection
+from .bijections import AffineCouplingBijection, CoupledRationalQuadraticSplineBijection, ReshapingBijection
 from .densities import BijectionDensity, NonSquareTailDensity, SplitDensity
 
 Tensor = torch.Tensor
@@ -72,6 +72,20 @@ class AclStep:
     hw: int = 0                        # H*W of the conditioner output (compact tail only)
 
 
+@dataclass
+class RqsStep:
+    """``nsf-c`` layer (`bijections/nsf.py:45-84`, inverse direction of nsf `coupling.py:90-122`): the
+    identity half goes through the free-parameter spline, the conditioner (with all tangents) reads the
+    result, the transformed half goes through the conditional spline -- both on the spline kernel."""
+    bijection: CoupledRationalQuadraticSplineBijection
+    ident: int                   # slot holding the identity features (B, n_id), natural order
+    mod: int                     # slot holding the transformed features (B, M), natural order
+    out_ident: int
+    out_mod: int
+    n_id: int = 0
+    M: int = 0
+
+
 class LayerProgram:
     def __init__(self, head_prior):
         """``head_prior``: the density subtree below the head (``head.prior``)."""
@@ -91,7 +105,7 @@ class LayerProgram:
         while not isinstance(node, NonSquareTailDensity):
             if isinstance(node, BijectionDensity):
                 bij = node.bijection
-                if not isinstance(bij, (AffineCouplingBijection, ReshapingBijection)):
+                if not isinstance(bij, (AffineCouplingBijection, ReshapingBijection, CoupledRationalQuadraticSplineBijection)):
                     raise ValueError(f"Cannot handle bijection of class {type(bij).__name__} on the JVP path")
                 nodes.append(bij)
                 node = node.prior
@@ -119,8 +133,9 @@ class LayerProgram:
             blocks.append(SymBlock(None, np.sort(perm[d:])))
         for node in reversed(self.nodes):
             if isinstance(node, ReshapingBijection):
-                probe = torch.arange(D).view(1, *node.z_shape)
-                src = node.reshape_z(probe).flatten().numpy()      # x[p] = z[src[p]]
+                bufs = list(node.buffers())                        # a permutation layer indexes with its buffer
+                probe = torch.arange(D, device=bufs[0].device if bufs else None).view(1, *node.z_shape)
+                src = node.reshape_z(probe).flatten().cpu().numpy()      # x[p] = z[src[p]]
                 new_pos = np.empty(D, dtype=np.int64)
                 new_pos[src] = np.arange(D)
                 for b in blocks:
@@ -129,6 +144,8 @@ class LayerProgram:
                 assert node.dim == 1
                 blocks.append(SymBlock(None, np.arange(D, 2 * D, dtype=np.int64)))
                 D *= 2
+            elif isinstance(node, CoupledRationalQuadraticSplineBijection):
+                blocks = self._compile_rqs(node, blocks, D)
             else:
                 blocks = self._compile_acl(node, blocks, D)
         self.final_blocks = blocks
@@ -191,6 +208,24 @@ class LayerProgram:
         out = self._new_slot()
         self.steps.append(AclStep(bij, cond, tuple(in_shape), mod, out, cmap, cinv, mod_pos.size, Q, pos, hw))
         return keep_blocks + [SymBlock(out, mod_pos)]
+
+    def _compile_rqs(self, bij, blocks: List[SymBlock], D: int) -> List[SymBlock]:
+        """Both halves change (a spline does not fix 0, so zero padding is materialised too): the
+        identity features and the transformed features are each assembled into one compact slot in
+        natural order and replaced by the step's two outputs."""
+        ident_pos, mod_pos = (t.cpu().numpy().astype(np.int64) for t in bij.partition())
+        assert ident_pos.size + mod_pos.size == D
+        ident = self._assemble_any(blocks, ident_pos, D)
+        mod = self._assemble_any(blocks, mod_pos, D)
+        out_i, out_m = self._new_slot(), self._new_slot()
+        self.steps.append(RqsStep(bij, ident, mod, out_i, out_m, int(ident_pos.size), int(mod_pos.size)))
+        return [SymBlock(out_i, ident_pos), SymBlock(out_m, mod_pos)]
+
+    def _assemble_any(self, blocks: Sequence[SymBlock], target: np.ndarray, D: int) -> int:
+        """:meth:`_assemble` over whatever blocks hold the target positions (blocks may straddle them)"""
+        want = np.zeros(D, dtype=bool)
+        want[target] = True
+        return self._assemble([b for b in blocks if want[b.pos].any()], target, D)
 
     def _assemble(self, blocks: Sequence[SymBlock], target: np.ndarray, D: int) -> int:
         """Slot whose element i is the value at logical position target[i] (0 where target[i] < 0
@@ -262,6 +297,15 @@ class LayerProgram:
                 x = torch.zeros(B, step.n, dtype=z.dtype, device=dev)
                 V = None if m is None else torch.zeros(B, m, step.n, dtype=z.dtype, device=dev)
                 slots[step.out] = (x, V)
+            elif isinstance(step, RqsStep):
+                bij, tb = step.bijection, step.bijection.tail_bound
+                x_id, V_id = slots[step.ident]
+                ucw, uch, udv = bij.unconditional_tables(B)
+                zero_t = None if m is None else torch.zeros(B, m, *ucw.shape[1:], dtype=z.dtype, device=dev)
+                x_id, V_id, _ = ops.rqs_coupling_jvp(x_id, V_id, ucw, uch, udv, zero_t, zero_t, zero_t, tb)
+                z_m, V_m = slots[step.mod]
+                x_m, V_m, _ = ops.rqs_coupling_jvp(z_m, V_m, *bij.conditional_tables(x_id, V_id), tb)
+                slots[step.out_ident], slots[step.out_mod] = (x_id, V_id), (x_m, V_m)
             else:
                 xc, Vc = slots[step.cond]
                 x_in = xc.view(B, *step.in_shape)
@@ -295,6 +339,8 @@ class LayerProgram:
                 lines.append(f"gather  {s.srcs} -> {s.out}  n_out={s.idx.size}")
             elif isinstance(s, ZerosStep):
                 lines.append(f"zeros   -> {s.out}  n={s.n}")
+            elif isinstance(s, RqsStep):
+                lines.append(f"rqs     ident={s.ident} mod={s.mod} -> {s.out_ident},{s.out_mod}  n_id={s.n_id} M={s.M}")
             else:
                 lines.append(f"acl     {type(s.bijection).__name__}: cond={s.cond} mod={s.mod} -> {s.out}  "
                              f"M={s.M} Q={s.Q} {'mapped' if s.map is not None else ('compact-tail' if s.pos is not None else 'identity')}")
@@ -303,3 +349,7 @@ class LayerProgram:
     def modified_elements(self) -> int:
         """sum_l M_l, the factor of the kernel-(a) byte model."""
         return sum(s.M for s in self.steps if isinstance(s, AclStep))
+
+    def spline_elements(self) -> int:
+        """elements pushed through the spline kernel per sample (identity + transformed halves)"""
+        return sum(s.M + s.n_id for s in self.steps if isinstance(s, RqsStep))

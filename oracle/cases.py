@@ -72,6 +72,20 @@ CASES = {
     "img8_hutch_d8": dict(dataset="mnist", x_shape=(1, 8, 8), batch=4, epoch=60, data="pixels", hutch=True,
                           overrides=dict(g_ij_loss=True, latent_dimension=8, g_hidden_channels=[8, 8],
                                          prior_num_density_layers=2, log_jacobian_method="hutch_with_cg")),
+    # north_star's "rational-quadratic-spline coupling" layers ON the JVP stack (nsf-c):
+    # schema_type nsf with the coupling variant and no LU-linear layers.  The reference has no spline
+    # _jvp; oracle/gen_golden.py gives its bijection class the autograd JVP of the nsf transform
+    # (torch.autograd.functional.jvp over flow.inverse) and then runs the reference unchanged.
+    "power_nsfc_gij_d4": dict(dataset="power", x_shape=(6,), batch=10, epoch=60, data="uniform",
+                              overrides=dict(g_ij_loss=True, latent_dimension=4, schema_type="nsf", autoregressive=False,
+                                             use_linear=False, num_density_layers=3, num_hidden_layers=2,
+                                             num_hidden_channels=16, num_bins=6, tail_bound=3, dropout_probability=0.0,
+                                             **COMMON)),
+    "hepmass_nsfc_gij_d10": dict(dataset="hepmass", x_shape=(21,), batch=6, epoch=60, data="uniform",
+                                 overrides=dict(g_ij_loss=True, latent_dimension=10, schema_type="nsf", autoregressive=False,
+                                                use_linear=False, num_density_layers=4, num_hidden_layers=2,
+                                                num_hidden_channels=32, num_bins=8, tail_bound=3, dropout_probability=0.0,
+                                                **COMMON)),
     # BASELINE.json configs[4] (CIFAR-shape latent sweep) at reduced size: 3x16x16 -> d=160 > 128,
     # the regime of the panel-blocked Cholesky and the multi-tile tcgen05 Gram
     "img16c3_gij_d160": dict(dataset="cifar10", x_shape=(3, 16, 16), batch=2, epoch=60, data="pixels",

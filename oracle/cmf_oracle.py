@@ -289,6 +289,86 @@ def _squeeze_layer(shape, f) -> _Reshape:
     return _Reshape(shape, zs, fwd, inv)
 
 
+class _RandPerm(_Layer):
+    """`reshaping.py:32-44` RandomChannelwisePermutationBijection (``rand-channel-perm``)."""
+
+    def __init__(self, shape, params: Params, prefix: str):
+        self.x_shape = self.z_shape = tuple(shape)
+        self.perm, self.inv = params[prefix + "permutation"], params[prefix + "inverse_permutation"]
+
+    def x_to_z(self, x): return x[:, self.perm], None
+    def z_to_x(self, z): return z[:, self.inv]
+    def jvp(self, z, v): return z[:, self.inv], v[:, self.inv]
+
+
+class _NsfCoupling(_Layer):
+    """``nsf-c``: `bijections/nsf.py:45-84` = nsf ``PiecewiseRationalQuadraticCouplingTransform``
+    (`gitmodules/nsf/nde/transforms/coupling.py:60-122,399-473`) with an alternating binary mask
+    (`utils/torchutils.py:87-98`), a ResidualNet conditioner (`nn/resnet.py:10-105`, relu, no batch
+    norm, no context), linear tails and the unconditional spline on the identity features
+    (`nonlinearities.py:337-406`).  The spline arithmetic is ``oracle/rqs_oracle.py``.
+    The reference has no ``_jvp`` for this bijection: the oracle's is the autograd JVP of
+    the z -> x map, ``torch.autograd.functional.jvp`` -- the same definition ``oracle/gen_golden.py``
+    gives the reference class when it generates the fixture."""
+
+    def __init__(self, shape, layer: dict, params: Params, prefix: str):
+        import rqs_oracle as R
+        self.R = R
+        self.x_shape = self.z_shape = tuple(shape)
+        n = shape[0]
+        start = 0 if layer["reverse_mask"] else 1                 # even=reverse_mask: nsf.py:74-77
+        mask = torch.zeros(n, dtype=torch.bool)
+        mask[start::2] = True
+        idx = torch.arange(n)
+        self.tr, self.ident = idx[mask], idx[~mask]
+        self.K, self.tb = layer["num_bins"], float(layer["tail_bound"])
+        self.hidden, self.blocks = layer["num_hidden_channels"], layer["num_hidden_layers"]
+        self.p, self.prefix = params, prefix + "flow."
+
+    def _net(self, h):
+        p, pre = self.p, self.prefix + "transform_net."
+        h = F.linear(h, p[pre + "initial_layer.weight"], p[pre + "initial_layer.bias"])
+        for i in range(self.blocks):
+            t = F.linear(torch.relu(h), p[f"{pre}blocks.{i}.linear_layers.0.weight"], p[f"{pre}blocks.{i}.linear_layers.0.bias"])
+            t = F.linear(torch.relu(t), p[f"{pre}blocks.{i}.linear_layers.1.weight"], p[f"{pre}blocks.{i}.linear_layers.1.bias"])
+            h = h + t
+        return F.linear(h, p[pre + "final_layer.weight"], p[pre + "final_layer.bias"])
+
+    def _uncond(self, t, inverse):
+        u = self.prefix + "unconditional_transform."
+        prm = torch.cat((self.p[u + "unnormalized_widths"], self.p[u + "unnormalized_heights"],
+                         self.p[u + "unnormalized_derivatives"]), dim=-1)
+        prm = prm.unsqueeze(0).expand(t.shape[0], *prm.shape)
+        out, lad, _ = self.R.unconstrained_rqs(t, prm, self.K, self.tb, inverse)
+        return out, lad.sum(1, keepdim=True)
+
+    def _cond(self, t, ident, inverse):
+        prm = self._net(ident).view(t.shape[0], self.tr.numel(), 3 * self.K - 1)
+        out, lad, _ = self.R.unconstrained_rqs(t, prm, self.K, self.tb, inverse, hidden_features=self.hidden)
+        return out, lad.sum(1, keepdim=True)
+
+    def x_to_z(self, x):                                           # coupling.py:60-88
+        ident, tr = x[:, self.ident.to(x.device)], x[:, self.tr.to(x.device)]
+        z_tr, lad = self._cond(tr, ident, False)
+        z_id, lad_id = self._uncond(ident, False)
+        z = torch.empty_like(x)
+        z[:, self.ident.to(x.device)] = z_id
+        z[:, self.tr.to(x.device)] = z_tr
+        return z, lad + lad_id
+
+    def z_to_x(self, z):                                           # coupling.py:90-122
+        ident, tr = z[:, self.ident.to(z.device)], z[:, self.tr.to(z.device)]
+        x_id, _ = self._uncond(ident, True)
+        x_tr, _ = self._cond(tr, x_id, True)
+        x = torch.empty_like(z)
+        x[:, self.ident.to(z.device)] = x_id
+        x[:, self.tr.to(z.device)] = x_tr
+        return x
+
+    def jvp(self, z, v):
+        return torch.autograd.functional.jvp(self.z_to_x, z, v, create_graph=torch.is_grad_enabled())
+
+
 class _Elementwise(_Layer):
     """`math.py:9-105` preprocessing bijections above the head (scalar-mult, scalar-add, logit).
     Only ``x_to_z`` is on the path.  They sit ABOVE the head as BijectionDensity nodes, so their
@@ -429,6 +509,10 @@ class OracleFlow:
                 prefix += "prior."
             elif ty == "flatten":
                 node = _flatten_layer(shape); prefix += "prior."
+            elif ty == "rand-channel-perm":
+                node = _RandPerm(shape, params, prefix + "bijection."); prefix += "prior."
+            elif ty == "nsf-c":
+                node = _NsfCoupling(shape, layer, params, prefix + "bijection."); prefix += "prior."
             elif ty == "squeeze":
                 node = _squeeze_layer(shape, layer["factor"]); prefix += "prior."
             elif ty in ("scalar-mult", "scalar-add", "logit"):
@@ -716,6 +800,27 @@ def param_spec(schema: Sequence[dict], x_shape: Sequence[int]) -> Dict[str, tupl
             prefix += "prior."
         elif ty == "flatten":
             shape = (int(math.prod(shape)),); prefix += "prior."
+        elif ty == "rand-channel-perm":
+            spec[prefix + "bijection.permutation"] = (shape[0],)
+            spec[prefix + "bijection.inverse_permutation"] = (shape[0],)
+            prefix += "prior."
+        elif ty == "nsf-c":
+            n, K, hdn = shape[0], layer["num_bins"], layer["num_hidden_channels"]
+            n_tr = len(range(0 if layer["reverse_mask"] else 1, n, 2))
+            n_id = n - n_tr
+            fp = prefix + "bijection.flow."
+            spec[fp + "transform_net.initial_layer.weight"] = (hdn, n_id)
+            spec[fp + "transform_net.initial_layer.bias"] = (hdn,)
+            for i in range(layer["num_hidden_layers"]):
+                for j in (0, 1):
+                    spec[f"{fp}transform_net.blocks.{i}.linear_layers.{j}.weight"] = (hdn, hdn)
+                    spec[f"{fp}transform_net.blocks.{i}.linear_layers.{j}.bias"] = (hdn,)
+            spec[fp + "transform_net.final_layer.weight"] = (n_tr * (3 * K - 1), hdn)
+            spec[fp + "transform_net.final_layer.bias"] = (n_tr * (3 * K - 1),)
+            spec[fp + "unconditional_transform.unnormalized_widths"] = (n_id, K)
+            spec[fp + "unconditional_transform.unnormalized_heights"] = (n_id, K)
+            spec[fp + "unconditional_transform.unnormalized_derivatives"] = (n_id, K - 1)
+            prefix += "prior."
         elif ty == "squeeze":
             f = layer["factor"]
             shape = (shape[0] * f * f, shape[1] // f, shape[2] // f); prefix += "prior."

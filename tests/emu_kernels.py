@@ -163,6 +163,52 @@ def conv3x3_c64_wgrad(x, g_y, deterministic=None):
                                                (False, True, False))[1]
 
 
-ALL = ["coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
+def _rqs_inverse(z, cw, ch, dv, tb):
+    """inverse spline from knot tables with linear tails: the restated nsf arithmetic of oracle/rqs_oracle.py"""
+    import rqs_oracle as R
+    inside = (z >= -tb) & (z <= tb)
+    out, _, idx = R.spline_from_tables(torch.where(inside, z, torch.zeros_like(z)), cw, ch, dv, True)
+    return torch.where(inside, out, z), torch.where(inside, idx, torch.full_like(idx, -1))
+
+
+def _rqs_push(z, V, cw, ch, dv, CW, CH, DV, tb, graph):
+    f = lambda a, b, c, e: _rqs_inverse(a, b, c, e, tb)[0]
+    x, bins = _rqs_inverse(z, cw, ch, dv, tb)
+    if V is None:
+        return x, None, bins
+    cols = [torch.autograd.functional.jvp(f, (z, cw, ch, dv), (V[:, k], CW[:, k], CH[:, k], DV[:, k]), create_graph=graph)[1]
+            for k in range(V.shape[1])]
+    return x, torch.stack(cols, 1), bins
+
+
+def rqs_coupling_jvp_fwd(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound):
+    x, Vo, bins = _rqs_push(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound, False)
+    return x.detach(), None if Vo is None else Vo.detach(), bins.to(torch.int32)
+
+
+def rqs_coupling_jvp_bwd(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound, g_x, g_V):
+    names = [z_m, V_m, cw, ch, dv, CW, CH, DV]
+    with torch.enable_grad():
+        leaves = [None if t is None else t.detach().clone().requires_grad_(True) for t in names]
+        z, V, a, b, c, A, Bq, Cq = leaves
+        x, Vo, _ = _rqs_push(z, V, a, b, c, A, Bq, Cq, tail_bound, True)
+        loss = 0.0 if g_x is None else (x * g_x).sum()
+        if Vo is not None and g_V is not None:
+            loss = loss + (Vo * g_V).sum()
+        live = [t for t in leaves if t is not None]
+        grads = torch.autograd.grad(loss, live, allow_unused=True)
+    it = iter(grads)
+    out = []
+    for t in leaves:
+        if t is None:
+            out.append(None)
+        else:
+            g = next(it)
+            out.append(torch.zeros_like(t) if g is None else g.detach())
+    g_z, g_Vin, g_cw, g_ch, g_dv, g_CW, g_CH, g_DV = out
+    return g_z, g_Vin, g_cw, g_ch, g_dv, g_CW, g_CH, g_DV
+
+
+ALL = ["rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

@@ -348,6 +348,54 @@ def test_hutch_with_cg_gradients_match_fp64_oracle(name, batch, m):
     assert len(flow_params) == len([k for k, v in params.items() if v.is_floating_point() and v.grad is not None])
 
 
+@pytest.mark.parametrize("name", ["power_nsfc_gij_d4", "hepmass_nsfc_gij_d10"])
+def test_nsfc_model_spline_bins_bit_exact_and_matches_fp64_oracle(name):
+    """``nsf-c`` layers on the JVP stack, model level: (1) every bin index the spline
+    kernel selects inside the model equals the reference's ``searchsorted`` over the very knots it was
+    given (`gitmodules/nsf/utils/torchutils.py:133-138`); (2) G, log det, penalty against the fp64
+    oracle (autograd JVP over the restated nsf transform) on fresh weights and inputs."""
+    import rqs_oracle as R
+    from cmf_b200 import ops
+    g = load_golden(name)
+    case = dict(CASES[name], batch=37)
+    density = build_product(g, "cpu")
+    filled = fill_state_dict(density.state_dict(), salt=4, gain=2.0)
+    density.load_state_dict(filled)
+    density = density.cuda().train()
+    x = make_input(case) * 1.7                      # some features beyond the tail bound after the flow
+    head, depth = find_head(strip_wrappers(density))
+    calls, real = [], ops.rqs_coupling_jvp
+
+    def spy(z_m, V_m, cw, ch, dv, CW, CH, DV, tb):
+        out = real(z_m, V_m, cw, ch, dv, CW, CH, DV, tb)
+        calls.append((z_m.detach().cpu(), ch.detach().cpu(), out[2].cpu(), tb))
+        return out
+    ops.rqs_coupling_jvp = spy
+    try:
+        with torch.no_grad():
+            z = head("extract-latent", x.cuda())
+            logdet, recon, gram, l1 = head._exact_log_det_jac_and_reconstruction(z, "offdiag")
+    finally:
+        ops.rqs_coupling_jvp = real
+    n_layers = sum(1 for l in g["schema"] if l["type"] == "nsf-c")
+    assert len(calls) == 2 * n_layers               # identity half + transformed half per layer
+    outside = 0
+    for z_m, ch, bins, tb in calls:
+        inside = (z_m >= -tb) & (z_m <= tb)
+        ref = torch.where(inside, R.searchsorted(ch, z_m), torch.full_like(bins, -1, dtype=torch.long))
+        assert torch.equal(bins.long(), ref), "spline bin indices must be bit-exact"
+        outside += int((~inside).sum())
+    params = {(k[7:] if k.startswith("module.") else k): (v.double() if v.is_floating_point() else v) for k, v in filled.items()}
+    flow = O.OracleFlow(g["schema"], params, case["x_shape"])
+    with torch.no_grad():
+        _, z64, _ = flow.encode(x.double())
+        ld64, _, gram64, _ = flow.exact_log_det(z64)
+    assert_close(z, z64, RTOL, atol=1e-6, what="latent")
+    assert_close(gram, gram64, RTOL, what="G")
+    assert_close(logdet, ld64, RTOL, atol=1e-4, what="log det")
+    record(name, "nsf-c model G vs fp64 oracle", float((gram.double().cpu() - gram64).abs().max() / gram64.abs().max()), RTOL)
+
+
 def test_hutch_with_cg_matches_oracle():
     """log_jacobian_method=hutch_with_cg with injected probes (the image-config default)."""
     g = load_golden("hepmass_gij_d10_warm")
