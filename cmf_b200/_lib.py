@@ -36,6 +36,11 @@ SIGNATURES = {
     "cmf_chol_logdet_bwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "cmf_rqs_coupling_jvp_fwd": (_i, [_i, _i, _i, _i, C.c_float] + [_vp] * 12),
     "cmf_rqs_coupling_jvp_bwd": (_i, [_i, _i, _i, _i, C.c_float] + [_vp] * 19),
+    "cmf_preproc_logit_fwd": (_i, [_i, _i, _vp, _vp, C.c_float, C.c_float, _vp, _vp, _vp]),
+    "cmf_coupling_x_to_z_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_coupling_x_to_z_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_sumsq_diff_fwd": (_i, [_i, _i, _vp, _vp, _vp, _vp]),
+    "cmf_sumsq_diff_bwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_conv3x3_c64_usable": (_i, [_i, _i, _i]),
     "cmf_conv3x3_c64_prep": (_i, [_vp, _i, _vp, _vp]),
     "cmf_conv3x3_c64_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp]),

@@ -170,6 +170,33 @@ class AffineCouplingBijection(Bijection):
         out = self.coupler(inputs)
         return out["shift"], out["log-scale"]
 
+    def _encode_maps(self, device):
+        """int32 index maps of ``cmf_coupling_x_to_z_fwd/bwd`` for this layer's partition (cached per device)"""
+        cache = self.__dict__.setdefault("_enc_maps", {})
+        key = str(device)
+        if key not in cache:
+            _, mod_pos, _, dense = self.partition()
+            mod_pos = mod_pos.to(device=device, dtype=torch.int64)
+            D, M = int(math.prod(self.x_shape)), int(mod_pos.numel())
+            pos2j = torch.full((D,), -1, dtype=torch.int32, device=device)
+            pos2j[mod_pos] = torch.arange(M, dtype=torch.int32, device=device)
+            if dense:       # the conditioner emits a full-resolution output; element at position i reads q = i
+                qmap = mod_pos.to(torch.int32)
+                q2pos = torch.full((D,), -1, dtype=torch.int32, device=device)
+                q2pos[mod_pos] = qmap
+            else:           # compact conditioner output in the order of mod_pos
+                qmap, q2pos = None, mod_pos.to(torch.int32)
+            cache[key] = (pos2j, qmap, q2pos)
+        return cache[key]
+
+    def _x_to_z_fused(self, x, conditioner_input):
+        """encode direction of `acl.py:43-46,101-111` on the fused kernel: one launch instead of the
+        split / exp / add / mul / combine / masked-sum string"""
+        from . import ops
+        st, _ = self.coupler.st_batched(conditioner_input, None)
+        z, lj = ops.coupling_x_to_z(x.flatten(1), st, *self._encode_maps(x.device))
+        return {"z": z.view_as(x), "log-jac": lj}
+
     def partition(self) -> Tuple[Tensor, Tensor, tuple, bool]:
         """(passthrough positions, modified positions, conditioner input shape, dense_input).
 
@@ -191,10 +218,7 @@ class Checkerboard2dAffineCouplingBijection(AffineCouplingBijection):
         self.register_buffer("mask", (1 - mask if reverse_mask else mask).contiguous())
 
     def _x_to_z(self, x, **kw):
-        m = self.mask
-        t, s = self._couple(m * x)
-        return {"z": m * x + (1 - m) * ((x + t) * torch.exp(s)),
-                "log-jac": ((1 - m) * s).flatten(1).sum(1, keepdim=True)}
+        return self._x_to_z_fused(x, self.mask * x)
 
     def _z_to_x(self, z, **kw):
         m = self.mask
@@ -227,10 +251,7 @@ class ChannelwiseAffineCouplingBijection(AffineCouplingBijection):
         return self._do_combine(a, b)
 
     def _x_to_z(self, x, **kw):
-        keep, moved = self._split(x)
-        t, s = self._couple(keep)
-        return {"z": self._combine(keep, (moved + t) * torch.exp(s)),
-                "log-jac": s.flatten(1).sum(1, keepdim=True)}
+        return self._x_to_z_fused(x, self._split(x)[0])
 
     def _z_to_x(self, z, **kw):
         keep, moved = self._split(z)

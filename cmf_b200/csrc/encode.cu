@@ -1,0 +1,192 @@
+// Encode-pass and loss-epilogue kernels: the elementwise / per-sample-reduction work
+// around the head that the reference issues as strings of small ATen ops.
+//
+//   preproc_logit        x -> logit(mult * (x + noise) + add) with its log-Jacobian per sample:
+//                        DequantizationDensity (wrapper.py:27-30) + scalar-mult + scalar-add + logit
+//                        (math.py:41-53,70-105; schemas.py:30-50), four modules, ~12 launches -> 1
+//   coupling_x_to_z      affine coupling in the ENCODE direction, z_m = (x_m + t) e^{s}, log-jac = sum s,
+//                        with the passthrough half copied through (acl.py:43-46,101-111): split, exp,
+//                        add, mul, combine / index_put, masked sum -> 1 (and 1 for the adjoint)
+//   sumsq_diff           out[b] = sum_i (a[b,i] - c[b,i])^2 (c may be null): the reconstruction error
+//                        (non_square.py:111-114) and the Gaussian log-prob's quadratic form
+//                        (gaussian.py:9-22), + adjoint
+//
+// All HBM-bound, primal-sized (B x D, no tangent factor): one CTA per sample, 128-bit accesses are not
+// worth their alignment constraints at these sizes (D <= 3072).  Algorithmic bytes: 12 D per sample
+// (preproc: read x, noise, write y), 16 D (coupling forward), 8 D (sumsq).
+#include "common.cuh"
+
+namespace cmf {
+namespace {
+
+constexpr int kEncThreads = 256;
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+    v = warp_sum(v);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float t = (threadIdx.x < kEncThreads / 32) ? red[threadIdx.x] : 0.f;
+    if (warp == 0) {
+        t = warp_sum(t);
+        if (lane == 0) red[0] = t;
+    }
+    __syncthreads();
+    const float out = red[0];
+    __syncthreads();
+    return out;
+}
+
+__global__ void __launch_bounds__(kEncThreads)
+preproc_logit_kernel(int n, float* __restrict__ x, const float* __restrict__ noise, float mult, float add, float lj0,
+                     float* __restrict__ y, float* __restrict__ logjac) {
+    __shared__ float red[kEncThreads / 32];
+    const size_t base = (size_t)blockIdx.x * n;
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < n; i += kEncThreads) {
+        float v = x[base + i];
+        if (noise) {                       // the reference adds the noise IN PLACE to the caller's batch
+            v += noise[base + i];
+            x[base + i] = v;
+        }
+        const float u = mult * v + add;
+        y[base + i] = logf(u) - logf(1.f - u);                       // math.py:47
+        const float uc = fminf(fmaxf(u, 1e-7f), 1.f - 1e-7f);       // math.py:50-52 (clamped in the log-Jacobian only)
+        acc += -logf(uc) - logf(1.f - uc);
+    }
+    const float tot = block_sum(acc, red);
+    if (threadIdx.x == 0) logjac[blockIdx.x] = lj0 + tot;
+}
+
+// pos2j (D): compact index j of the modified element at flat position i, or -1 (passthrough)
+// qmap (M) or null: conditioner position q of compact element j (null: q = j)
+__global__ void __launch_bounds__(kEncThreads)
+coupling_x_to_z_fwd_kernel(int D, int Q, const float* __restrict__ x, const float* __restrict__ st,
+                           const int32_t* __restrict__ pos2j, const int32_t* __restrict__ qmap,
+                           float* __restrict__ z, float* __restrict__ logjac) {
+    __shared__ float red[kEncThreads / 32];
+    const size_t xb = (size_t)blockIdx.x * D, sb = (size_t)blockIdx.x * 2 * Q;
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < D; i += kEncThreads) {
+        const int j = __ldg(pos2j + i);
+        float v = x[xb + i];
+        if (j >= 0) {
+            const int q = qmap ? __ldg(qmap + j) : j;
+            const float s = st[sb + Q + q];
+            v = (v + st[sb + q]) * expf(s);
+            acc += s;
+        }
+        z[xb + i] = v;
+    }
+    const float tot = block_sum(acc, red);
+    if (threadIdx.x == 0) logjac[blockIdx.x] = tot;
+}
+
+// q2pos (Q): flat position i of the element that reads conditioner position q, or -1
+__global__ void __launch_bounds__(kEncThreads)
+coupling_x_to_z_bwd_kernel(int D, int Q, const float* __restrict__ z, const float* __restrict__ st,
+                           const int32_t* __restrict__ pos2j, const int32_t* __restrict__ qmap,
+                           const int32_t* __restrict__ q2pos, const float* __restrict__ g_z,
+                           const float* __restrict__ g_lj, float* __restrict__ g_x, float* __restrict__ g_st) {
+    const size_t xb = (size_t)blockIdx.x * D, sb = (size_t)blockIdx.x * 2 * Q;
+    const float glj = g_lj ? g_lj[blockIdx.x] : 0.f;
+    for (int i = threadIdx.x; i < D; i += kEncThreads) {
+        const int j = __ldg(pos2j + i);
+        float g = g_z ? g_z[xb + i] : 0.f;
+        if (j >= 0) {
+            const int q = qmap ? __ldg(qmap + j) : j;
+            g *= expf(st[sb + Q + q]);
+        }
+        g_x[xb + i] = g;
+    }
+    for (int q = threadIdx.x; q < Q; q += kEncThreads) {
+        const int i = __ldg(q2pos + q);
+        float gt = 0.f, gs = 0.f;
+        if (i >= 0) {
+            const float g = g_z ? g_z[xb + i] : 0.f;
+            gt = g * expf(st[sb + Q + q]);            // d z / d t = e^s
+            gs = g * z[xb + i] + glj;                 // d z / d s = z, d logjac / d s = 1
+        }
+        g_st[sb + q] = gt;
+        g_st[sb + Q + q] = gs;
+    }
+}
+
+__global__ void __launch_bounds__(kEncThreads)
+sumsq_diff_fwd_kernel(int n, const float* __restrict__ a, const float* __restrict__ c, float* __restrict__ out) {
+    __shared__ float red[kEncThreads / 32];
+    const size_t base = (size_t)blockIdx.x * n;
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < n; i += kEncThreads) {
+        const float d = a[base + i] - (c ? c[base + i] : 0.f);
+        acc += d * d;
+    }
+    const float tot = block_sum(acc, red);
+    if (threadIdx.x == 0) out[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kEncThreads)
+sumsq_diff_bwd_kernel(int n, const float* __restrict__ a, const float* __restrict__ c, const float* __restrict__ g,
+                      float* __restrict__ g_a) {
+    const size_t base = (size_t)blockIdx.x * n;
+    const float gg = 2.f * g[blockIdx.x];
+    for (int i = threadIdx.x; i < n; i += kEncThreads) g_a[base + i] = gg * (a[base + i] - (c ? c[base + i] : 0.f));
+}
+
+}  // namespace
+}  // namespace cmf
+
+using namespace cmf;
+
+extern "C" int cmf_preproc_logit_fwd(int B, int n, float* x, const float* noise, float mult, float add,
+                                     float* y, float* logjac, cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && n >= 0, "preproc_logit: negative size");
+    CMF_REQUIRE(mult != 0.f, "preproc_logit: scalar multiplication by zero is not a bijection");
+    if (B == 0) return 0;
+    CMF_REQUIRE(x && y && logjac, "preproc_logit: null pointer");
+    preproc_logit_kernel<<<(unsigned)B, kEncThreads, 0, (cudaStream_t)stream>>>(n, x, noise, mult, add,
+                                                                               (float)n * logf(fabsf(mult)), y, logjac);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int cmf_coupling_x_to_z_fwd(int B, int D, int Q, const float* x, const float* st, const int32_t* pos2j,
+                                       const int32_t* qmap, float* z, float* logjac, cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && D >= 0 && Q >= 0, "coupling_x_to_z: negative size");
+    if (B == 0) return 0;
+    CMF_REQUIRE(x && st && pos2j && z && logjac, "coupling_x_to_z: null pointer");
+    coupling_x_to_z_fwd_kernel<<<(unsigned)B, kEncThreads, 0, (cudaStream_t)stream>>>(D, Q, x, st, pos2j, qmap, z, logjac);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int cmf_coupling_x_to_z_bwd(int B, int D, int Q, const float* z, const float* st, const int32_t* pos2j,
+                                       const int32_t* qmap, const int32_t* q2pos, const float* g_z, const float* g_logjac,
+                                       float* g_x, float* g_st, cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && D >= 0 && Q >= 0, "coupling_x_to_z_bwd: negative size");
+    if (B == 0) return 0;
+    CMF_REQUIRE(z && st && pos2j && q2pos && g_x && g_st, "coupling_x_to_z_bwd: null pointer");
+    coupling_x_to_z_bwd_kernel<<<(unsigned)B, kEncThreads, 0, (cudaStream_t)stream>>>(D, Q, z, st, pos2j, qmap, q2pos, g_z,
+                                                                                     g_logjac, g_x, g_st);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int cmf_sumsq_diff_fwd(int B, int n, const float* a, const float* c, float* out, cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && n >= 0, "sumsq_diff: negative size");
+    if (B == 0) return 0;
+    CMF_REQUIRE(a && out, "sumsq_diff: null pointer");
+    sumsq_diff_fwd_kernel<<<(unsigned)B, kEncThreads, 0, (cudaStream_t)stream>>>(n, a, c, out);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int cmf_sumsq_diff_bwd(int B, int n, const float* a, const float* c, const float* g, float* g_a,
+                                  cmf_stream_t stream) {
+    CMF_REQUIRE(B >= 0 && n >= 0, "sumsq_diff_bwd: negative size");
+    if (B == 0) return 0;
+    CMF_REQUIRE(a && g && g_a, "sumsq_diff_bwd: null pointer");
+    sumsq_diff_bwd_kernel<<<(unsigned)B, kEncThreads, 0, (cudaStream_t)stream>>>(n, a, c, g, g_a);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}

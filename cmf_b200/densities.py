@@ -79,6 +79,10 @@ class DiagonalGaussianDensity(Density):
             self.register_buffer("_fixed_samples", self.sample(num_fixed_samples))
 
     def _elbo(self, z):
+        if getattr(self, "_standard", False):       # N(0, I): the quadratic form on the fused kernel
+            from . import ops
+            dim = z[0].numel()
+            return {"elbo": -0.5 * dim * math.log(2 * math.pi) - 0.5 * ops.sumsq_diff(z), "z": z}
         w = z.flatten(1)
         mu = self.mean.expand_as(z).flatten(1)
         var = self.stddev.expand_as(z).flatten(1) ** 2
@@ -102,7 +106,9 @@ class DiagonalGaussianDensity(Density):
 
 def standard_gaussian(shape) -> DiagonalGaussianDensity:
     """`factory.py:200-205`."""
-    return DiagonalGaussianDensity(torch.zeros(tuple(shape)), torch.ones(tuple(shape)), num_fixed_samples=64)
+    density = DiagonalGaussianDensity(torch.zeros(tuple(shape)), torch.ones(tuple(shape)), num_fixed_samples=64)
+    density._standard = True     # buffers stay (state-dict parity); their values are known: 0 and 1
+    return density
 
 
 class SplitDensity(Density):
@@ -152,7 +158,34 @@ class DequantizationDensity(WrapperDensity):
     """`wrapper.py:27-30`: uniform noise added IN PLACE to the caller's batch, like the reference."""
 
     def _elbo(self, x, **kwargs):
-        return super()._elbo(x.add_(torch.rand_like(x)), **kwargs)
+        chain = self._logit_chain()
+        if chain is None or x.requires_grad or not x.is_contiguous():
+            return super()._elbo(x.add_(torch.rand_like(x)), **kwargs)
+        # dequantise + scalar-mult + scalar-add + logit (`wrapper.py:27-30`, `math.py:41-105`,
+        # `config/schemas.py:30-50`) in one pass over the batch; the three BijectionDensity nodes keep
+        # their place in the tree (state dict, sampling, ood) and their result dicts are rebuilt here
+        from . import kernels
+        mult_node, add_node, logit_node = chain
+        mult, add = mult_node.bijection.value, add_node.bijection.value
+        y, lj = kernels.preproc_logit_fwd(x, torch.rand_like(x), mult, add)
+        inner = logit_node.prior.elbo(y, **kwargs)
+        if "elbo" not in inner:
+            return inner                                  # ood: {"likelihood", "reconstruction-error"}
+        lj_mult = x[0].numel() * math.log(abs(mult))
+        d_logit = {"elbo": inner["elbo"] + (lj - lj_mult), "prior-dict": inner}
+        d_add = {"elbo": d_logit["elbo"], "prior-dict": d_logit}
+        return {"elbo": d_add["elbo"] + lj_mult, "prior-dict": d_add}
+
+    def _logit_chain(self):
+        """the three elementwise nodes `schemas.py:30-50` puts below the dequantiser, or None"""
+        from .bijections import LogitBijection, ScalarAdditionBijection, ScalarMultiplicationBijection
+        nodes, node = [], self.density
+        for cls in (ScalarMultiplicationBijection, ScalarAdditionBijection, LogitBijection):
+            if not (isinstance(node, BijectionDensity) and isinstance(node.bijection, cls)):
+                return None
+            nodes.append(node)
+            node = node.prior
+        return nodes
 
 
 class NonSquareTailDensity(Density):

@@ -106,7 +106,7 @@ class FusedNonSquareHeadDensity(Density):
 
         if add_reconstruction:
             assert not visualization
-            reconstruction_loss = torch.sum((reconstructed_x - x).flatten(start_dim=1) ** 2, dim=-1, keepdim=True)
+            reconstruction_loss = ops.sumsq_diff(reconstructed_x, x)          # non_square.py:111-114
         else:
             reconstruction_loss = 0
 

@@ -331,3 +331,76 @@ def conv3x3_c64_wgrad(x: Tensor, g_y: Tensor, deterministic: Optional[bool] = No
                                                  int(bool(deterministic)), _stream()),
                    "cmf_conv3x3_c64_wgrad")
     return g_w
+
+
+# ------------------------------------------------------------------ encode pass / loss epilogue (N4)
+def preproc_logit_fwd(x: Tensor, noise: Optional[Tensor], mult: float, add: float) -> Tuple[Tensor, Tensor]:
+    """x (B, ...) gets ``noise`` added IN PLACE (wrapper.py:27-30); returns (logit(mult * x + add) with x's
+    shape, log-Jacobian (B,1))."""
+    lib = _lib.load()
+    if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
+        raise _lib.CmfB200Error("preproc_logit: x must be a contiguous CUDA float32 tensor (it is updated in place)")
+    B = x.shape[0]
+    n = x[0].numel() if B else 0
+    if noise is not None:
+        noise = _req(noise, "noise")
+        assert noise.shape == x.shape
+    y = torch.empty_like(x)
+    lj = torch.empty(B, 1, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_preproc_logit_fwd(B, n, _ptr(x), _ptr(noise), float(mult), float(add), _ptr(y), _ptr(lj), _stream()),
+                   "cmf_preproc_logit_fwd")
+    return y, lj
+
+
+def coupling_x_to_z_fwd(x: Tensor, st: Tensor, pos2j: Tensor, qmap: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    """x (B,D) flat, st (B,2Q), pos2j (D) int32, qmap (M) int32|None -> z (B,D), log-jac (B,1)"""
+    lib = _lib.load()
+    x, st, pos2j = _req(x, "x"), _req(st, "st"), _req(pos2j, "pos2j", torch.int32)
+    B, D = x.shape
+    Q = st.shape[1] // 2
+    assert pos2j.numel() == D
+    z = torch.empty_like(x)
+    lj = torch.empty(B, 1, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_coupling_x_to_z_fwd(B, D, Q, _ptr(x), _ptr(st), _ptr(pos2j), _ptr(qmap), _ptr(z), _ptr(lj), _stream()),
+                   "cmf_coupling_x_to_z_fwd")
+    return z, lj
+
+
+def coupling_x_to_z_bwd(z: Tensor, st: Tensor, pos2j: Tensor, qmap: Optional[Tensor], q2pos: Tensor,
+                        g_z: Optional[Tensor], g_lj: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    lib = _lib.load()
+    z, st = _req(z, "z"), _req(st, "st")
+    B, D = z.shape
+    Q = st.shape[1] // 2
+    g_z = None if g_z is None else _req(g_z, "g_z")
+    g_lj = None if g_lj is None else _req(g_lj, "g_lj")
+    g_x, g_st = torch.empty_like(z), torch.empty_like(st)
+    with torch.cuda.device(z.device):
+        _lib.check(lib.cmf_coupling_x_to_z_bwd(B, D, Q, _ptr(z), _ptr(st), _ptr(pos2j), _ptr(qmap), _ptr(q2pos), _ptr(g_z),
+                                               _ptr(g_lj), _ptr(g_x), _ptr(g_st), _stream()), "cmf_coupling_x_to_z_bwd")
+    return g_x, g_st
+
+
+def sumsq_diff_fwd(a: Tensor, c: Optional[Tensor]) -> Tensor:
+    """a, c (B,n) -> (B,1): sum_i (a - c)^2 (c None: sum a^2)"""
+    lib = _lib.load()
+    a = _req(a, "a")
+    c = None if c is None else _req(c, "c")
+    B, n = a.shape
+    out = torch.empty(B, 1, dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        _lib.check(lib.cmf_sumsq_diff_fwd(B, n, _ptr(a), _ptr(c), _ptr(out), _stream()), "cmf_sumsq_diff_fwd")
+    return out
+
+
+def sumsq_diff_bwd(a: Tensor, c: Optional[Tensor], g: Tensor) -> Tensor:
+    lib = _lib.load()
+    a, g = _req(a, "a"), _req(g, "g")
+    c = None if c is None else _req(c, "c")
+    B, n = a.shape
+    g_a = torch.empty_like(a)
+    with torch.cuda.device(a.device):
+        _lib.check(lib.cmf_sumsq_diff_bwd(B, n, _ptr(a), _ptr(c), _ptr(g), _ptr(g_a), _stream()), "cmf_sumsq_diff_bwd")
+    return g_a

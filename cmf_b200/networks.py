@@ -27,7 +27,9 @@ _TC_CONV = os.environ.get("CMF_CONV", "tc") != "cudnn"
 # K = 32 stages per FP32 drain in the data-gradient launches of the backward pass.  Forward values
 # pass through G^-1 (errors amplified by cond(G) ~ 5e3) and keep the per-stage drain; a gradient is
 # consumed as is, so 4e-7 instead of 2e-7 relative error buys 7 % of those launches.
-_BWD_DRAIN = 2
+_BWD_DRAIN = int(os.environ.get("CMF_BWD_DRAIN", "2"))
+# drain interval of the forward launches (primal and tangent push); see DESIGN.md 3a for the measurements
+_FWD_DRAIN = int(os.environ.get("CMF_FWD_DRAIN", "1"))
 
 
 class library_convs:
@@ -214,20 +216,21 @@ class _ResidualStackJoint(torch.autograd.Function):
         for k in range(K):
             w1, b1, w2, b2 = tensors[4 * k:4 * k + 4]
             ws1, ws2 = kernels.conv3x3_c64_prep(w1, False), kernels.conv3x3_c64_prep(w2, False)
-            h1 = kernels.conv3x3_c64(A0[Nt:], ws1, b1)                                   # primal, one launch ahead
+            h1 = kernels.conv3x3_c64(A0[Nt:], ws1, b1, drain=_FWD_DRAIN)                 # primal, one launch ahead
             hb = kernels.relu_mask_pack(h1)
             A1 = new()
             torch.clamp_min(h1, 0, out=A1[Nt:])
-            kernels.conv3x3_c64(A0[:Nt], ws1, None, mask_src=hb, mask_div=d, mask_first=True, out=A1[:Nt])
-            x = kernels.conv3x3_c64(A1[Nt:], ws2, b2, res=x)
+            kernels.conv3x3_c64(A0[:Nt], ws1, None, mask_src=hb, mask_div=d, mask_first=True, out=A1[:Nt], drain=_FWD_DRAIN)
+            x = kernels.conv3x3_c64(A1[Nt:], ws2, b2, res=x, drain=_FWD_DRAIN)
             xbits.append(xb); hbits.append(hb); saved += [A0, A1]
             if k + 1 < K:
                 xb = kernels.relu_mask_pack(x)
                 A0 = new()
                 torch.clamp_min(x, 0, out=A0[Nt:])
-                S, _ = kernels.conv3x3_c64(A1[:Nt], ws2, None, mask_src=xb, mask_div=d, res=S, second=True, out2=A0[:Nt])
+                S, _ = kernels.conv3x3_c64(A1[:Nt], ws2, None, mask_src=xb, mask_div=d, res=S, second=True, out2=A0[:Nt],
+                                           drain=_FWD_DRAIN)
             else:
-                S = kernels.conv3x3_c64(A1[:Nt], ws2, None, res=S)
+                S = kernels.conv3x3_c64(A1[:Nt], ws2, None, res=S, drain=_FWD_DRAIN)
         ctx.d, ctx.K, ctx.Nt = d, K, Nt
         ctx.save_for_backward(*xbits, *hbits, *tensors[0::4], *tensors[2::4], *saved)
         return x, S

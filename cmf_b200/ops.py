@@ -305,3 +305,49 @@ def conv3x3_c64(x: Tensor, weight: Tensor, bias: Optional[Tensor] = None, wsplit
 def conv3x3_c64_usable(x: Tensor, weight: Tensor) -> bool:
     return (x.dim() == 4 and tuple(weight.shape) == (64, 64, 3, 3) and x.shape[1] == 64
             and x.dtype == torch.float32 and kernels.conv3x3_c64_usable(x.shape[0], x.shape[2], x.shape[3]))
+
+
+# ------------------------------------------------------------------ encode pass / loss epilogue (N4)
+class _CouplingXToZ(Function):
+    @staticmethod
+    def forward(ctx, x, st, pos2j, qmap, q2pos):
+        z, lj = kernels.coupling_x_to_z_fwd(x, st, pos2j, qmap)
+        ctx.save_for_backward(z, st)
+        ctx.maps = (pos2j, qmap, q2pos)
+        ctx.set_materialize_grads(False)
+        return z, lj
+
+    @staticmethod
+    def backward(ctx, g_z, g_lj):
+        z, st = ctx.saved_tensors
+        pos2j, qmap, q2pos = ctx.maps
+        g_x, g_st = kernels.coupling_x_to_z_bwd(z, st, pos2j, qmap, q2pos, g_z, None if g_lj is None else g_lj.reshape(-1))
+        return g_x, g_st, None, None, None
+
+
+def coupling_x_to_z(x: Tensor, st: Tensor, pos2j: Tensor, qmap: Optional[Tensor], q2pos: Tensor) -> Tuple[Tensor, Tensor]:
+    """Affine coupling in the encode direction on the flattened layer input (`acl.py:43-46,101-111`):
+    z = x at passthrough positions, (x + t) e^s at modified ones; log-jac (B,1) = sum s.  st (B,2Q) =
+    [shift | log-scale] as the coupler emits it; the int32 maps relate flat positions, compact indices and
+    conditioner positions (see include/cmf_b200.h)."""
+    return _CouplingXToZ.apply(x, st, pos2j, qmap, q2pos)
+
+
+class _SumSqDiff(Function):
+    @staticmethod
+    def forward(ctx, a, c):
+        ctx.save_for_backward(a, c)
+        return kernels.sumsq_diff_fwd(a, c)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, c = ctx.saved_tensors
+        g_a = kernels.sumsq_diff_bwd(a, c, g.reshape(-1).contiguous())
+        return (g_a if ctx.needs_input_grad[0] else None), (-g_a if (c is not None and ctx.needs_input_grad[1]) else None)
+
+
+def sumsq_diff(a: Tensor, c: Optional[Tensor] = None) -> Tensor:
+    """(B,1): sum over everything but the batch of (a - c)^2 -- the reconstruction error of
+    `non_square.py:111-114` and the quadratic form of `gaussian.py:9-22`."""
+    a2 = a.flatten(1)
+    return _SumSqDiff.apply(a2, None if c is None else c.flatten(1))

@@ -231,6 +231,31 @@ int cmf_rqs_coupling_jvp_bwd(int B, int d, int M, int K, float tail_bound,
                              float* g_z, float* g_Vin, float* g_cw, float* g_ch, float* g_dv,
                              float* g_CW, float* g_CH, float* g_DV, cmf_stream_t stream);
 
+/* Encode pass and loss epilogue: primal-sized elementwise work around the head, one CTA
+ * per sample.
+ *   preproc_logit: DequantizationDensity + scalar-mult + scalar-add + logit (wrapper.py:27-30,
+ *     math.py:41-53,70-105; config/schemas.py:30-50) in one pass.  x (B,n) gets `noise` (B,n, may be NULL)
+ *     added IN PLACE like the reference; y = logit(mult * x + add); logjac (B) = n log|mult| + sum(-log u
+ *     - log(1 - u)) with u clamped to [1e-7, 1 - 1e-7] in the log-Jacobian only. */
+int cmf_preproc_logit_fwd(int B, int n, float* x, const float* noise, float mult, float add,
+                          float* y, float* logjac, cmf_stream_t stream);
+/*   coupling_x_to_z: affine coupling in the encode direction (acl.py:43-46,101-111), whole layer:
+ *     z[b,i] = x[b,i] for passthrough positions, (x[b,i] + t) * exp(s) for modified ones, logjac (B) = sum s.
+ *     pos2j (D) int32: compact index j of the modified element at flat position i, or -1; qmap (M) int32
+ *     or NULL: conditioner position of compact element j (NULL: q = j); st (B,2Q) = [shift | log-scale].
+ *     Adjoint: q2pos (Q) int32 = flat position read through conditioner position q, or -1; g_st is
+ *     written densely.  g_z, g_logjac may be NULL (zero). */
+int cmf_coupling_x_to_z_fwd(int B, int D, int Q, const float* x, const float* st, const int32_t* pos2j,
+                            const int32_t* qmap, float* z, float* logjac, cmf_stream_t stream);
+int cmf_coupling_x_to_z_bwd(int B, int D, int Q, const float* z, const float* st, const int32_t* pos2j,
+                            const int32_t* qmap, const int32_t* q2pos, const float* g_z, const float* g_logjac,
+                            float* g_x, float* g_st, cmf_stream_t stream);
+/*   sumsq_diff: out[b] = sum_i (a[b,i] - c[b,i])^2, c may be NULL: the reconstruction error
+ *     (non_square.py:111-114) and the quadratic form of the standard-normal log-prob (gaussian.py:9-22).
+ *     Adjoint w.r.t. a: g_a = 2 g[b] (a - c). */
+int cmf_sumsq_diff_fwd(int B, int n, const float* a, const float* c, float* out, cmf_stream_t stream);
+int cmf_sumsq_diff_bwd(int B, int n, const float* a, const float* c, const float* g, float* g_a, cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

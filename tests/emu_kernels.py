@@ -5,6 +5,8 @@ shapes and index-map semantics as include/cmf_b200.h) so the host logic -- layer
 autograd wiring, head, sharding -- can be exercised on the GPU-less build container.  They are
 installed by the ``emu`` fixture through monkeypatching and are never importable from cmf_b200.
 """
+import math
+
 import torch
 
 PENALTY = {"none": 0, "offdiag": 1, "diag": 2}
@@ -209,6 +211,58 @@ def rqs_coupling_jvp_bwd(z_m, V_m, cw, ch, dv, CW, CH, DV, tail_bound, g_x, g_V)
     return g_z, g_Vin, g_cw, g_ch, g_dv, g_CW, g_CH, g_DV
 
 
-ALL = ["rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
+def preproc_logit_fwd(x, noise, mult, add):
+    if noise is not None:
+        x.add_(noise)
+    u = mult * x + add
+    uc = u.clamp(1e-7, 1 - 1e-7)
+    n = x[0].numel()
+    lj = n * math.log(abs(mult)) + (-torch.log(uc) - torch.log(1 - uc)).flatten(1).sum(1, keepdim=True)
+    return torch.log(u) - torch.log(1 - u), lj
+
+
+def coupling_x_to_z_fwd(x, st, pos2j, qmap):
+    B, D = x.shape
+    Q = st.shape[1] // 2
+    j = pos2j.long()
+    mod = j >= 0
+    jj = j.clamp(min=0)
+    q = jj if qmap is None else qmap.long()[jj]
+    t, s = st[:, :Q][:, q], st[:, Q:][:, q]
+    z = torch.where(mod, (x + t) * torch.exp(s), x)
+    return z, torch.where(mod, s, torch.zeros_like(s)).sum(1, keepdim=True)
+
+
+def coupling_x_to_z_bwd(z, st, pos2j, qmap, q2pos, g_z, g_lj):
+    B, D = z.shape
+    Q = st.shape[1] // 2
+    j = pos2j.long()
+    mod = j >= 0
+    jj = j.clamp(min=0)
+    q = jj if qmap is None else qmap.long()[jj]
+    gz = torch.zeros_like(z) if g_z is None else g_z
+    e = torch.exp(st[:, Q:][:, q])
+    g_x = torch.where(mod, gz * e, gz)
+    i = q2pos.long()
+    used = i >= 0
+    ii = i.clamp(min=0)
+    glj = torch.zeros(B, 1, dtype=z.dtype) if g_lj is None else g_lj.view(B, 1)
+    gt = torch.where(used, gz[:, ii] * torch.exp(st[:, Q:]), torch.zeros_like(st[:, Q:]))
+    gs = torch.where(used, gz[:, ii] * z[:, ii] + glj, torch.zeros_like(st[:, Q:]))
+    return g_x, torch.cat((gt, gs), dim=1)
+
+
+def sumsq_diff_fwd(a, c):
+    d = a if c is None else a - c
+    return (d * d).sum(1, keepdim=True)
+
+
+def sumsq_diff_bwd(a, c, g):
+    d = a if c is None else a - c
+    return 2 * g.view(-1, 1) * d
+
+
+ALL = ["preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
+       "rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

@@ -120,3 +120,23 @@ def test_no_cpu_fallback():
     density = build_product(g)
     with pytest.raises(CmfB200Error):
         run_loss(g, density)
+
+
+def test_fused_preprocessing_equals_the_node_chain(emu, monkeypatch):
+    """DequantizationDensity's one-pass preprocessing (dequantise, scalar-mult, scalar-add, logit) against the
+    three BijectionDensity nodes it stands in for, on the same noise"""
+    g = load_golden("img8_gij_d8")
+    density = build_product(g).eval()
+    x = make_input(CASES["img8_gij_d8"]).floor()
+    noise = torch.rand(x.shape, generator=torch.Generator().manual_seed(0))
+    monkeypatch.setattr(torch, "rand_like", lambda t, **kw: noise.clone())
+    with torch.no_grad():
+        x1, x2 = x.clone(), x.clone()
+        fused = density.elbo(x1)
+        plain = density.module.density.elbo(x2.add_(noise))
+    assert torch.equal(x1, x + noise)
+    assert_close(fused["elbo"], plain["elbo"], 1e-6, what="elbo")
+    depth = 0
+    while "low-dim-x" not in fused:
+        fused, depth = fused["prior-dict"], depth + 1
+    assert depth >= 4          # mult, add, logit, head ... nested like the reference's result dicts
