@@ -46,9 +46,21 @@ constexpr int kTaps = 9;
 constexpr int kStages = 2 * kTaps;     // per tile: 2 channel chunks x 9 taps
 constexpr int kWRing = 4;
 constexpr int kWStageBytes = 2 * kC * kChunkC * 4;     // hi + lo tile: 16 KB
-constexpr int kMmaWarp1 = 2 + 4 * kTiles;              // second MMA issuer (tile 1)
-constexpr int kHaloWarp = 3 + 4 * kTiles;               // halo-window loader
-constexpr int kConvThreads = 32 * (4 + 4 * kTiles);    // 384
+// Row workers: kGroups warps per TMEM lane quarter and tile.  Group g of a tile stages channels
+// [16 g, 16 g + 16) of every 32-channel stage and drains / stores output channels [32 g, 32 g + 32): the
+// work per stage is unchanged, but each scheduler now holds four worker warps instead of two, which is
+// what hides the tcgen05.st / tcgen05.ld / mbarrier latencies the workers are bound by (r01: 0.8
+// eligible warps per scheduler, tensor pipe 46 % active).
+#ifndef CMF_CONV_GROUPS
+#define CMF_CONV_GROUPS 2
+#endif
+constexpr int kGroups = CMF_CONV_GROUPS;
+constexpr int kWorkerWarps = 4 * kGroups * kTiles;      // 16
+constexpr int kMmaWarp1 = 2 + kWorkerWarps;             // second MMA issuer (tile 1)
+constexpr int kHaloWarp = 3 + kWorkerWarps;              // halo-window loader
+constexpr int kConvThreads = 32 * (4 + kWorkerWarps);   // 640
+constexpr int kCg = kChunkC / kGroups;                  // channels of a stage staged by one worker
+constexpr int kOg = kC / kGroups;                       // output channels drained by one worker
 constexpr int kConvTmemCols = 512;
 constexpr int kMaxBox = 256;
 
@@ -168,7 +180,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
         for (int t = 0; t < kTiles; ++t) {
             for (int c = 0; c < 2; ++c) {
                 mbar_init(&a_full[t][c], 32);              // one cp.async arrival per producer lane
-                mbar_init(&at_full[t][c], kTileM / 32);     // one arrival per worker warp
+                mbar_init(&at_full[t][c], kGroups * kTileM / 32);     // one arrival per worker warp
             }
         }
         mbar_fence_init();
@@ -293,12 +305,15 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
         }
     } else {
         // ------------------------------------------------------------------ row workers
-        const int t = (warp - 2) >> 2;
+        const int wi = warp - 2;
+        const int t = wi / (4 * kGroups);
+        const int grp = (wi >> 2) % kGroups;           // channel group of this warp (see kGroups)
         const int rb = warp & 3;                       // TMEM lane quarter this warp may touch
         const int m = rb * 32 + lane;                  // row of the tile = output pixel p0 + m
         const uint32_t lane_addr = (uint32_t)(rb * 32) << 16;
-        const uint32_t row_addr = smem_u32(halo) + (uint32_t)((t * 2 * kHaloElems + P.hl + m) * 4);
+        const uint32_t row_addr = smem_u32(halo) + (uint32_t)((t * 2 * kHaloElems + grp * kCg * kPitch + P.hl + m) * 4);
         const long long hw = P.HW;
+        constexpr int kHalves = kOg / 32;              // 32-column accumulator slices this worker owns
         for (int it = 0; it < nit; ++it) {
             bool act; long long g0;
             tile_of(it, t, act, g0);
@@ -321,12 +336,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     okbits |= (ok ? 1u : 0u) << tp;
                 }
             }
-            float accr[kC];
+            float accr[kOg];
 #pragma unroll
-            for (int j = 0; j < kC; ++j) accr[j] = 0.f;
-            // software pipeline: the 32 shared-memory loads of stage s+1 are issued while the
+            for (int j = 0; j < kOg; ++j) accr[j] = 0.f;
+            // software pipeline: the shared-memory loads of stage s+1 are issued while the
             // tcgen05.st of stage s is in flight (its completion wait is the longest latency here)
-            float v[32];
+            float v[kCg];
             auto load_stage = [&](int s) {
                 const int chunk = s / kTaps, tap = s - chunk * kTaps;
                 const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
@@ -335,19 +350,19 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 const bool ok = (okbits >> tap) & 1u;
                 if (__all_sync(0xffffffffu, ok)) {      // interior rows: no zero-fill, no predicates
 #pragma unroll
-                    for (int c = 0; c < kChunkC; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
+                    for (int c = 0; c < kCg; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
                 } else {
 #pragma unroll
-                    for (int c = 0; c < kChunkC; ++c) v[c] = ok ? ld_shared_f32(src + (uint32_t)(c * kPitch * 4)) : 0.f;
+                    for (int c = 0; c < kCg; ++c) v[c] = ok ? ld_shared_f32(src + (uint32_t)(c * kPitch * 4)) : 0.f;
                 }
             };
             // drain the accumulator of the segment that ended with global stage e into the FP32 registers
             auto drain = [&](int e) {
                 mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
                 tc_fence_after();
-                const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + ((e / kSeg) & 1)) * kC) + lane_addr;
+                const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + ((e / kSeg) & 1)) * kC + grp * kOg) + lane_addr;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
+                for (int h = 0; h < kHalves; ++h) {
                     float u[32];
                     tmem_ld_32x32(acc + h * 32, u);
 #pragma unroll
@@ -362,9 +377,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 const int gs = gs0 + s;
                 if (s < kStages) {
                     const int b = gs & 1;
-                    float hi[32], lo[32];
+                    float hi[kCg], lo[kCg];
 #pragma unroll
-                    for (int c = 0; c < kChunkC; ++c) {
+                    for (int c = 0; c < kCg; ++c) {
                         // TF32 head: round to nearest where the result feeds the metric (kSeg == 1); the
                         // gradient launches (kSeg >= 2) truncate -- one operation less, the remainder then
                         // loses 2 of its 13 bits in the tensor core (2^-21 |x| instead of 2^-22)
@@ -373,9 +388,9 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     }
                     if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
                     tc_fence_after();
-                    const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64) + lane_addr;
-                    tmem_st_32x32(stg, hi);
-                    tmem_st_32x32(stg + 32, lo);
+                    const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64 + grp * kCg) + lane_addr;
+                    tmem_st_cols<kCg>(stg, hi);
+                    tmem_st_cols<kCg>(stg + 32, lo);
                     if (s + 1 < kStages) load_stage(s + 1);
                     tmem_st_wait();
                     tc_fence_before();
@@ -387,6 +402,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 if (s > 0 && ((gs % kSeg) == 0 || s == kStages)) drain(gs - 1);
             }
             if (valid) {
+                const int j0 = grp * kOg;                                  // first output channel of this worker
                 const long long o = (long long)im * kC * hw + p;
                 // joint batch: tangent images first (mask row im / mask_div, no bias), then the primal images
                 const bool in_tail = P.tail > 0 && im >= P.tail;
@@ -394,7 +410,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 const float* bias = (P.tail == 0 || in_tail) ? P.bias : nullptr;
                 if (!P.mask_src && !P.mask_bits && !P.res) {
 #pragma unroll
-                    for (int j = 0; j < kC; ++j) P.y[o + (long long)j * hw] = accr[j] + (bias ? __ldg(bias + j) : 0.f);
+                    for (int j = 0; j < kOg; ++j)
+                        P.y[o + (long long)(j0 + j) * hw] = accr[j] + (bias ? __ldg(bias + j0 + j) : 0.f);
                 } else {
                     const float* ms = P.mask_src ? P.mask_src + (long long)mrow * kC * hw + p : nullptr;
                     const float* rs = P.res ? P.res + o : nullptr;
@@ -402,8 +419,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     float* y2 = P.y2 ? P.y2 + o : nullptr;
                     const bool mask_first = P.mask_first != 0;
                     // every load of a batch is issued before the batch's stores so that the latencies
-                    // overlap (the compiler cannot hoist loads over possibly aliasing stores): first all 64
-                    // mask values, packed into two words, then the skip connection 32 channels at a time
+                    // overlap (the compiler cannot hoist loads over possibly aliasing stores): first the
+                    // mask values, packed into words, then the skip connection 32 channels at a time
                     uint32_t keep_bits[2] = {0xffffffffu, 0xffffffffu};
                     if (P.mask_bits) {       // one 8-byte load instead of 64 strided ones
                         const uint2 mb = __ldg(P.mask_bits + (long long)mrow * hw + p);
@@ -411,26 +428,28 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                         keep_bits[1] = mb.y;
                     } else if (kFloatMask && ms) {
 #pragma unroll
-                        for (int h = 0; h < 2; ++h) {
+                        for (int h = 0; h < kHalves; ++h) {
+                            const int hh = j0 / 32 + h;
                             float mv[32];
 #pragma unroll
-                            for (int e = 0; e < 32; ++e) mv[e] = __ldg(ms + (32 * h + e) * hw);
+                            for (int e = 0; e < 32; ++e) mv[e] = __ldg(ms + (32 * hh + e) * hw);
                             uint32_t bits = 0;
 #pragma unroll
                             for (int e = 0; e < 32; ++e) bits |= (mv[e] > 0.f ? 1u : 0u) << e;
-                            keep_bits[h] = bits;
+                            keep_bits[hh] = bits;
                         }
                     }
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
+                    for (int h = 0; h < kHalves; ++h) {
+                        const int hh = j0 / 32 + h;                     // 32-channel word of the mask / slice of the output
                         float rv[32];
 #pragma unroll
-                        for (int e = 0; e < 32; ++e) rv[e] = rs ? __ldg(rs + (32 * h + e) * hw) : 0.f;
+                        for (int e = 0; e < 32; ++e) rv[e] = rs ? __ldg(rs + (32 * hh + e) * hw) : 0.f;
 #pragma unroll
                         for (int e = 0; e < 32; ++e) {
-                            const int j = 32 * h + e;
-                            float v2 = accr[j] + (bias ? __ldg(bias + j) : 0.f);
-                            const bool keep = (keep_bits[h] >> e) & 1u;
+                            const int j = 32 * hh + e;
+                            float v2 = accr[32 * h + e] + (bias ? __ldg(bias + j) : 0.f);
+                            const bool keep = (keep_bits[hh] >> e) & 1u;
                             if (mask_first && !keep) v2 = 0.f;
                             v2 += rv[e];
                             y1[j * hw] = v2;

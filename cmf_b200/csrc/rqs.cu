@@ -124,17 +124,26 @@ __device__ __forceinline__ Jet<S> jet_input(S v, int which, S zero, S one) {
 
 constexpr int kRqsThreads = 128;
 
-// warp-cooperative bin search for the 32 elements owned by this warp: lane l holds knot l of the
-// element being searched; bin = popc(ballot(z >= knot_l)) - 1  (torchutils.py:133-138).
-__device__ __forceinline__ int warp_bin_search(const float* __restrict__ knots, long long warp_base,
-                                               long long total, int K, float z, int lane) {
+// Shared-memory staging of the knot tables (north_star: "knots staged via shared memory"): the rows of
+// a warp's 32 consecutive elements are one contiguous block of 32 (K+1) floats, so the warp copies the
+// block with consecutive lanes on consecutive floats (K+1 full-line loads instead of 32 partial-row
+// loads), then searches / picks out of the tile.
+__device__ __forceinline__ void warp_stage_rows(float* tile, const float* __restrict__ table, long long warp_base,
+                                                int n, int K, int lane) {
+    const int kp = K + 1;
+    __syncwarp();
+    const float* src = table + warp_base * kp;
+    for (int pos = lane; pos < n * kp; pos += 32) tile[pos] = __ldg(src + pos);
+    __syncwarp();
+}
+// bin = popc(ballot(z >= knot_l)) - 1 over the staged height knots (torchutils.py:133-138)
+__device__ __forceinline__ int warp_bin_search_tile(const float* tile, int n, int K, float z, int lane) {
     int bin = -1;
-    for (int i = 0; i < 32; ++i) {
-        const long long ei = warp_base + i;
-        if (ei >= total) break;                                  // warp-uniform
+    const int kp = K + 1;
+    for (int i = 0; i < n; ++i) {
         const float zi = __shfl_sync(0xffffffffu, z, i);
         float knot = 0.f;
-        if (lane <= K) knot = __ldg(knots + ei * (K + 1) + lane);
+        if (lane <= K) knot = tile[i * kp + lane];
         if (lane == K) knot = __fadd_rn(knot, 1e-6f);            // bin_locations[..., -1] += eps
         const unsigned bits = __ballot_sync(0xffffffffu, lane <= K && zi >= knot);
         if (lane == i) bin = __popc(bits) - 1;
@@ -148,22 +157,27 @@ struct RqsElem {
     float p[kNP];        // z, cw0, cw1, ch0, ch1, dv0, dv1
 };
 
-__device__ __forceinline__ RqsElem rqs_load_elem(bool valid, long long e, int K, float tb, float z, int bin,
-                                                 const float* __restrict__ cw, const float* __restrict__ ch,
-                                                 const float* __restrict__ dv) {
+// the same element record with all three tables read through the shared-memory tile (all lanes of the
+// warp must call this: it stages cooperatively)
+__device__ __forceinline__ RqsElem rqs_load_elem_staged(float* tile, bool valid, long long warp_base, int n, int K, float tb,
+                                                        float z, int lane, const float* __restrict__ cw,
+                                                        const float* __restrict__ ch, const float* __restrict__ dv) {
     RqsElem E;
+    const int kp = K + 1;
+    warp_stage_rows(tile, ch, warp_base, n, K, lane);
+    const int bin = warp_bin_search_tile(tile, n, K, z, lane);
     E.inside = valid && z >= -tb && z <= tb;
     E.bin = E.inside ? min(max(bin, 0), K - 1) : -1;
     E.p[0] = z;
-    if (E.inside) {
-        const long long o = e * (K + 1) + E.bin;
-        E.p[1] = __ldg(cw + o); E.p[2] = __ldg(cw + o + 1);
-        E.p[3] = __ldg(ch + o); E.p[4] = __ldg(ch + o + 1);
-        E.p[5] = __ldg(dv + o); E.p[6] = __ldg(dv + o + 1);
-    } else {
 #pragma unroll
-        for (int q = 1; q < kNP; ++q) E.p[q] = 0.f;
-    }
+    for (int q = 1; q < kNP; ++q) E.p[q] = 0.f;
+    const int o = lane * kp + (E.inside ? E.bin : 0);
+    if (E.inside) { E.p[3] = tile[o]; E.p[4] = tile[o + 1]; }
+    warp_stage_rows(tile, cw, warp_base, n, K, lane);
+    if (E.inside) { E.p[1] = tile[o]; E.p[2] = tile[o + 1]; }
+    warp_stage_rows(tile, dv, warp_base, n, K, lane);
+    if (E.inside) { E.p[5] = tile[o]; E.p[6] = tile[o + 1]; }
+    __syncwarp();
     return E;
 }
 
@@ -180,14 +194,17 @@ rqs_coupling_fwd_kernel(int B, int d, int M, int K, float tb,
                         const float* __restrict__ cw, const float* __restrict__ ch, const float* __restrict__ dv,
                         const float* __restrict__ CW, const float* __restrict__ CH, const float* __restrict__ DV,
                         float* __restrict__ x_m, float* __restrict__ V_out, int32_t* __restrict__ bin_out) {
+    __shared__ float tiles[kRqsThreads / 32][32 * 32];          // K + 1 <= 32 floats per row
     const long long total = (long long)B * M;
     const long long e = (long long)blockIdx.x * kRqsThreads + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const bool valid = e < total;
+    const long long e0 = e - lane;
+    if (e0 >= total) return;                                      // warp-uniform
+    const int n = (int)min((long long)32, total - e0);
     const float z = valid ? __ldg(z_m + e) : 0.f;
-    const int bin = warp_bin_search(ch, e - lane, total, K, z, lane);
+    const RqsElem E = rqs_load_elem_staged(tiles[threadIdx.x >> 5], valid, e0, n, K, tb, z, lane, cw, ch, dv);
     if (!valid) return;
-    const RqsElem E = rqs_load_elem(valid, e, K, tb, z, bin, cw, ch, dv);
     Jet<float> f;
     if (E.inside) f = rqs_eval_grad(E);
     x_m[e] = E.inside ? f.v : z;
@@ -213,6 +230,22 @@ __device__ __forceinline__ void rqs_store_row(float* row, int K, int bin, float 
     for (int l = 0; l <= K; ++l) row[l] = (l == bin) ? v0 : ((l == bin + 1) ? v1 : 0.f);
 }
 
+// The adjoint writes DENSE rows of K+1 floats per element (zero outside the two selected knots).  A
+// thread storing its own row puts 32 lanes on 32 different sectors per instruction (stride K+1 floats:
+// the 35 %-of-HBM finding of round 1).  The rows of a warp's 32 consecutive elements are ONE contiguous
+// block of 32 (K+1) floats, so each lane writes its row into a shared-memory tile and the warp copies
+// the tile out with consecutive lanes on consecutive floats (full 128-byte lines).
+// `n` = rows of this warp that exist, `dst` = global address of row 0 of the block.
+__device__ __forceinline__ void rqs_store_rows_coalesced(float* tile, float* dst, int K, int lane, int n,
+                                                         int bin, float v0, float v1) {
+    const int kp = K + 1;
+    float* mine = tile + lane * kp;
+    for (int l = 0; l < kp; ++l) mine[l] = (l == bin) ? v0 : ((l == bin + 1) ? v1 : 0.f);
+    __syncwarp();
+    for (int pos = lane; pos < n * kp; pos += 32) __stcs(dst + pos, tile[pos]);
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(kRqsThreads)
 rqs_coupling_bwd_kernel(int B, int d, int M, int K, float tb,
                         const float* __restrict__ z_m, const float* __restrict__ V_m,
@@ -222,59 +255,73 @@ rqs_coupling_bwd_kernel(int B, int d, int M, int K, float tb,
                         float* __restrict__ g_z, float* __restrict__ g_Vin,
                         float* __restrict__ g_cw, float* __restrict__ g_ch, float* __restrict__ g_dv,
                         float* __restrict__ g_CW, float* __restrict__ g_CH, float* __restrict__ g_DV) {
+    __shared__ float tiles[kRqsThreads / 32][32 * 32];          // K + 1 <= 32 floats per row
     const long long total = (long long)B * M;
     const long long e = (long long)blockIdx.x * kRqsThreads + threadIdx.x;
     const int lane = threadIdx.x & 31;
+    float* tile = tiles[threadIdx.x >> 5];
     const bool valid = e < total;
+    const long long e0 = e - lane;                                // the warp's first element
+    if (e0 >= total) return;                                      // whole warp past the end (warp-uniform)
+    const int n = (int)min((long long)32, total - e0);            // rows of this warp that exist
     const float z = valid ? __ldg(z_m + e) : 0.f;
-    const int bin = warp_bin_search(ch, e - lane, total, K, z, lane);
-    if (!valid) return;
-    const RqsElem E = rqs_load_elem(valid, e, K, tb, z, bin, cw, ch, dv);
+    const RqsElem E = rqs_load_elem_staged(tile, valid, e0, n, K, tb, z, lane, cw, ch, dv);
+    const bool inside = valid && E.inside;
     Jet<float> f;
-    if (E.inside) f = rqs_eval_grad(E);
-    const float gx = g_x ? __ldg(g_x + e) : 0.f;
+    if (inside) f = rqs_eval_grad(E);
+    const float gx = (valid && g_x) ? __ldg(g_x + e) : 0.f;
     float r[kNP];
 #pragma unroll
     for (int q = 0; q < kNP; ++q) r[q] = 0.f;
-    const int b = (int)(e / M), j = (int)(e - (long long)b * M);
+    const int b = valid ? (int)(e / M) : 0, j = valid ? (int)(e - (long long)b * M) : 0;
+    // fast path: the warp's rows lie in ONE sample, so for every tangent k they are one contiguous block
+    const int b0 = (int)(e0 / M);
+    const bool one_sample = (e0 + n - 1) / M == b0;
+    const int j0 = (int)(e0 - (long long)b0 * M);
+    const int sbin = inside ? E.bin : -2;                         // -2: no knot selected, an all-zero row
     for (int k = 0; k < d; ++k) {
         const long long ek = ((long long)b * d + k) * M + j;
-        const float gk = __ldg(g_V + ek);
+        const float gk = valid ? __ldg(g_V + ek) : 0.f;
         const long long row = ek * (K + 1);
-        if (E.inside) {
+        float a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (inside) {
             const long long o = row + E.bin;
             r[0] = fmaf(gk, __ldg(V_m + ek), r[0]);
             r[1] = fmaf(gk, __ldg(CW + o), r[1]); r[2] = fmaf(gk, __ldg(CW + o + 1), r[2]);
             r[3] = fmaf(gk, __ldg(CH + o), r[3]); r[4] = fmaf(gk, __ldg(CH + o + 1), r[4]);
             r[5] = fmaf(gk, __ldg(DV + o), r[5]); r[6] = fmaf(gk, __ldg(DV + o + 1), r[6]);
-            g_Vin[ek] = gk * f.g[0];
-            rqs_store_row(g_CW + row, K, E.bin, gk * f.g[1], gk * f.g[2]);
-            rqs_store_row(g_CH + row, K, E.bin, gk * f.g[3], gk * f.g[4]);
-            rqs_store_row(g_DV + row, K, E.bin, gk * f.g[5], gk * f.g[6]);
-        } else {
-            g_Vin[ek] = gk;
-            rqs_store_row(g_CW + row, K, -2, 0.f, 0.f);
-            rqs_store_row(g_CH + row, K, -2, 0.f, 0.f);
-            rqs_store_row(g_DV + row, K, -2, 0.f, 0.f);
+#pragma unroll
+            for (int q = 0; q < 6; ++q) a[q] = gk * f.g[q + 1];
+        }
+        if (valid) g_Vin[ek] = inside ? gk * f.g[0] : gk;
+        if (one_sample) {
+            const long long blk = (((long long)b0 * d + k) * M + j0) * (K + 1);
+            rqs_store_rows_coalesced(tile, g_CW + blk, K, lane, n, sbin, a[0], a[1]);
+            rqs_store_rows_coalesced(tile, g_CH + blk, K, lane, n, sbin, a[2], a[3]);
+            rqs_store_rows_coalesced(tile, g_DV + blk, K, lane, n, sbin, a[4], a[5]);
+        } else if (valid) {                                       // a warp straddling two samples (M < 32 or a sample end)
+            rqs_store_row(g_CW + row, K, sbin, a[0], a[1]);
+            rqs_store_row(g_CH + row, K, sbin, a[2], a[3]);
+            rqs_store_row(g_DV + row, K, sbin, a[4], a[5]);
         }
     }
-    const long long row = e * (K + 1);
-    if (E.inside) {
+    float a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (inside) {
         // Hessian-vector product H r: the gradient jet evaluated over duals in direction r
         Jet<Dual> in[kNP];
 #pragma unroll
         for (int q = 0; q < kNP; ++q) in[q] = jet_input<Dual>(Dual{E.p[q], r[q]}, q, Dual{0.f, 0.f}, Dual{1.f, 0.f});
         const Jet<Dual> h = rqs_inverse_bin(in[0], in[1], in[2], in[3], in[4], in[5], in[6]);
         g_z[e] = fmaf(gx, f.g[0], h.g[0].e);
-        rqs_store_row(g_cw + row, K, E.bin, fmaf(gx, f.g[1], h.g[1].e), fmaf(gx, f.g[2], h.g[2].e));
-        rqs_store_row(g_ch + row, K, E.bin, fmaf(gx, f.g[3], h.g[3].e), fmaf(gx, f.g[4], h.g[4].e));
-        rqs_store_row(g_dv + row, K, E.bin, fmaf(gx, f.g[5], h.g[5].e), fmaf(gx, f.g[6], h.g[6].e));
-    } else {
+#pragma unroll
+        for (int q = 0; q < 6; ++q) a[q] = fmaf(gx, f.g[q + 1], h.g[q + 1].e);
+    } else if (valid) {
         g_z[e] = gx;
-        rqs_store_row(g_cw + row, K, -2, 0.f, 0.f);
-        rqs_store_row(g_ch + row, K, -2, 0.f, 0.f);
-        rqs_store_row(g_dv + row, K, -2, 0.f, 0.f);
     }
+    const long long blk = e0 * (K + 1);                           // primal rows: always one contiguous block
+    rqs_store_rows_coalesced(tile, g_cw + blk, K, lane, n, sbin, a[0], a[1]);
+    rqs_store_rows_coalesced(tile, g_ch + blk, K, lane, n, sbin, a[2], a[3]);
+    rqs_store_rows_coalesced(tile, g_dv + blk, K, lane, n, sbin, a[4], a[5]);
 }
 
 }  // namespace cmf

@@ -36,7 +36,9 @@ def test_preproc_logit(B, shape, lam):
     uc = u.clamp(1e-7, 1 - 1e-7)
     _close(y, torch.log(u) - torch.log(1 - u), rtol=1e-5, what="logit")
     ref_lj = u[0].numel() * math.log(abs(mult)) + (-torch.log(uc) - torch.log(1 - uc)).flatten(1).sum(1, keepdim=True)
-    _close(lj, ref_lj, rtol=1e-6, what="log-jac")
+    # the log-Jacobian is n log|mult| (~ -4.3e3 for 28x28) plus a sum of n terms of the opposite sign: the
+    # result is small, its fp32 rounding is that of the two large parts
+    _close(lj, ref_lj, rtol=0.0, atol=2e-7 * u[0].numel() * abs(math.log(abs(mult))), what="log-jac")
     y2, lj2 = K.preproc_logit_fwd(x, None, mult, add)                    # no noise: x untouched
     assert torch.equal(y2, y) and torch.equal(lj2, lj)
 
