@@ -35,8 +35,15 @@ def _headers():
     return glob.glob(os.path.join(CSRC, "*.cuh")) + [HEADER, os.path.abspath(__file__)]
 
 
+def _flags_now() -> str:
+    return " ".join(NVCC_FLAGS + os.environ.get("CMF_NVCC_EXTRA", "").split())
+
+
 def needs_build() -> bool:
     if not os.path.exists(LIB):
+        return True
+    tag = os.path.join(OBJ_DIR, ".flags")
+    if os.path.exists(tag) and open(tag).read() != _flags_now():      # built with other -D switches
         return True
     t = os.path.getmtime(LIB)
     return any(os.path.getmtime(p) > t for p in sources() + _headers())

@@ -38,6 +38,37 @@ using namespace tc;
 
 namespace {
 
+// timing-only ablations (WRONG results): 1 = no tcgen05.ld in the drain, 2 = no tcgen05.st staging,
+// 4 = no shared-memory loads / split, 8 = no MMAs (commit only), 16 = no epilogue stores
+#ifndef CMF_CONV_ABLATE
+#define CMF_CONV_ABLATE 0
+#endif
+// experiment switches: pure-spin (test_wait) instead of suspending try_wait on the critical hops
+#ifndef CMF_CONV_SPIN
+#define CMF_CONV_SPIN 0
+#endif
+// Experiment switch (measured, rejected): a converged warp waits on an mbarrier through ONE lane and is
+// released by __syncwarp, to cut the number of mbarrier transactions (16 worker warps x 32 lanes poll
+// two `done` phases per stage).  It is SLOWER (1.149 vs 1.056 ms on the 28x28 tangent launch): the
+// polls are not what the synchronisation skeleton costs (profiles/r02_summary.md).
+#ifndef CMF_CONV_WARPWAIT
+#define CMF_CONV_WARPWAIT 0
+#endif
+__device__ __forceinline__ void wait_warp(uint64_t* bar, uint32_t parity) {
+    if (CMF_CONV_WARPWAIT) {
+        if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity);
+        __syncwarp();
+    } else {
+        mbar_wait(bar, parity);
+    }
+}
+__device__ __forceinline__ void wait_issuer(uint64_t* bar, uint32_t parity) {
+    if (CMF_CONV_SPIN & 1) mbar_spin(bar, parity); else wait_warp(bar, parity);
+}
+__device__ __forceinline__ void wait_worker(uint64_t* bar, uint32_t parity) {
+    if (CMF_CONV_SPIN & 2) mbar_spin(bar, parity); else wait_warp(bar, parity);
+}
+
 constexpr int kC = 64;                 // channels (in = out)
 constexpr int kTileM = 128;            // output pixels per tile (TMEM lanes)
 constexpr int kTiles = 2;              // tiles per CTA sharing one weight stream
@@ -205,9 +236,13 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                     if (gs >= kWRing) mbar_wait(&done[r], ((gs / kWRing) - 1) & 1);      // stage gs - 4 has completed
                     const int chunk = s / kTaps, tap = s % kTaps;
                     uint8_t* dst = wring + (size_t)r * kWStageBytes;
-                    mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
-                    tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
-                    tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
+                    if (CMF_CONV_ABLATE & 32) {
+                        mbar_arrive(&w_full[r]);
+                    } else {
+                        mbar_arrive_expect_tx(&w_full[r], kWStageBytes);
+                        tma_load_2d(dst, &tmw, &w_full[r], chunk * kChunkC, tap * kC);                       // hi
+                        tma_load_2d(dst + kWStageBytes / 2, &tmw, &w_full[r], chunk * kChunkC, (kTaps + tap) * kC);   // lo
+                    }
                     // halo buffers are recycled as soon as every worker is past their last read:
                     // chunk 1 of this pair once stage 0 of this pair has completed (s = 4 waited for it),
                     // chunk 0 of the next pair once stage 9 has completed (s = 13 waited for it).  The
@@ -238,7 +273,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             for (int h = 0; h < 2; ++h) {
                 const int col = 4 * (lane + 32 * h);
                 const long long sp = ws + col;
-                if (col < P.win && sp >= 0 && sp < P.total_px) {
+                if (!(CMF_CONV_ABLATE & 64) && col < P.win && sp >= 0 && sp < P.total_px) {
                     const long long im = sp / hw;
                     const float* src = P.x + ((im * kC + c * kChunkC) * hw + (sp - im * hw));
                     const uint32_t dst = dst_buf + (uint32_t)(col * 4);
@@ -274,15 +309,15 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             for (int s = 0; s < kStages; ++s, ++gs) {
                 const int r = gs % kWRing;
                 const int b = gs & 1;
-                mbar_wait(&w_full[r], (gs / kWRing) & 1);
-                if (act) mbar_wait(&at_full[t][b], (gs >> 1) & 1);
+                wait_issuer(&w_full[r], (gs / kWRing) & 1);
+                if (act) wait_issuer(&at_full[t][b], (gs >> 1) & 1);
                 // accumulator (segment gs / kSeg, parity) was drained (two segments ago) by every worker warp BEFORE it arrived on
                 // at_full for this stage (program order + tcgen05.wait::ld), so no extra barrier is needed
                 tc_fence_after();
                 const uint32_t acc = acc0 + (uint32_t)(((gs / kSeg) & 1) * kC);
                 const uint32_t fresh = (gs % kSeg) == 0 ? 0u : 1u;      // 0: first stage of a segment overwrites
                 if (elect_one()) {
-                    if (act) {
+                    if (act && !(CMF_CONV_ABLATE & 8)) {
                         const uint64_t dbh = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes));
                         const uint64_t dbl = umma_desc_sw128(wring_addr + (uint32_t)(r * kWStageBytes + kWStageBytes / 2));
                         const uint32_t a_hi = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64);
@@ -298,7 +333,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
 #pragma unroll
                         for (int k = 0; k < kChunkC / 8; ++k) umma_tf32_ts(acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
                     }
-                    umma_commit(&done[r]);      // frees the weight slot and this tile's staging buffer; ends the segment
+                    if (CMF_CONV_ABLATE & 256) mbar_arrive(&done[r]);
+                    else umma_commit(&done[r]);      // frees the weight slot and this tile's staging buffer; ends the segment
                 }
                 __syncwarp();
             }
@@ -345,10 +381,13 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             auto load_stage = [&](int s) {
                 const int chunk = s / kTaps, tap = s - chunk * kTaps;
                 const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
-                if (tap == 0) mbar_wait(&a_full[t][chunk], it & 1);
+                if (tap == 0) wait_worker(&a_full[t][chunk], it & 1);
                 const uint32_t src = row_addr + (uint32_t)((chunk * kHaloElems + dy * P.W + dx) * 4);
                 const bool ok = (okbits >> tap) & 1u;
-                if (__all_sync(0xffffffffu, ok)) {      // interior rows: no zero-fill, no predicates
+                if (CMF_CONV_ABLATE & 4) {
+#pragma unroll
+                    for (int c = 0; c < kCg; ++c) v[c] = (float)(c + tap);
+                } else if (__all_sync(0xffffffffu, ok)) {      // interior rows: no zero-fill, no predicates
 #pragma unroll
                     for (int c = 0; c < kCg; ++c) v[c] = ld_shared_f32(src + (uint32_t)(c * kPitch * 4));
                 } else {
@@ -358,13 +397,18 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
             };
             // drain the accumulator of the segment that ended with global stage e into the FP32 registers
             auto drain = [&](int e) {
-                mbar_wait(&done[e % kWRing], (e / kWRing) & 1);
+                wait_worker(&done[e % kWRing], (e / kWRing) & 1);
                 tc_fence_after();
                 const uint32_t acc = tmem_base + kAccCol + (uint32_t)((t * 2 + ((e / kSeg) & 1)) * kC + grp * kOg) + lane_addr;
 #pragma unroll
                 for (int h = 0; h < kHalves; ++h) {
                     float u[32];
-                    tmem_ld_32x32(acc + h * 32, u);
+                    if (CMF_CONV_ABLATE & 1) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) u[j] = accr[h * 32 + j] * 0.5f;
+                    } else {
+                        tmem_ld_32x32(acc + h * 32, u);
+                    }
 #pragma unroll
                     for (int j = 0; j < 32; j += 2) fadd2(accr[h * 32 + j], accr[h * 32 + j + 1], u[j], u[j + 1]);
                 }
@@ -386,11 +430,18 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                         hi[c] = __uint_as_float((__float_as_uint(v[c]) + (kSeg == 1 ? 0x1000u : 0u)) & 0xFFFFE000u);
                         lo[c] = v[c] - hi[c];                                                       // exact signed remainder
                     }
-                    if (gs >= 2) mbar_wait(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
+                    if (gs >= 2) wait_worker(&done[(gs - 2) % kWRing], ((gs - 2) / kWRing) & 1);     // staging buffer b is free
                     tc_fence_after();
                     const uint32_t stg = tmem_base + kStgCol + (uint32_t)((t * 2 + b) * 64 + grp * kCg) + lane_addr;
-                    tmem_st_cols<kCg>(stg, hi);
-                    tmem_st_cols<kCg>(stg + 32, lo);
+                    if (!(CMF_CONV_ABLATE & 2)) {
+                        tmem_st_cols<kCg>(stg, hi);
+                        tmem_st_cols<kCg>(stg + 32, lo);
+                    } else {
+                        float keep = 0.f;
+#pragma unroll
+                        for (int c = 0; c < kCg; ++c) keep += hi[c] + lo[c];
+                        if (keep == 123.456f) accr[0] += keep;      // keeps the split alive
+                    }
                     if (s + 1 < kStages) load_stage(s + 1);
                     tmem_st_wait();
                     tc_fence_before();
@@ -399,9 +450,14 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap tmw, ConvParams P) {
                 }
                 // drain one stage late, so the tensor pipe already works on the next stage in the other
                 // accumulator; the pair's last segment right after its own stage
-                if (s > 0 && ((gs % kSeg) == 0 || s == kStages)) drain(gs - 1);
+                if (!(CMF_CONV_ABLATE & 128) && s > 0 && ((gs % kSeg) == 0 || s == kStages)) drain(gs - 1);
             }
-            if (valid) {
+            if ((CMF_CONV_ABLATE & 16) && valid) {
+                float keep = 0.f;
+#pragma unroll
+                for (int j = 0; j < kOg; ++j) keep += accr[j];
+                if (keep == 123.456f) P.y[0] = keep;
+            } else if (valid) {
                 const int j0 = grp * kOg;                                  // first output channel of this worker
                 const long long o = (long long)im * kC * hw + p;
                 // joint batch: tangent images first (mask row im / mask_div, no bias), then the primal images

@@ -32,6 +32,23 @@ _BWD_DRAIN = int(os.environ.get("CMF_BWD_DRAIN", "2"))
 _FWD_DRAIN = int(os.environ.get("CMF_FWD_DRAIN", "1"))
 
 
+class recompute_activations:
+    """Activation recomputation for the residual-stack node: inside this context (or with
+    ``CMF_RECOMPUTE=1`` in the environment) ``_ResidualStackJoint`` keeps only the stack's INPUT (primal
+    and tangents) for the backward pass and re-runs its forward launches there, instead of keeping two
+    (B d + B) x 64 x H x W buffers per residual block (51 GiB at the MNIST-shape batch of 50; the
+    CIFAR-shape d = 512 sweep fits B = 6 without this).  Costs one extra forward of the stack in the
+    backward pass; the gradients are bit-identical (same launches on the same data)."""
+    depth = 1 if os.environ.get("CMF_RECOMPUTE", "0") == "1" else 0
+
+    def __enter__(self):
+        recompute_activations.depth += 1
+
+    def __exit__(self, *exc):
+        recompute_activations.depth -= 1
+        return False
+
+
 class library_convs:
     """Inside this context every conditioner convolution is the library call ``F.conv2d`` (which
     autograd can differentiate twice).  Used for the primal run whose VJP is itself differentiated
@@ -201,7 +218,8 @@ class _ResidualStackJoint(torch.autograd.Function):
     `jvp_layers.py:38-46`, is piecewise constant in them)."""
 
     @staticmethod
-    def forward(ctx, h, V, d, *tensors):
+    def _run(h, V, d, tensors):
+        """the forward launches; returns (x_out, S_out, xbits, hbits, [A0_0, A1_0, A0_1, ...])"""
         from . import kernels
         K = len(tensors) // 4
         B, Nt = h.shape[0], V.shape[0]
@@ -231,8 +249,18 @@ class _ResidualStackJoint(torch.autograd.Function):
                                            drain=_FWD_DRAIN)
             else:
                 S = kernels.conv3x3_c64(A1[:Nt], ws2, None, res=S, drain=_FWD_DRAIN)
-        ctx.d, ctx.K, ctx.Nt = d, K, Nt
-        ctx.save_for_backward(*xbits, *hbits, *tensors[0::4], *tensors[2::4], *saved)
+        return x, S, xbits, hbits, saved
+
+    @staticmethod
+    def forward(ctx, h, V, d, *tensors):
+        K = len(tensors) // 4
+        x, S, xbits, hbits, saved = _ResidualStackJoint._run(h, V, d, tensors)
+        ctx.d, ctx.K, ctx.Nt = d, K, V.shape[0]
+        ctx.recompute = recompute_activations.depth > 0
+        if ctx.recompute:
+            ctx.save_for_backward(h, V, *tensors)
+        else:
+            ctx.save_for_backward(*xbits, *hbits, *tensors[0::4], *tensors[2::4], *saved)
         return x, S
 
     @staticmethod
@@ -240,7 +268,12 @@ class _ResidualStackJoint(torch.autograd.Function):
         from . import kernels
         K, d, Nt = ctx.K, ctx.d, ctx.Nt
         t = ctx.saved_tensors
-        xbits, hbits, w1s, w2s, saved = t[:K], t[K:2 * K], t[2 * K:3 * K], t[3 * K:4 * K], t[4 * K:]
+        if ctx.recompute:
+            tensors = t[2:]
+            _, _, xbits, hbits, saved = _ResidualStackJoint._run(t[0], t[1], d, tensors)
+            w1s, w2s = tensors[0::4], tensors[2::4]
+        else:
+            xbits, hbits, w1s, w2s, saved = t[:K], t[K:2 * K], t[2 * K:3 * K], t[3 * K:4 * K], t[4 * K:]
         g = torch.empty_like(saved[0])
         for part, src in ((g[:Nt], g_S), (g[Nt:], g_h)):
             if src is None:
