@@ -41,6 +41,10 @@ SIGNATURES = {
     "cmf_coupling_x_to_z_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cmf_sumsq_diff_fwd": (_i, [_i, _i, _vp, _vp, _vp, _vp]),
     "cmf_sumsq_diff_bwd": (_i, [_i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_flat_stack_usable": (_i, [_i, _i, _i, _i, _i, _i]),
+    "cmf_flat_stack_fwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_flat_stack_bwd_partials": (_i, [_i]),
+    "cmf_flat_stack_bwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cmf_conv3x3_c64_usable": (_i, [_i, _i, _i]),
     "cmf_conv3x3_c64_prep": (_i, [_vp, _i, _vp, _vp]),
     "cmf_conv3x3_c64_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp]),

@@ -9,6 +9,7 @@ There is no CPU fallback: the ops raise if the CUDA library is missing or a tens
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import numpy as np
@@ -21,6 +22,9 @@ from .networks import library_convs
 from .program import LayerProgram
 
 Tensor = torch.Tensor
+
+# CMF_FLAT_STACK=0 keeps the small flat configs on the per-layer program (A/B measurements)
+_FLAT_STACK = os.environ.get("CMF_FLAT_STACK", "1") != "0"
 
 
 class FusedNonSquareHeadDensity(Density):
@@ -145,6 +149,11 @@ class FusedNonSquareHeadDensity(Density):
     def _get_full_jac_transpose_jac(self, latent: Tensor, create_graph: bool = True):
         """`non_square.py:298-311`: (G (B,d,d), reconstruction).  One program run with V0 = I."""
         B, d = latent.shape
+        plan = self.program.flat_plan
+        if plan is not None and _FLAT_STACK:
+            # small flat flow: tail pad, all coupling layers with their MLP conditioners and J^T J in one launch
+            gram, x = ops.flat_stack_gram(latent, plan.params(), plan.desc)
+            return gram, x.view(B, *self.x_shape)
         eye = torch.eye(d, dtype=latent.dtype, device=latent.device).expand(B, d, d).contiguous()
         blocks, _ = self.program.run(latent, eye)
         gram = ops.gram([Vb for _, _, Vb in blocks])

@@ -404,3 +404,46 @@ def sumsq_diff_bwd(a: Tensor, c: Optional[Tensor], g: Tensor) -> Tensor:
     with torch.cuda.device(a.device):
         _lib.check(lib.cmf_sumsq_diff_bwd(B, n, _ptr(a), _ptr(c), _ptr(g), _ptr(g_a), _stream()), "cmf_sumsq_diff_bwd")
     return g_a
+
+
+# ------------------------------------------------------------------ whole-stack kernel, small flat configs (N1-ii)
+def flat_stack_usable(D: int, d: int, L: int, nh: int, max_width: int, P: int) -> bool:
+    return bool(_lib.load().cmf_flat_stack_usable(int(D), int(d), int(L), int(nh), int(max_width), int(P)))
+
+
+def _desc_ptr(desc):
+    import numpy as np
+    assert isinstance(desc, np.ndarray) and desc.dtype == np.int32 and desc.flags["C_CONTIGUOUS"]
+    return desc.ctypes.data, int(desc.size)
+
+
+def flat_stack_fwd(desc, z: Tensor, params: Tensor) -> Tuple[Tensor, Tensor]:
+    """desc: host int32 descriptor (see include/cmf_b200.h), z (B,d), params (P,) -> G (B,d,d), x (B,D)"""
+    lib = _lib.load()
+    z, params = _req(z, "z"), _req(params, "params")
+    B, d = z.shape
+    D = int(desc[0])
+    G = torch.empty(B, d, d, dtype=torch.float32, device=z.device)
+    x = torch.empty(B, D, dtype=torch.float32, device=z.device)
+    ptr, n = _desc_ptr(desc)
+    with torch.cuda.device(z.device):
+        _lib.check(lib.cmf_flat_stack_fwd(ptr, n, B, _ptr(z), _ptr(params), _ptr(G), _ptr(x), _stream()), "cmf_flat_stack_fwd")
+    return G, x
+
+
+def flat_stack_bwd(desc, z: Tensor, params: Tensor, g_G: Optional[Tensor], g_x: Optional[Tensor]) -> Tuple[Tensor, Tensor]:
+    """-> g_z (B,d), g_params (P,) (the per-CTA partials summed in a fixed order)"""
+    lib = _lib.load()
+    z, params = _req(z, "z"), _req(params, "params")
+    g_G = None if g_G is None else _req(g_G, "g_G")
+    g_x = None if g_x is None else _req(g_x, "g_x")
+    B, d = z.shape
+    P = params.numel()
+    g_z = torch.empty_like(z)
+    nparts = lib.cmf_flat_stack_bwd_partials(B)
+    parts = torch.empty(max(nparts, 1), P, dtype=torch.float32, device=z.device)
+    ptr, n = _desc_ptr(desc)
+    with torch.cuda.device(z.device):
+        _lib.check(lib.cmf_flat_stack_bwd(ptr, n, B, _ptr(z), _ptr(params), _ptr(g_G), _ptr(g_x), _ptr(g_z), _ptr(parts),
+                                          _stream()), "cmf_flat_stack_bwd")
+    return g_z, (parts.sum(0) if nparts else torch.zeros_like(params))

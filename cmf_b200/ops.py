@@ -351,3 +351,28 @@ def sumsq_diff(a: Tensor, c: Optional[Tensor] = None) -> Tensor:
     `non_square.py:111-114` and the quadratic form of `gaussian.py:9-22`."""
     a2 = a.flatten(1)
     return _SumSqDiff.apply(a2, None if c is None else c.flatten(1))
+
+
+# ------------------------------------------------------------------ whole-stack kernel, small flat configs (N1-ii)
+class _FlatStackGram(Function):
+    @staticmethod
+    def forward(ctx, z, params, desc):
+        G, x = kernels.flat_stack_fwd(desc, z, params)
+        ctx.save_for_backward(z, params)
+        ctx.desc = desc
+        ctx.set_materialize_grads(False)
+        return G, x
+
+    @staticmethod
+    def backward(ctx, g_G, g_x):
+        z, params = ctx.saved_tensors
+        g_z, g_params = kernels.flat_stack_bwd(ctx.desc, z, params, None if g_G is None else g_G.contiguous(),
+                                               None if g_x is None else g_x.contiguous())
+        return g_z, g_params, None
+
+
+def flat_stack_gram(z: Tensor, params: Tensor, desc) -> Tuple[Tensor, Tensor]:
+    """(G (B,d,d), x (B,D)) of a small flat flow in one launch: tail pad, every coupling layer with its
+    tanh-MLP conditioner (primal + d tangents) and J^T J (`non_square.py:298-311,397-410`,
+    `acl.py:125-146`, `networks.py:206-224`).  ``desc`` from :class:`cmf_b200.program.FlatStackPlan`."""
+    return _FlatStackGram.apply(z, params, desc)

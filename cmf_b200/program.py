@@ -86,6 +86,57 @@ class RqsStep:
     M: int = 0
 
 
+class FlatStackPlan:
+    """Descriptor of a small flat flow for the whole-stack kernel (``cmf_flat_stack_fwd/bwd``): built when
+    every node between head and tail is an identity view or a channelwise affine coupling whose
+    conditioner is one shared tanh MLP, and the sizes fit the kernel (the 2-D configs of
+    `config/two_d.py`: D <= 8, d <= 8, widths <= 16).  ``params()`` packs the model's parameters into
+    the flat buffer the kernel reads (a differentiable ``torch.cat``: autograd routes the kernel's
+    packed gradient back to every parameter)."""
+
+    def __init__(self, nodes, tail):
+        from .bijections import ChannelwiseAffineCouplingBijection, ViewBijection
+        from .networks import ChunkedSharedCoupler, TangentMLP
+        from . import kernels
+        self.ok = False
+        D, d = tail.flattened_dims, tail.latent_dimension
+        layers, tensors, off, nh, widest = [], [], 0, None, 0
+        for node in reversed(nodes):                           # z -> x order
+            if isinstance(node, ViewBijection):
+                if int(np.prod(node.x_shape)) != D or len(node.z_shape) != 1:
+                    return
+                continue
+            if not isinstance(node, ChannelwiseAffineCouplingBijection) or tuple(node.x_shape) != (D,):
+                return
+            net = getattr(node.coupler, "shift_log_scale_net", None)
+            if not isinstance(node.coupler, ChunkedSharedCoupler) or not isinstance(net, TangentMLP) or net.activation != "tanh":
+                return
+            keep, mod, _, dense = node.partition()
+            linears = [m for m in net if isinstance(m, torch.nn.Linear)]
+            if dense or (nh is not None and len(linears) - 1 != nh):
+                return
+            nh = len(linears) - 1
+            widths = [linears[0].in_features] + [m.out_features for m in linears]
+            w_off, b_off = [], []
+            for m in linears:
+                w_off.append(off); off += m.weight.numel(); tensors.append(m.weight)
+                b_off.append(off); off += m.bias.numel(); tensors.append(m.bias)
+            widest = max(widest, *widths)
+            layers.append((keep.tolist(), mod.tolist(), widths, w_off, b_off))
+        if not layers or not kernels.flat_stack_usable(D, d, len(layers), nh, widest, off):
+            return
+        perm = tail.permutation.detach().cpu().numpy().astype(np.int64)
+        desc = [D, d, len(layers), nh, off] + [int(p) for p in perm[:d]]
+        for keep, mod, widths, w_off, b_off in layers:
+            desc += [len(keep), len(mod)] + [int(i) for i in keep] + [int(i) for i in mod] + widths + w_off + b_off
+        self.desc = np.asarray(desc, dtype=np.int32)
+        self.tensors, self.D, self.d, self.P = tensors, D, d, off
+        self.ok = True
+
+    def params(self) -> Tensor:
+        return torch.cat([t.reshape(-1) for t in self.tensors])
+
+
 class LayerProgram:
     def __init__(self, head_prior):
         """``head_prior``: the density subtree below the head (``head.prior``)."""
@@ -95,6 +146,8 @@ class LayerProgram:
         self._n_slots = 0
         self._dev_cache: Dict[Tuple[int, str], Tensor] = {}
         self._compile()
+        plan = FlatStackPlan(self.nodes, self.tail)
+        self.flat_plan = plan if plan.ok else None
 
     # ------------------------------------------------------------------ tree walk
     @staticmethod

@@ -256,6 +256,33 @@ int cmf_coupling_x_to_z_bwd(int B, int D, int Q, const float* z, const float* st
 int cmf_sumsq_diff_fwd(int B, int n, const float* a, const float* c, float* out, cmf_stream_t stream);
 int cmf_sumsq_diff_bwd(int B, int n, const float* a, const float* c, const float* g, float* g_a, cmf_stream_t stream);
 
+/* Whole-stack kernel for the small flat configs (the 2-D group of config/two_d.py:
+ * `flat-realnvp`, D <= 8, tanh MLP conditioners of width 10): ONE launch pushes the primal and all d
+ * tangent columns through the tail pad (non_square.py:397-410), every affine coupling layer INCLUDING
+ * its conditioner MLP with the reference's JVP rules (acl.py:125-146, networks.py:206-224,
+ * jvp_layers.py:38-64) and forms G = J^T J (non_square.py:307-308); one more launch is the adjoint of all
+ * of it.  The model's parameters live in shared memory, a sample's state in registers / local memory;
+ * per sample the kernel reads z (B,d) and writes G (B,d,d) and the primal output x (B,D).
+ *   desc (int32, host memory): D, d, L, nh, P, pos[d] (logical position of latent k after the tail pad),
+ *     then per layer in z -> x order: n_keep, n_mod, keep[n_keep], mod[n_mod] (logical positions in
+ *     conditioner-input / -output order), width[nh + 2] (MLP widths, first = n_keep, last = 2 n_mod),
+ *     w_off[nh + 1], b_off[nh + 1] (offsets of each Linear's weight (out,in) / bias in `params`).
+ *   params (P) fp32: the packed parameters.  bwd: g_G, g_x may be NULL (zero); g_params_partial holds
+ *     cmf_flat_stack_bwd_partials(B) x P floats, one partial per CTA (the host adds them). */
+#define CMF_FLAT_MAX_D       8
+#define CMF_FLAT_MAX_LATENT  8
+#define CMF_FLAT_MAX_WIDTH   16
+#define CMF_FLAT_MAX_HIDDEN  4
+#define CMF_FLAT_MAX_LAYERS  16
+#define CMF_FLAT_MAX_PARAMS  4096
+int cmf_flat_stack_usable(int D, int d, int L, int nh, int max_width, int P);
+int cmf_flat_stack_fwd(const int32_t* desc, int desc_len, int B, const float* z, const float* params,
+                       float* G, float* x, cmf_stream_t stream);
+int cmf_flat_stack_bwd_partials(int B);
+int cmf_flat_stack_bwd(const int32_t* desc, int desc_len, int B, const float* z, const float* params,
+                       const float* g_G, const float* g_x, float* g_z, float* g_params_partial,
+                       cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -262,7 +262,58 @@ def sumsq_diff_bwd(a, c, g):
     return 2 * g.view(-1, 1) * d
 
 
-ALL = ["preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
+def flat_stack_usable(D, d, L, nh, max_width, P):
+    return 1 <= D <= 8 and 1 <= d <= min(8, D) and 1 <= L <= 16 and 1 <= nh <= 4 and max_width <= 16 and P <= 4096
+
+
+def _flat_stack_eval(desc, z, params):
+    """the whole-stack kernel's contract in batched torch ops (descriptor layout: include/cmf_b200.h)"""
+    it = iter(int(v) for v in desc)
+    D, d, L, nh, P = (next(it) for _ in range(5))
+    pos = [next(it) for _ in range(d)]
+    B = z.shape[0]
+    x = z.new_zeros(B, D)
+    x = x.index_copy(1, torch.tensor(pos), z)
+    V = z.new_zeros(B, d, D)
+    V[:, torch.arange(d), torch.tensor(pos)] = 1.0
+    for _ in range(L):
+        n_keep, n_mod = next(it), next(it)
+        keep = torch.tensor([next(it) for _ in range(n_keep)])
+        mod = torch.tensor([next(it) for _ in range(n_mod)])
+        widths = [next(it) for _ in range(nh + 2)]
+        w_off = [next(it) for _ in range(nh + 1)]
+        b_off = [next(it) for _ in range(nh + 1)]
+        h, H = x[:, keep], V[:, :, keep]
+        for j in range(nh + 1):
+            W = params[w_off[j]: w_off[j] + widths[j] * widths[j + 1]].view(widths[j + 1], widths[j])
+            bias = params[b_off[j]: b_off[j] + widths[j + 1]]
+            h, H = h @ W.t() + bias, H @ W.t()
+            if j < nh:
+                h = torch.tanh(h)
+                H = H * (1 - h * h).unsqueeze(1)
+        t, s, T, S = h[:, :n_mod], h[:, n_mod:], H[:, :, :n_mod], H[:, :, n_mod:]
+        e = torch.exp(-s)
+        zq, Vq = x[:, mod], V[:, :, mod]
+        x = x.index_copy(1, mod, zq * e - t)
+        V = V.index_copy(2, mod, e.unsqueeze(1) * (Vq - zq.unsqueeze(1) * S) - T)
+    return V @ V.transpose(1, 2), x
+
+
+def flat_stack_fwd(desc, z, params):
+    G, x = _flat_stack_eval(desc, z, params)
+    return G.detach(), x.detach()
+
+
+def flat_stack_bwd(desc, z, params, g_G, g_x):
+    with torch.enable_grad():
+        zz, pp = z.detach().clone().requires_grad_(True), params.detach().clone().requires_grad_(True)
+        G, x = _flat_stack_eval(desc, zz, pp)
+        loss = (G * (torch.zeros_like(G) if g_G is None else g_G)).sum() + (x * (torch.zeros_like(x) if g_x is None else g_x)).sum()
+        gz, gp = torch.autograd.grad(loss, (zz, pp), allow_unused=True)
+    return (torch.zeros_like(z) if gz is None else gz), (torch.zeros_like(params) if gp is None else gp)
+
+
+ALL = ["flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
        "rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

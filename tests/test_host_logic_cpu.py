@@ -71,7 +71,7 @@ def test_intermediates(emu, name):
         assert_close(l1, g["l1_offdiag"], 2e-5, what="l1")
         if g["x_pre"] is not None:
             rl = ((recon - g["x_pre"]).flatten(1) ** 2).sum(-1, keepdim=True)
-            assert_close(rl, g["recon_loss"], 2e-5, what="recon")
+            assert_close(rl, g["recon_loss"], 2e-5, atol=1e-9, what="recon")   # d = D: the error is rounding noise (~1e-14)
         # primal-only program == tangent program's primal
         assert_close(head.flow_forward(z), recon, 1e-6, what="flow_forward")
 

@@ -267,3 +267,56 @@ def test_ops_autograd_matches_torch_autograd():
     _close(loss, loss_r, rtol=1e-5)
     for a, b in zip(dev_in, ref_in):
         _close(a.grad, b.grad, rtol=2e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("name,batch", [("sphere_gij_d3", 1000), ("sphere_gkk_d2", 77), ("sinusoid_gij_d6", 1000), ("sinusoid_plain_d3", 5)])
+def test_flat_stack_kernel_matches_the_layer_program(name, batch):
+    """Whole-stack kernel against the per-layer program it replaces (coupling kernel +
+    torch MLP JVPs + Gram kernel), on the 2-D config models: G, primal output, and the adjoint w.r.t. the
+    latent and EVERY parameter for random cotangents."""
+    import cmf_b200.head as H
+    from conftest import load_golden
+    from cases import CASES
+    from detfill import fill_state_dict
+    from helpers import build_product, strip_wrappers, find_head
+    g = load_golden(name)
+    density = build_product(g, "cpu")
+    density.load_state_dict(fill_state_dict(density.state_dict(), salt=2, gain=1.5))
+    density = density.to(DEV).train()
+    head, _ = find_head(strip_wrappers(density))
+    assert head.program.flat_plan is not None, "the 2-D configs must qualify for the whole-stack kernel"
+    d = head.program.d
+    gen = torch.Generator().manual_seed(batch)
+    z0 = torch.randn(batch, d, generator=gen).to(DEV)
+    gG = torch.randn(batch, d, d, generator=gen).to(DEV)
+    gX = torch.randn(batch, *head.x_shape, generator=gen).to(DEV)
+    results = []
+    for flat in (True, False):
+        H._FLAT_STACK = flat
+        try:
+            density.zero_grad()
+            z = z0.clone().requires_grad_(True)
+            gram, recon = head._get_full_jac_transpose_jac(z)
+            ((gram * gG).sum() + (recon * gX).sum()).backward()
+            results.append((gram.detach(), recon.detach(), z.grad.clone(),
+                            {n: p.grad.clone() for n, p in head.named_parameters() if p.grad is not None}))
+        finally:
+            H._FLAT_STACK = True
+    (G1, x1, gz1, gp1), (G0, x0, gz0, gp0) = results
+    _close(G1, G0, rtol=1e-5, what="G")
+    _close(x1, x0, rtol=1e-5, what="x")
+    _close(gz1, gz0, rtol=1e-4, atol=1e-5, what="g_z")
+    assert set(gp1) == set(gp0) and gp1
+    for n in gp0:
+        _close(gp1[n], gp0[n], rtol=1e-4, atol=1e-5 * float(gp0[n].abs().max()) + 1e-7, what=n)
+
+
+def test_flat_stack_rejects_what_it_cannot_hold():
+    import numpy as np
+    import cmf_b200.kernels as K
+    assert not K.flat_stack_usable(21, 10, 10, 4, 128, 500000)         # tabular: widths of 128 stay on the layer program
+    assert K.flat_stack_usable(3, 3, 5, 2, 10, 840)
+    from cmf_b200._lib import CmfB200Error
+    bad = np.asarray([3, 3, 5, 2, 840, 0, 1], dtype=np.int32)             # truncated descriptor
+    with pytest.raises(CmfB200Error):
+        K.flat_stack_fwd(bad, torch.zeros(2, 3, device=DEV), torch.zeros(840, device=DEV))
