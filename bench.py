@@ -398,14 +398,19 @@ def conv_roofline(conv, tf32, peaks, peak_kind):
                                     "frac": 6.0 * k["tflops"] / peaks["bf16_tflops"]},
            "algorithmic_flops_per_step": k["algorithmic_flops_per_step"],
            "full_size_launches": {v: d for v, d in k["by_variant"].items() if not v.startswith("N=50 ")}}
-    tpath = os.path.join(ROOT, "profiles", "conv_traffic.json")
-    if os.path.exists(tpath):
-        with open(tpath) as f:
-            t = json.load(f)
-        out.update(traffic=t["dram_bytes_per_launch"], traffic_source=t["source"], traffic_algorithmic=t.get("algorithmic_bytes_per_launch"))
-    else:
-        out.update(traffic=None, traffic_source="no ncu --set full capture of the current kernel is committed")
+    out.update(committed_traffic("conv_traffic.json"))
     return out
+
+
+def committed_traffic(name):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture"""
+    tpath = os.path.join(ROOT, "profiles", name)
+    if not os.path.exists(tpath):
+        return {"traffic": None, "traffic_source": "no ncu --set full capture of the current kernel is committed"}
+    with open(tpath) as f:
+        t = json.load(f)
+    return {"traffic": t["dram_bytes_per_launch"], "traffic_source": t["source"],
+            "traffic_algorithmic": t.get("algorithmic_bytes_per_launch")}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -799,8 +804,8 @@ def run_own_arm(args, cfg, schema):
             "conv_kernels": conv,
             "roofline_scope_a": {"kernel": "coupling_bwd_{vec4,map} (10 launches/step)", "bound": "hbm",
                                  "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                                 "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
-                                 "algorithmic_bytes_per_step": cb_bytes},
+                                 "frac": achieved / peaks["hbm_gbs"], "peak_source": peak_kind,
+                                 "algorithmic_bytes_per_step": cb_bytes, **committed_traffic("coupling_traffic.json")},
             "peak_mem_gib": peak_mem,
         }
         if breakdown is not None:
