@@ -45,6 +45,15 @@ SIGNATURES = {
     "cmf_flat_stack_fwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_flat_stack_bwd_partials": (_i, [_i]),
     "cmf_flat_stack_bwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_mlp_usable": (_i, [_i, _vp, _i]),
+    "cmf_mlp_pack_floats": (_ll, [_i]),
+    "cmf_mlp_tiles": (_i, [_i, _i]),
+    "cmf_mlp_save_floats": (_ll, [_i, _i, _i]),
+    "cmf_mlp_partials": (_i, [_i, _i]),
+    "cmf_mlp_partial_floats": (_ll, [_i, _i, _i]),
+    "cmf_mlp_pack": (_i, [_i, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_mlp_jvp_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_mlp_jvp_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cmf_conv3x3_c64_usable": (_i, [_i, _i, _i]),
     "cmf_conv3x3_c64_prep": (_i, [_vp, _i, _vp, _vp]),
     "cmf_conv3x3_c64_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp]),

@@ -4,7 +4,7 @@ fp32 contiguous tensors and raises otherwise -- there is no CPU path.
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
@@ -447,3 +447,85 @@ def flat_stack_bwd(desc, z: Tensor, params: Tensor, g_G: Optional[Tensor], g_x: 
         _lib.check(lib.cmf_flat_stack_bwd(ptr, n, B, _ptr(z), _ptr(params), _ptr(g_G), _ptr(g_x), _ptr(g_z), _ptr(parts),
                                           _stream()), "cmf_flat_stack_bwd")
     return g_z, (parts.sum(0) if nparts else torch.zeros_like(params))
+
+
+# ------------------------------------------------------------------------------------------------
+# tangent-batched tanh-MLP conditioner (flat couplers)
+# ------------------------------------------------------------------------------------------------
+MLP_TILE = 128
+MLP_PART_PER_LIN = MLP_TILE * MLP_TILE + MLP_TILE
+
+
+def _int_array(values):
+    import ctypes as C
+    return (C.c_int * len(values))(*[int(v) for v in values])
+
+
+def _ptr_array(tensors):
+    import ctypes as C
+    return (C.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+
+
+def mlp_usable(widths: Sequence[int], d: int, x: Tensor) -> bool:
+    """the fused MLP launches take these widths / this tangent count, and x is theirs to take (fp32 CUDA matrix)"""
+    return (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2
+            and bool(_lib.load().cmf_mlp_usable(len(widths) - 1, _int_array(widths), int(d))))
+
+
+def mlp_pack(weights: Sequence[Tensor], biases: Sequence[Tensor]) -> Tuple[Tensor, list]:
+    """Linear weights (out, in) / biases (out,) -> (wpack, widths): both operand layouts, zero padded to 128 x 128."""
+    lib = _lib.load()
+    weights = [_req(w, "weight") for w in weights]
+    biases = [_req(b, "bias") for b in biases]
+    widths = [weights[0].shape[1]] + [w.shape[0] for w in weights]
+    for l, w in enumerate(weights):
+        if w.shape[1] != widths[l] or biases[l].shape != (widths[l + 1],):
+            raise _lib.CmfB200Error("mlp_pack: Linear shapes do not chain")
+    nlin = len(weights)
+    wpack = torch.empty(lib.cmf_mlp_pack_floats(nlin), dtype=torch.float32, device=weights[0].device)
+    with torch.cuda.device(wpack.device):
+        _lib.check(lib.cmf_mlp_pack(nlin, _int_array(widths), _ptr_array(weights), _ptr_array(biases), _ptr(wpack), _stream()),
+                   "cmf_mlp_pack")
+    return wpack, widths
+
+
+def mlp_jvp_fwd(x: Tensor, V: Optional[Tensor], wpack: Tensor, widths: Sequence[int], save: bool):
+    """x (B, n_in), V (B, d, n_in) or None -> st (B, n_out), ST (B, d, n_out) or None, saved = (save_T, save_U) or None"""
+    lib = _lib.load()
+    x = _req(x, "x")
+    V = None if V is None else _req(V, "V")
+    B, d, nlin = x.shape[0], (0 if V is None else V.shape[1]), len(widths) - 1
+    if x.shape[1] != widths[0] or (V is not None and (V.shape[0] != B or V.shape[2] != widths[0])):
+        raise _lib.CmfB200Error("mlp_jvp_fwd: input shapes do not match the first Linear")
+    st = torch.empty(B, widths[-1], dtype=torch.float32, device=x.device)
+    ST = None if V is None else torch.empty(B, d, widths[-1], dtype=torch.float32, device=x.device)
+    saved = None
+    if save:
+        n = lib.cmf_mlp_save_floats(B, d, nlin)
+        saved = (torch.empty(max(n, 4), dtype=torch.float32, device=x.device), torch.empty(max(n, 4), dtype=torch.float32, device=x.device))
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_mlp_jvp_fwd(B, d, nlin, _int_array(widths), _ptr(x), _ptr(V), _ptr(wpack), _ptr(st), _ptr(ST),
+                                       _ptr(saved[0]) if save else None, _ptr(saved[1]) if save else None, _stream()),
+                   "cmf_mlp_jvp_fwd")
+    return st, ST, saved
+
+
+def mlp_jvp_bwd(x: Tensor, V: Optional[Tensor], wpack: Tensor, widths: Sequence[int], saved, g_st: Tensor, g_ST: Optional[Tensor]):
+    """-> g_x, g_V (or None), [g_W[l] (out, in) views], [g_b[l]] (the per-CTA partials reduced in a fixed order)"""
+    lib = _lib.load()
+    x, g_st = _req(x, "x"), _req(g_st, "g_st")
+    V = None if V is None else _req(V, "V")
+    B, d, nlin = x.shape[0], (0 if V is None else V.shape[1]), len(widths) - 1
+    if V is not None:
+        g_ST = torch.zeros(B, d, widths[-1], dtype=torch.float32, device=x.device) if g_ST is None else _req(g_ST, "g_ST")
+    g_x = torch.empty_like(x)
+    g_V = None if V is None else torch.empty_like(V)
+    partial = torch.empty(max(lib.cmf_mlp_partial_floats(B, d, nlin), 4), dtype=torch.float32, device=x.device)
+    gpack = torch.empty(nlin, MLP_PART_PER_LIN, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_mlp_jvp_bwd(B, d, nlin, _int_array(widths), _ptr(x), _ptr(V), _ptr(wpack), _ptr(saved[0]), _ptr(saved[1]),
+                                       _ptr(g_st), _ptr(g_ST), _ptr(g_x), _ptr(g_V), _ptr(partial), _ptr(gpack), _stream()),
+                   "cmf_mlp_jvp_bwd")
+    g_W = [gpack[l, :MLP_TILE * MLP_TILE].view(MLP_TILE, MLP_TILE)[:widths[l + 1], :widths[l]] for l in range(nlin)]
+    g_b = [gpack[l, MLP_TILE * MLP_TILE:MLP_TILE * MLP_TILE + widths[l + 1]] for l in range(nlin)]
+    return g_x, g_V, g_W, g_b

@@ -32,6 +32,10 @@ _BWD_DRAIN = int(os.environ.get("CMF_BWD_DRAIN", "2"))
 _FWD_DRAIN = int(os.environ.get("CMF_FWD_DRAIN", "1"))
 
 
+# CMF_MLP=torch keeps the tanh-MLP conditioners of the flat couplers on F.linear + elementwise ops
+_MLP_FUSED = os.environ.get("CMF_MLP", "fused") != "torch"
+
+
 class recompute_activations:
     """Activation recomputation for the residual-stack node: inside this context (or with
     ``CMF_RECOMPUTE=1`` in the environment) ``_ResidualStackJoint`` keeps only the stack's INPUT (primal
@@ -50,8 +54,8 @@ class recompute_activations:
 
 
 class library_convs:
-    """Inside this context every conditioner convolution is the library call ``F.conv2d`` (which
-    autograd can differentiate twice).  Used for the primal run whose VJP is itself differentiated
+    """Inside this context every conditioner convolution is the library call ``F.conv2d`` and every
+    MLP conditioner the ``F.linear`` stack (which autograd can differentiate twice).  Used for the primal run whose VJP is itself differentiated
     (`non_square.py:199`, ``create_graph=True`` of hutch_with_cg): the tcgen05 convolution ops carry
     first-order adjoints only."""
     depth = 0
@@ -100,9 +104,29 @@ class TangentMLP(nn.Sequential):
         layers.append(nn.Linear(prev, num_out))
         super().__init__(*layers)
         self.activation = activation
+        self.widths = [num_in, *hidden, num_out]
+
+    def _fused(self, x: Tensor, d: int) -> bool:
+        """the whole stack as one launch of the hand-written kernel (``ops.mlp_jvp``)"""
+        from . import kernels
+        return (_MLP_FUSED and library_convs.depth == 0 and self.activation == "tanh"
+                and kernels.mlp_usable(self.widths, d, x))
+
+    def _linears(self):
+        lin = [m for m in self if isinstance(m, nn.Linear)]
+        return [m.weight for m in lin], [m.bias for m in lin]
+
+    def forward(self, x: Tensor) -> Tensor:
+        if self._fused(x, 0):
+            from . import ops
+            return ops.mlp_jvp(x, None, *self._linears())[0]
+        return super().forward(x)
 
     def jvp_batched(self, x: Tensor, V: Tensor) -> Tuple[Tensor, Tensor]:
         """x (B,p), V (B,d,p) -> y (B,o), Y (B,d,o)."""
+        if self._fused(x, V.shape[1]):
+            from . import ops
+            return ops.mlp_jvp(x, V, *self._linears())
         for mod in self:
             if isinstance(mod, nn.Linear):
                 x, V = mod(x), F.linear(V, mod.weight)

@@ -376,3 +376,36 @@ def flat_stack_gram(z: Tensor, params: Tensor, desc) -> Tuple[Tensor, Tensor]:
     tanh-MLP conditioner (primal + d tangents) and J^T J (`non_square.py:298-311,397-410`,
     `acl.py:125-146`, `networks.py:206-224`).  ``desc`` from :class:`cmf_b200.program.FlatStackPlan`."""
     return _FlatStackGram.apply(z, params, desc)
+
+
+# ------------------------------------------------------------------ whole tanh-MLP conditioner, flat couplers (N1-ii)
+class _MlpJvp(Function):
+    @staticmethod
+    def forward(ctx, x, V, nlin, *wb):
+        weights, biases = wb[:nlin], wb[nlin:]
+        wpack, widths = kernels.mlp_pack(weights, biases)
+        need = any(ctx.needs_input_grad)
+        st, ST, saved = kernels.mlp_jvp_fwd(x, V, wpack, widths, save=need)
+        if need:
+            tensors = [x, wpack, *saved] + ([V] if V is not None else [])
+            ctx.save_for_backward(*tensors)
+        ctx.widths, ctx.has_V = widths, V is not None
+        ctx.set_materialize_grads(False)
+        return st, ST
+
+    @staticmethod
+    def backward(ctx, g_st, g_ST):
+        x, wpack, save_T, save_U, *rest = ctx.saved_tensors
+        V = rest[0] if ctx.has_V else None
+        if g_st is None:
+            g_st = torch.zeros(x.shape[0], ctx.widths[-1], dtype=x.dtype, device=x.device)
+        g_x, g_V, g_W, g_b = kernels.mlp_jvp_bwd(x, V, wpack, ctx.widths, (save_T, save_U), g_st.contiguous(),
+                                                 None if g_ST is None else g_ST.contiguous())
+        return (g_x, g_V, None, *g_W, *g_b)
+
+
+def mlp_jvp(x: Tensor, V: Optional[Tensor], weights, biases) -> Tuple[Tensor, Optional[Tensor]]:
+    """A tanh MLP on the primal x (B, n_in) and, if given, on the tangents V (B, d, n_in) by the
+    reference's JVP rules (`networks.py:24-32,206-224`, `jvp_layers.py:38-47`), the whole stack in
+    one launch; its adjoint (inputs, weights, biases) in one launch plus a fixed-order reduction."""
+    return _MlpJvp.apply(x, V, len(weights), *weights, *biases)

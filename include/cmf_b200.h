@@ -283,6 +283,38 @@ int cmf_flat_stack_bwd(const int32_t* desc, int desc_len, int B, const float* z,
                        const float* g_G, const float* g_x, float* g_z, float* g_params_partial,
                        cmf_stream_t stream);
 
+/* ---- tangent-batched tanh-MLP conditioner of the flat couplers --------------------
+ * The whole MLP of a coupler -- Linear, tanh, ..., Linear; primal + d tangent columns -- in one launch,
+ * and its adjoint (data, weight and bias gradients) in one launch plus a fixed-order reduction.
+ * Replaces cmf/models/components/networks.py:206-224 (get_mlp), :24-32 (NN_Sequential_JVP.jvp),
+ * jvp_layers.py:38-47 (bias-free Linear on the tangent, tanh' of the primal as the tangent's mask) and
+ * what autograd derives from them at cmf/trainer.py:216.  Exact FP32 FMA (the reference runs these
+ * Linears in FP32), bitwise reproducible.
+ *   width[0 .. nlin]: input width, hidden widths, output width; every width in 1 .. 128, nlin <= 8;
+ *   d in 0 .. 127 (d = 0: primal only, V / ST / g_ST / g_V / save_U may be null).
+ *   x (B, width[0]), V (B, d, width[0]) -> st (B, width[nlin]) (with bias), ST (B, d, width[nlin]).
+ *   cmf_mlp_pack: W[l] (width[l+1], width[l]) row-major and b[l] (width[l+1]) (host arrays of device
+ *     pointers) -> wpack (cmf_mlp_pack_floats(nlin) floats): both operand layouts, zero padded.
+ *   save_T, save_U: cmf_mlp_save_floats(B, d, nlin) floats each, written by the forward launch for the
+ *     adjoint (masked / unmasked hidden vectors, tile by tile); both null = inference.
+ *   partial: cmf_mlp_partial_floats(B, d, nlin) floats of scratch (one partial per CTA, no zeroing needed);
+ *   gpack (nlin x (128*128 + 128) floats): g_W[l][j][k] at l*16512 + j*128 + k, g_b[l][j] at l*16512 + 16384 + j.
+ *   16-byte alignment of wpack, save_T, save_U.  No allocation, no synchronisation. */
+#define CMF_MLP_MAX_LINEARS 8
+int cmf_mlp_usable(int nlin, const int* width, int d);
+long long cmf_mlp_pack_floats(int nlin);
+int cmf_mlp_tiles(int B, int d);
+long long cmf_mlp_save_floats(int B, int d, int nlin);
+int cmf_mlp_partials(int B, int d);
+long long cmf_mlp_partial_floats(int B, int d, int nlin);
+int cmf_mlp_pack(int nlin, const int* width, const float* const* W, const float* const* b, float* wpack,
+                 cmf_stream_t stream);
+int cmf_mlp_jvp_fwd(int B, int d, int nlin, const int* width, const float* x, const float* V,
+                    const float* wpack, float* st, float* ST, float* save_T, float* save_U, cmf_stream_t stream);
+int cmf_mlp_jvp_bwd(int B, int d, int nlin, const int* width, const float* x, const float* V,
+                    const float* wpack, const float* save_T, const float* save_U, const float* g_st,
+                    const float* g_ST, float* g_x, float* g_V, float* partial, float* gpack, cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -313,7 +313,63 @@ def flat_stack_bwd(desc, z, params, g_G, g_x):
     return (torch.zeros_like(z) if gz is None else gz), (torch.zeros_like(params) if gp is None else gp)
 
 
-ALL = ["flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
+def mlp_usable(widths, d, x):
+    return x.dim() == 2 and x.dtype == torch.float32 and len(widths) - 1 <= 8 and max(widths) <= 128 and 0 <= d < 128
+
+
+def mlp_pack(weights, biases):
+    widths = [weights[0].shape[1]] + [w.shape[0] for w in weights]
+    return torch.cat([w.reshape(-1) for w in weights] + [b.reshape(-1) for b in biases]), widths
+
+
+def _mlp_unpack(wpack, widths):
+    ws, bs, o = [], [], 0
+    for l in range(len(widths) - 1):
+        n = widths[l] * widths[l + 1]
+        ws.append(wpack[o:o + n].view(widths[l + 1], widths[l]))
+        o += n
+    for l in range(len(widths) - 1):
+        bs.append(wpack[o:o + widths[l + 1]])
+        o += widths[l + 1]
+    return ws, bs
+
+
+def _mlp_eval(x, V, ws, bs):
+    """`networks.py:24-32,206-224`, `jvp_layers.py:38-47`: Linear (bias-free on the tangents), tanh with its JVP mask"""
+    for l, (W, b) in enumerate(zip(ws, bs)):
+        x = x @ W.t() + b
+        V = None if V is None else V @ W.t()
+        if l + 1 < len(ws):
+            x = torch.tanh(x)
+            V = None if V is None else V * (1 - x * x).unsqueeze(1)
+    return x, V
+
+
+def mlp_jvp_fwd(x, V, wpack, widths, save):
+    st, ST = _mlp_eval(x, V, *_mlp_unpack(wpack, widths))
+    saved = (x.new_zeros(4), x.new_zeros(4)) if save else None
+    return st.detach(), (None if ST is None else ST.detach()), saved
+
+
+def mlp_jvp_bwd(x, V, wpack, widths, saved, g_st, g_ST):
+    with torch.enable_grad():
+        xx = x.detach().clone().requires_grad_(True)
+        VV = None if V is None else V.detach().clone().requires_grad_(True)
+        ws, bs = _mlp_unpack(wpack.detach(), widths)
+        ws = [w.clone().requires_grad_(True) for w in ws]
+        bs = [b.clone().requires_grad_(True) for b in bs]
+        st, ST = _mlp_eval(xx, VV, ws, bs)
+        loss = (st * g_st).sum() + (0 if (ST is None or g_ST is None) else (ST * g_ST).sum())
+        ins = [xx] + ([VV] if VV is not None else []) + ws + bs
+        gr = list(torch.autograd.grad(loss, ins, allow_unused=True))
+        gr = [torch.zeros_like(t) if g is None else g for g, t in zip(gr, ins)]
+    g_x = gr.pop(0)
+    g_V = gr.pop(0) if VV is not None else None
+    n = len(ws)
+    return g_x, g_V, gr[:n], gr[n:]
+
+
+ALL = ["mlp_usable", "mlp_pack", "mlp_jvp_fwd", "mlp_jvp_bwd", "flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
        "rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

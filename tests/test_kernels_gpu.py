@@ -320,3 +320,104 @@ def test_flat_stack_rejects_what_it_cannot_hold():
     bad = np.asarray([3, 3, 5, 2, 840, 0, 1], dtype=np.int32)             # truncated descriptor
     with pytest.raises(CmfB200Error):
         K.flat_stack_fwd(bad, torch.zeros(2, 3, device=DEV), torch.zeros(840, device=DEV))
+
+
+# ------------------------------------------------------------------------------------------------
+# whole tanh-MLP conditioner (cmf_mlp_pack / cmf_mlp_jvp_fwd / cmf_mlp_jvp_bwd)
+# ------------------------------------------------------------------------------------------------
+MLP_SHAPES = [  # B, d, widths
+    (50, 6, [3, 128, 128, 128, 128, 6]),        # power-shape coupler, S = 18 samples per tile, ragged last tile
+    (37, 10, [11, 128, 128, 128, 128, 20]),     # hepmass-shape coupler, S = 11
+    (300, 3, [2, 10, 10, 2]),                   # 2-D coupler widths (small-tile paths of the weight gradient)
+    (5, 0, [4, 32, 32, 8]),                     # primal only (encode pass / prior flow)
+    (260, 0, [21, 128, 128, 42]),               # primal only, three tiles
+    (9, 2, [5, 7]),                             # a single Linear
+    (23, 5, [40, 100, 70, 90]),                 # every width between the 32 / 64 thresholds and 128
+    (3, 127, [6, 33, 64, 65, 12]),              # one sample per tile
+    (1, 1, [1, 1, 1]),
+]
+
+
+def _mlp_case(B, d, widths, seed=0):
+    g = torch.Generator().manual_seed(seed + B + d + sum(widths))
+    r = lambda *s: torch.rand(*s, generator=g, dtype=torch.float64) * 2 - 1
+    ws = [r(widths[l + 1], widths[l]) * (1.5 / widths[l] ** 0.5) for l in range(len(widths) - 1)]
+    bs = [r(widths[l + 1]) * 0.5 for l in range(len(widths) - 1)]
+    x, V = r(B, widths[0]), (r(B, d, widths[0]) if d else None)
+    g_st, g_ST = r(B, widths[-1]), (r(B, d, widths[-1]) if d else None)
+    return ws, bs, x, V, g_st, g_ST
+
+
+@pytest.mark.parametrize("B,d,widths", MLP_SHAPES)
+def test_mlp_jvp_fwd_bwd(B, d, widths):
+    """One-launch MLP conditioner against the Linear / tanh / JVP-mask stack in fp64
+    (`networks.py:24-32,206-224`, `jvp_layers.py:38-47`): outputs, and the adjoint w.r.t. inputs,
+    tangents, every weight and bias."""
+    import cmf_b200.kernels as K
+    ws, bs, x, V, g_st, g_ST = _mlp_case(B, d, widths)
+    f = lambda t: None if t is None else t.float().to(DEV)
+    assert K.mlp_usable(widths, d, f(x))
+    wpack, w2 = K.mlp_pack([f(w) for w in ws], [f(b) for b in bs])
+    assert w2 == widths
+    st, ST, saved = K.mlp_jvp_fwd(f(x), f(V), wpack, widths, save=True)
+    st0, ST0, _ = K.mlp_jvp_fwd(f(x), f(V), wpack, widths, save=False)          # inference launch: same values
+    assert torch.equal(st, st0) and (ST is None or torch.equal(ST, ST0))
+    epack, _ = E.mlp_pack(ws, bs)
+    rst, rST, _ = E.mlp_jvp_fwd(x, V, epack, widths, False)
+    _close(st, rst, what="st")
+    if d:
+        _close(ST, rST, what="ST")
+    g_x, g_V, g_W, g_b = K.mlp_jvp_bwd(f(x), f(V), wpack, widths, saved, f(g_st), f(g_ST))
+    rg_x, rg_V, rg_W, rg_b = E.mlp_jvp_bwd(x, V, epack, widths, None, g_st, g_ST)
+    _close(g_x, rg_x, rtol=2e-5, what="g_x")
+    if d:
+        _close(g_V, rg_V, rtol=2e-5, what="g_V")
+    for l in range(len(ws)):
+        assert g_W[l].shape == ws[l].shape and g_b[l].shape == bs[l].shape
+        _close(g_W[l], rg_W[l], rtol=2e-5, what=f"g_W[{l}]")
+        _close(g_b[l], rg_b[l], rtol=2e-5, what=f"g_b[{l}]")
+    # bitwise reproducible (fixed reduction orders everywhere)
+    g_x2, g_V2, g_W2, g_b2 = K.mlp_jvp_bwd(f(x), f(V), wpack, widths, saved, f(g_st), f(g_ST))
+    assert torch.equal(g_x, g_x2) and all(torch.equal(a, b) for a, b in zip(g_W + g_b, g_W2 + g_b2))
+
+
+def test_mlp_op_through_autograd_and_many_tiles():
+    """ops.mlp_jvp at the tabular step's size (B = 5000, d = 6: 278 tiles over 148 persistent CTAs) against the
+    F.linear stack it replaces, through autograd."""
+    from cmf_b200 import networks, ops
+    torch.manual_seed(0)
+    net = networks.TangentMLP(3, [128] * 4, 6, "tanh").to(DEV)
+    x = torch.randn(5000, 3, device=DEV, requires_grad=True)
+    V = torch.randn(5000, 6, 3, device=DEV, requires_grad=True)
+    gy, gY = torch.randn(5000, 6, device=DEV), torch.randn(5000, 6, 6, device=DEV)
+    res = []
+    for fused in (True, False):
+        networks._MLP_FUSED = fused
+        try:
+            for t in (x, V, *net.parameters()):
+                t.grad = None
+            y, Y = net.jvp_batched(x, V)
+            ((y * gy).sum() + (Y * gY).sum()).backward()
+            res.append((y.detach(), Y.detach(), x.grad.clone(), V.grad.clone(), [p.grad.clone() for p in net.parameters()]))
+        finally:
+            networks._MLP_FUSED = True
+    (y1, Y1, gx1, gV1, gp1), (y0, Y0, gx0, gV0, gp0) = res
+    _close(y1, y0, what="y"); _close(Y1, Y0, what="Y")
+    _close(gx1, gx0, rtol=1e-4, what="g_x"); _close(gV1, gV0, rtol=1e-4, what="g_V")
+    for a, b in zip(gp1, gp0):
+        _close(a, b, rtol=1e-4, what="g_param")
+    # primal-only entry (encode pass) and no-grad mode
+    y2 = net(x.detach())
+    _close(y2, y0, what="forward")
+
+
+def test_mlp_rejects_what_it_cannot_hold():
+    import cmf_b200.kernels as K
+    from cmf_b200._lib import CmfB200Error
+    x = torch.zeros(4, 3, device=DEV)
+    assert not K.mlp_usable([3, 512, 512, 6], 6, x)                   # wider than a tile: stays on F.linear
+    assert not K.mlp_usable([3, 128, 6], 128, x)                      # 1 + d rows of a sample must fit a tile
+    assert not K.mlp_usable([3, 128, 6], 2, x.cpu())
+    wpack, widths = K.mlp_pack([torch.zeros(8, 3, device=DEV)], [torch.zeros(8, device=DEV)])
+    with pytest.raises(CmfB200Error):
+        K.mlp_jvp_fwd(torch.zeros(4, 5, device=DEV), None, wpack, widths, save=False)     # wrong input width
