@@ -16,4 +16,9 @@ timeout 600 ncu --set full --clock-control none --import-source on -k regex:conv
 timeout 100 python scripts/one_coupling.py || exit 1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:coupling_bwd_vec4 -s 2 -c 1 -f \
     -o gpurun_out/${R}_coupling_bwd python scripts/one_coupling.py > gpurun_out/ncu4.log 2>&1
+timeout 100 python scripts/one_mlp.py || exit 1
+timeout 400 ncu --set full --clock-control none --import-source on -k regex:mlp_fwd_kernel -s 1 -c 1 -f \
+    -o gpurun_out/${R}_mlp_fwd python scripts/one_mlp.py > gpurun_out/ncu5.log 2>&1
+timeout 400 ncu --set full --clock-control none --import-source on -k regex:mlp_bwd_kernel -s 1 -c 1 -f \
+    -o gpurun_out/${R}_mlp_bwd python scripts/one_mlp.py > gpurun_out/ncu6.log 2>&1
 ls -la gpurun_out/ | tail -12
