@@ -45,6 +45,10 @@ SIGNATURES = {
     "cmf_flat_stack_fwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_flat_stack_bwd_partials": (_i, [_i]),
     "cmf_flat_stack_bwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_resnet_tail_usable": (_i, [_i, _i]),
+    "cmf_resnet_tail_partial_floats": (_ll, [_i, _i, _i, _i, _i, _i]),
+    "cmf_resnet_tail_fwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_resnet_tail_bwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "cmf_mlp_usable": (_i, [_i, _vp, _i]),
     "cmf_mlp_pack_floats": (_ll, [_i]),
     "cmf_mlp_tiles": (_i, [_i, _i]),

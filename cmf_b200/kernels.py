@@ -529,3 +529,58 @@ def mlp_jvp_bwd(x: Tensor, V: Optional[Tensor], wpack: Tensor, widths: Sequence[
     g_W = [gpack[l, :MLP_TILE * MLP_TILE].view(MLP_TILE, MLP_TILE)[:widths[l + 1], :widths[l]] for l in range(nlin)]
     g_b = [gpack[l, MLP_TILE * MLP_TILE:MLP_TILE * MLP_TILE + widths[l + 1]] for l in range(nlin)]
     return g_x, g_V, g_W, g_b
+
+
+# ------------------------------------------------------------------------------------------------
+# tail of the image couplers' conditioner: ReLU -> 1x1 conv -> scaled tanh, primal + tangents
+# ------------------------------------------------------------------------------------------------
+def resnet_tail_usable(x: Tensor, C: int, num_out: int) -> bool:
+    """the fused tail takes C hidden channels -> num_out outputs, and x (the net's input) is fp32 on a CUDA device"""
+    return x.is_cuda and x.dtype == torch.float32 and bool(_lib.load().cmf_resnet_tail_usable(int(C), int(num_out)))
+
+
+def resnet_tail_fwd(h: Tensor, Hv: Optional[Tensor], inv: Optional[Tensor], P: int, w2: Tensor, b2: Tensor, sw: Tensor, sb: Tensor):
+    """h (B, C, HW), Hv (B d, C, HW) or None, inv int32 (HW) or None, w2 (O, C), b2 / sw / sb (O) -> y (B, O, P), Y (B, d, O, P) or None"""
+    lib = _lib.load()
+    h, w2, b2, sw, sb = _req(h, "h"), _req(w2, "w2"), _req(b2, "b2"), _req(sw, "sw"), _req(sb, "sb")
+    B, C, HW = h.shape
+    O = w2.shape[0]
+    d = 0
+    if Hv is not None:
+        Hv = _req(Hv, "Hv")
+        assert Hv.shape[1:] == (C, HW) and (B == 0 or Hv.shape[0] % B == 0)
+        d = Hv.shape[0] // max(B, 1)
+    inv = None if inv is None else _req(inv, "inv", torch.int32)
+    assert w2.shape == (O, C) and b2.numel() == O and sw.numel() == O and sb.numel() == O and (inv is None or inv.numel() == HW)
+    y = torch.empty(B, O, P, dtype=torch.float32, device=h.device)
+    Y = None if Hv is None else torch.empty(B, d, O, P, dtype=torch.float32, device=h.device)
+    with torch.cuda.device(h.device):
+        _lib.check(lib.cmf_resnet_tail_fwd(B, d, C, HW, int(P), O, _ptr(h), _ptr(Hv), _ptr(inv), _ptr(w2), _ptr(b2), _ptr(sw), _ptr(sb),
+                                           _ptr(y), _ptr(Y), _stream()), "cmf_resnet_tail_fwd")
+    return y, Y
+
+
+def resnet_tail_bwd(h: Tensor, Hv: Optional[Tensor], inv: Optional[Tensor], P: int, w2: Tensor, b2: Tensor, sw: Tensor, sb: Tensor,
+                    g_y: Optional[Tensor], g_Y: Optional[Tensor]):
+    """-> g_h (B, C, HW), g_Hv (B d, C, HW) or None (dense: zeros at unused positions), g_w2 (O, C), g_b2, g_sw, g_sb (O)"""
+    lib = _lib.load()
+    h, w2, b2, sw, sb = _req(h, "h"), _req(w2, "w2"), _req(b2, "b2"), _req(sw, "sw"), _req(sb, "sb")
+    B, C, HW = h.shape
+    O = w2.shape[0]
+    d = 0
+    if Hv is not None:
+        Hv = _req(Hv, "Hv")
+        d = Hv.shape[0] // max(B, 1)
+        g_Y = torch.zeros(B, d, O, P, dtype=torch.float32, device=h.device) if g_Y is None else _req(g_Y, "g_Y")
+    inv = None if inv is None else _req(inv, "inv", torch.int32)
+    g_y = None if g_y is None else _req(g_y, "g_y")
+    g_h = torch.empty_like(h)
+    g_Hv = None if Hv is None else torch.empty_like(Hv)
+    partial = torch.empty(max(lib.cmf_resnet_tail_partial_floats(B, d, HW, int(P), C, O), 4), dtype=torch.float32, device=h.device)
+    gp = torch.empty(O * C + 3 * O, dtype=torch.float32, device=h.device)
+    with torch.cuda.device(h.device):
+        _lib.check(lib.cmf_resnet_tail_bwd(B, d, C, HW, int(P), O, _ptr(h), _ptr(Hv), _ptr(inv), _ptr(w2), _ptr(b2), _ptr(sw), _ptr(sb),
+                                           _ptr(g_y), _ptr(g_Y), _ptr(g_h), _ptr(g_Hv), _ptr(partial), _ptr(gp), _stream()),
+                   "cmf_resnet_tail_bwd")
+    n = O * C
+    return g_h, g_Hv, gp[:n].view(O, C), gp[n:n + O], gp[n + O:n + 2 * O], gp[n + 2 * O:]

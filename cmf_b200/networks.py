@@ -32,6 +32,8 @@ _BWD_DRAIN = int(os.environ.get("CMF_BWD_DRAIN", "2"))
 _FWD_DRAIN = int(os.environ.get("CMF_FWD_DRAIN", "1"))
 
 
+# CMF_TAIL=torch keeps the ReLU -> 1x1 conv -> scaled tanh tail of the image couplers on library ops
+_TAIL_FUSED = os.environ.get("CMF_TAIL", "fused") != "torch"
 # CMF_MLP=torch keeps the tanh-MLP conditioners of the flat couplers on F.linear + elementwise ops
 _MLP_FUSED = os.environ.get("CMF_MLP", "fused") != "torch"
 
@@ -359,6 +361,8 @@ class ScaledTanhResNet(nn.Module):
         self.bias = nn.Parameter(torch.zeros(num_out, 1, 1))
 
     def forward(self, x: Tensor) -> Tensor:
+        if self._tail_fused(x):
+            return self._tail_apply(self.module[:-2](x), None, None)[0]
         return self.weights * torch.tanh(self.module(x)) + self.bias
 
     # -- compact tail ------------------------------------------------------------------------
@@ -375,8 +379,33 @@ class ScaledTanhResNet(nn.Module):
         assert isinstance(relu, nn.ReLU) and isinstance(last, nn.Conv2d) and last.kernel_size == (1, 1)
         return last
 
-    def forward_compact(self, x: Tensor, pos: Tensor) -> Tensor:
-        """x (B,C,H,W), pos (P,) int64 spatial positions -> y (B,O,P)."""
+    def _tail_fused(self, x: Tensor) -> bool:
+        """the tail as one launch of the hand-written kernel (``ops.resnet_tail``)"""
+        from . import kernels
+        last = self.module[-1]
+        return (_TAIL_FUSED and library_convs.depth == 0 and isinstance(last, nn.Conv2d) and last.kernel_size == (1, 1)
+                and last.bias is not None and kernels.resnet_tail_usable(x, last.weight.shape[1], last.weight.shape[0]))
+
+    def _tail_apply(self, h: Tensor, Hv, pos):
+        """h (B,C,H,W) hidden activations before the last ReLU, Hv (B*d,C,H,W) their tangents or None, pos as in
+        :meth:`jvp_batched` -> (y, Y): compact (B,O,P) / (B,d,O,P) with ``pos``, else (B,O,H,W) / (B,d,O,H,W)"""
+        from . import ops
+        last = self._tail()
+        B, _, H, W = h.shape
+        O = last.weight.shape[0]
+        inv, P = (None, H * W) if pos is None else (pos[1], pos[0].numel())
+        y, Y = ops.resnet_tail(h.flatten(2), None if Hv is None else Hv.flatten(2), inv, P, last.weight.flatten(1), last.bias,
+                               self.weights.flatten(), self.bias.flatten())
+        if pos is None:
+            y = y.view(B, O, H, W)
+            Y = None if Y is None else Y.view(B, -1, O, H, W)
+        return y, Y
+
+    def forward_compact(self, x: Tensor, pos) -> Tensor:
+        """x (B,C,H,W), pos = (idx int32 (P,), inv int32 (H*W,), pos int64 (P,)) -> y (B,O,P)."""
+        if self._tail_fused(x):
+            return self._tail_apply(self.module[:-2](x), None, pos)[0]
+        pos = pos[2]
         last = self._tail()
         h = self.module[:-2](x).flatten(2).index_select(2, pos)
         y = torch.matmul(last.weight.flatten(1), torch.relu(h)) + last.bias.view(1, -1, 1)
@@ -388,7 +417,8 @@ class ScaledTanhResNet(nn.Module):
         B, d = V.shape[:2]
         Hv = V.reshape(B * d, *V.shape[2:])
         h = x
-        body = list(self.module if pos is None else self.module[:-2])
+        fused_tail = self._tail_fused(x)
+        body = list(self.module if (pos is None and not fused_tail) else self.module[:-2])
         i = 0
         while i < len(body):
             mod = body[i]
@@ -407,6 +437,8 @@ class ScaledTanhResNet(nn.Module):
                 h = torch.relu(h)
             else:
                 raise ValueError(f"jvp unsupported for module {type(mod).__name__}")
+        if fused_tail:
+            return self._tail_apply(h, Hv, pos)
         if pos is not None:
             from . import ops
             idx, inv, pos64 = pos
@@ -461,7 +493,7 @@ class ChunkedSharedCoupler(nn.Module):
         spatial positions only (compact outputs, Q = channels * len(pos))."""
         net = self.shift_log_scale_net
         if V is None:
-            y = net(x) if pos is None else net.forward_compact(x, pos[2])
+            y = net(x) if pos is None else net.forward_compact(x, pos)
             return y.flatten(1), None
         y, Y = net.jvp_batched(x, V) if pos is None else net.jvp_batched(x, V, pos)
         return y.flatten(1), Y.flatten(2)

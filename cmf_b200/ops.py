@@ -409,3 +409,31 @@ def mlp_jvp(x: Tensor, V: Optional[Tensor], weights, biases) -> Tuple[Tensor, Op
     reference's JVP rules (`networks.py:24-32,206-224`, `jvp_layers.py:38-47`), the whole stack in
     one launch; its adjoint (inputs, weights, biases) in one launch plus a fixed-order reduction."""
     return _MlpJvp.apply(x, V, len(weights), *weights, *biases)
+
+
+# ------------------------------------------------------------------ tail of the image couplers' conditioner (N1-i)
+class _ResnetTail(Function):
+    @staticmethod
+    def forward(ctx, h, Hv, inv, P, w2, b2, sw, sb):
+        y, Y = kernels.resnet_tail_fwd(h, Hv, inv, P, w2, b2, sw, sb)
+        tensors = [h, w2, b2, sw, sb] + ([Hv] if Hv is not None else []) + ([inv] if inv is not None else [])
+        ctx.save_for_backward(*tensors)
+        ctx.has_Hv, ctx.has_inv, ctx.P = Hv is not None, inv is not None, P
+        ctx.set_materialize_grads(False)
+        return y, Y
+
+    @staticmethod
+    def backward(ctx, g_y, g_Y):
+        h, w2, b2, sw, sb, *rest = ctx.saved_tensors
+        Hv = rest.pop(0) if ctx.has_Hv else None
+        inv = rest.pop(0) if ctx.has_inv else None
+        g_h, g_Hv, g_w2, g_b2, g_sw, g_sb = kernels.resnet_tail_bwd(
+            h, Hv, inv, ctx.P, w2, b2, sw, sb, None if g_y is None else g_y.contiguous(), None if g_Y is None else g_Y.contiguous())
+        return g_h, g_Hv, None, None, g_w2, g_b2, g_sw, g_sb
+
+
+def resnet_tail(h: Tensor, Hv: Optional[Tensor], inv: Optional[Tensor], P: int, w2: Tensor, b2: Tensor, sw: Tensor, sb: Tensor):
+    """ReLU -> 1x1 convolution -> scaled tanh of the coupler ResNet (`networks.py:96-113,156-161`) on the primal
+    hidden activations h (B, C, HW) and the tangents Hv (B d, C, HW), at the positions ``inv`` selects:
+    y (B, O, P), Y (B, d, O, P)."""
+    return _ResnetTail.apply(h, Hv, inv, P, w2, b2, sw, sb)

@@ -315,6 +315,28 @@ int cmf_mlp_jvp_bwd(int B, int d, int nlin, const int* width, const float* x, co
                     const float* wpack, const float* save_T, const float* save_U, const float* g_st,
                     const float* g_ST, float* g_x, float* g_V, float* partial, float* gpack, cmf_stream_t stream);
 
+/* ---- tail of the image couplers' conditioner ------------------------------------------
+ * ReLU -> 1x1 convolution (C -> O) -> scaled tanh on the primal hidden activations h (B, C, HW) and, by the
+ * JVP rules, on the d tangent images Hv (B d, C, HW), evaluated at the P spatial positions the coupling
+ * layer uses (inv: position -> compact index or < 0; null = all positions, P == HW):
+ *   y (B, O, P) = sw * tanh(W2 relu(h) + b2) + sb,   Y (B, d, O, P) = (W2 (Hv * [h > 0])) * (1 - tanh^2) * sw.
+ * Replaces cmf/models/components/networks.py:156-161 (ReLU, 1x1 conv of get_resnet), :96-113
+ * (ScaledTanh2dModule and its jvp), jvp_layers.py:38-64, the `(1 - mask)` selection of acl.py:53-66, and
+ * their autograd.  The adjoint writes DENSE g_h (B, C, HW) / g_Hv (B d, C, HW) (zeros at unused positions) and
+ * g_params = [g_W2 (O, C) | g_b2 (O) | g_sw (O) | g_sb (O)]; partial: cmf_resnet_tail_partial_floats floats of
+ * scratch (no zeroing needed).  g_y may be null.  C <= 64, O <= 32.  Bitwise reproducible. */
+#define CMF_TAIL_MAX_C 64
+#define CMF_TAIL_MAX_OUT 32
+int cmf_resnet_tail_usable(int C, int O);
+long long cmf_resnet_tail_partial_floats(int B, int d, int HW, int P, int C, int O);
+int cmf_resnet_tail_fwd(int B, int d, int C, int HW, int P, int O, const float* h, const float* Hv,
+                        const int32_t* inv, const float* w2, const float* b2, const float* sw, const float* sb,
+                        float* y, float* Y, cmf_stream_t stream);
+int cmf_resnet_tail_bwd(int B, int d, int C, int HW, int P, int O, const float* h, const float* Hv,
+                        const int32_t* inv, const float* w2, const float* b2, const float* sw, const float* sb,
+                        const float* g_y, const float* g_Y, float* g_h, float* g_Hv, float* partial,
+                        float* g_params, cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

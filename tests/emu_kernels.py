@@ -313,6 +313,47 @@ def flat_stack_bwd(desc, z, params, g_G, g_x):
     return (torch.zeros_like(z) if gz is None else gz), (torch.zeros_like(params) if gp is None else gp)
 
 
+def resnet_tail_usable(x, C, num_out):
+    return x.dtype == torch.float32 and 1 <= C <= 64 and 1 <= num_out <= 32
+
+
+def _tail_eval(h, Hv, inv, P, w2, b2, sw, sb):
+    """`networks.py:96-113,156-161`, `jvp_layers.py:38-64` at the selected positions"""
+    B, C, HW = h.shape
+    if inv is not None:
+        sel = torch.nonzero(inv >= 0).flatten()
+        sel = sel[torch.argsort(inv[sel])]
+        assert sel.numel() == P
+        h = h.index_select(2, sel)
+        Hv = None if Hv is None else Hv.index_select(2, sel)
+    th = torch.tanh(torch.matmul(w2, torch.relu(h)) + b2.view(1, -1, 1))
+    y = sw.view(1, -1, 1) * th + sb.view(1, -1, 1)
+    Y = None
+    if Hv is not None:
+        d = Hv.shape[0] // B
+        Hm = Hv.view(B, d, C, -1) * (h > 0).to(h.dtype).unsqueeze(1)
+        Y = torch.matmul(w2, Hm) * ((1 - th * th) * sw.view(1, -1, 1)).unsqueeze(1)
+    return y, Y
+
+
+def resnet_tail_fwd(h, Hv, inv, P, w2, b2, sw, sb):
+    y, Y = _tail_eval(h, Hv, inv, P, w2, b2, sw, sb)
+    return y.detach(), (None if Y is None else Y.detach())
+
+
+def resnet_tail_bwd(h, Hv, inv, P, w2, b2, sw, sb, g_y, g_Y):
+    with torch.enable_grad():
+        ins = [t.detach().clone().requires_grad_(True) for t in (h, w2, b2, sw, sb)] + ([Hv.detach().clone().requires_grad_(True)] if Hv is not None else [])
+        y, Y = _tail_eval(ins[0], ins[5] if Hv is not None else None, inv, P, *ins[1:5])
+        loss = (0 if g_y is None else (y * g_y).sum()) + (0 if (Y is None or g_Y is None) else (Y * g_Y).sum())
+        if not torch.is_tensor(loss):
+            gr = [None] * len(ins)
+        else:
+            gr = list(torch.autograd.grad(loss, ins, allow_unused=True))
+    gr = [torch.zeros_like(t) if g is None else g for g, t in zip(gr, ins)]
+    return gr[0], (gr[5] if Hv is not None else None), gr[1], gr[2], gr[3], gr[4]
+
+
 def mlp_usable(widths, d, x):
     return x.dim() == 2 and x.dtype == torch.float32 and len(widths) - 1 <= 8 and max(widths) <= 128 and 0 <= d < 128
 
@@ -369,7 +410,7 @@ def mlp_jvp_bwd(x, V, wpack, widths, saved, g_st, g_ST):
     return g_x, g_V, gr[:n], gr[n:]
 
 
-ALL = ["mlp_usable", "mlp_pack", "mlp_jvp_fwd", "mlp_jvp_bwd", "flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
+ALL = ["resnet_tail_usable", "resnet_tail_fwd", "resnet_tail_bwd", "mlp_usable", "mlp_pack", "mlp_jvp_fwd", "mlp_jvp_bwd", "flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
        "rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

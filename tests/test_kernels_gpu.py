@@ -421,3 +421,83 @@ def test_mlp_rejects_what_it_cannot_hold():
     wpack, widths = K.mlp_pack([torch.zeros(8, 3, device=DEV)], [torch.zeros(8, device=DEV)])
     with pytest.raises(CmfB200Error):
         K.mlp_jvp_fwd(torch.zeros(4, 5, device=DEV), None, wpack, widths, save=False)     # wrong input width
+
+
+# ------------------------------------------------------------------------------------------------
+# tail of the image couplers' conditioner (cmf_resnet_tail_fwd / _bwd)
+# ------------------------------------------------------------------------------------------------
+TAIL_SHAPES = [  # B, d, C, HW, selection ("all" | "checker" | "third"), O
+    (3, 5, 64, 196, "checker", 2), (2, 4, 8, 64, "all", 2), (2, 0, 64, 49, "third", 6), (1, 3, 64, 130, "all", 12),
+    (2, 2, 20, 33, "checker", 24), (4, 64, 64, 784, "checker", 2), (2, 3, 64, 256, "all", 4), (1, 0, 5, 1, "all", 1),
+]
+
+
+@pytest.mark.parametrize("B,d,C,HW,sel,O", TAIL_SHAPES)
+def test_resnet_tail_fwd_bwd(B, d, C, HW, sel, O):
+    """ReLU -> 1x1 conv -> scaled tanh with its JVP at the selected positions (`networks.py:96-113,156-161`,
+    `jvp_layers.py:38-64`) against fp64: outputs, dense hidden gradients, every parameter gradient."""
+    import cmf_b200.kernels as K
+    g = torch.Generator().manual_seed(B + d + C + HW + O)
+    r = lambda *s: torch.rand(*s, generator=g, dtype=torch.float64) * 2 - 1
+    keep = {"all": torch.ones(HW, dtype=torch.bool), "checker": torch.arange(HW) % 2 == 0, "third": torch.arange(HW) % 3 == 1}[sel]
+    P = int(keep.sum())
+    inv = None
+    if sel != "all":
+        inv = torch.full((HW,), -1, dtype=torch.int32)
+        inv[keep] = torch.arange(P, dtype=torch.int32)
+    h, Hv = r(B, C, HW), (r(B * d, C, HW) if d else None)
+    w2, b2, sw, sb = r(O, C) * (1.5 / C ** 0.5), r(O) * 0.3, r(O) + 1.5, r(O)
+    g_y, g_Y = r(B, O, P), (r(B, d, O, P) if d else None)
+    f = lambda t: None if t is None else t.float().to(DEV)
+    dinv = None if inv is None else inv.to(DEV)
+    assert K.resnet_tail_usable(f(h), C, O)
+    y, Y = K.resnet_tail_fwd(f(h), f(Hv), dinv, P, f(w2), f(b2), f(sw), f(sb))
+    ry, rY = E.resnet_tail_fwd(h, Hv, inv, P, w2, b2, sw, sb)
+    _close(y, ry, what="y")
+    if d:
+        _close(Y, rY, what="Y")
+    out = K.resnet_tail_bwd(f(h), f(Hv), dinv, P, f(w2), f(b2), f(sw), f(sb), f(g_y), f(g_Y))
+    ref = E.resnet_tail_bwd(h, Hv, inv, P, w2, b2, sw, sb, g_y, g_Y)
+    for name, a, b in zip(("g_h", "g_Hv", "g_w2", "g_b2", "g_sw", "g_sb"), out, ref):
+        if b is not None:
+            _close(a, b, rtol=3e-5, what=name)
+    out2 = K.resnet_tail_bwd(f(h), f(Hv), dinv, P, f(w2), f(b2), f(sw), f(sb), f(g_y), f(g_Y))
+    assert all(torch.equal(a, b) for a, b in zip(out, out2) if a is not None)          # fixed reduction order
+
+
+def test_resnet_tail_in_the_conditioner():
+    """ScaledTanhResNet with the fused tail against the library tail, through autograd, compact and full outputs."""
+    from cmf_b200 import networks
+    torch.backends.cuda.matmul.allow_tf32 = False          # the library side of the comparison in plain FP32
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(0)
+    net = networks.ScaledTanhResNet(2, [64, 64], 4).to(DEV)
+    with torch.no_grad():
+        net.weights.add_(0.3 * torch.randn_like(net.weights)); net.bias.add_(0.3 * torch.randn_like(net.bias))
+    B, d, H, W = 3, 5, 14, 14
+    x = torch.randn(B, 2, H, W, device=DEV, requires_grad=True)
+    V = torch.randn(B, d, 2, H, W, device=DEV, requires_grad=True)
+    keep = (torch.arange(H * W) // W + torch.arange(H * W) % W) % 2 == 0
+    idx = torch.nonzero(keep).flatten()
+    inv = torch.full((H * W,), -1, dtype=torch.int32); inv[idx] = torch.arange(idx.numel(), dtype=torch.int32)
+    pos = (idx.int().to(DEV), inv.to(DEV), idx.to(DEV))
+    for p in (None, pos):
+        res = []
+        for fused in (True, False):
+            networks._TAIL_FUSED = fused
+            try:
+                for t in (x, V, *net.parameters()):
+                    t.grad = None
+                y, Y = net.jvp_batched(x, V, p)
+                gen = torch.Generator(device=DEV).manual_seed(1)
+                ((y * torch.randn(y.shape, device=DEV, generator=gen)).sum() + (Y * torch.randn(Y.shape, device=DEV, generator=gen)).sum()).backward()
+                res.append((y.detach(), Y.detach(), x.grad.clone(), V.grad.clone(), [q.grad.clone() for q in net.parameters()]))
+                y1 = net(x.detach()) if p is None else net.forward_compact(x.detach(), p)
+                _close(y1, y.detach(), what="primal-only entry")
+            finally:
+                networks._TAIL_FUSED = True
+        (y1, Y1, gx1, gV1, gp1), (y0, Y0, gx0, gV0, gp0) = res
+        _close(y1, y0, what="y"); _close(Y1, Y0, what="Y")
+        _close(gx1, gx0, rtol=1e-4, what="g_x"); _close(gV1, gV0, rtol=1e-4, what="g_V")
+        for a, b in zip(gp1, gp0):
+            _close(a, b, rtol=1e-4, atol=1e-6 + 1e-5 * float(b.abs().max()), what="g_param")
