@@ -459,13 +459,16 @@ OTHER_CONFIGS = [
      dict(g_ij_loss=True, latent_dimension=6)),
     ("hepmass-shape D=21 d=10 (configs[2] stand-in)", "hepmass", (21,), 750, dict(g_ij_loss=True, latent_dimension=10)),
     ("CIFAR-shape 3x32x32 d=64 (configs[4])", "cifar10", (3, 32, 32), 48, dict(g_ij_loss=True, latent_dimension=64)),
+    # the image configs' default log-det method (config/images.py:148): Hutchinson + CG surrogate, m = 1 probe
+    ("MNIST-shape 1x28x28 d=64, hutch_with_cg m=1 (images.py default method)", "mnist", (1, 28, 28), 50,
+     dict(g_ij_loss=False, latent_dimension=64, log_jacobian_method="hutch_with_cg", hutchinson_samples=1)),
 ]
 
 
 def run_other_configs(dev, rank, world, barrier):
     """ms/step and whole-job samples/s of each shape: loss + backward + gradient all-reduce on a
     batch resident in HBM, every rank its own shard (weak scaling), max over ranks.  The flat shapes
-    are launch-bound, so they run as one CUDA graph (cmf_b200.graphed); the image shape runs eagerly."""
+    run as one CUDA graph (cmf_b200.graphed) like the headline step; hutch_with_cg (host-side CG loop) runs eagerly."""
     import torch.distributed as dist
     from cmf_b200.config import get_config, get_schema
     from cmf_b200.factory import get_density
@@ -475,7 +478,8 @@ def run_other_configs(dev, rank, world, barrier):
     out = []
     for name, ds, x_shape, B, ov in OTHER_CONFIGS:
         try:
-            cfg = {**get_config(ds), **ov, "log_jacobian_method": "cholesky", "likelihood_warmup": False}
+            cfg = {**get_config(ds), "log_jacobian_method": "cholesky", **ov, "likelihood_warmup": False}
+            hutch = cfg["log_jacobian_method"] != "cholesky"
             torch.manual_seed(0)
             density = get_density(get_schema(cfg), x_shape)
             with torch.no_grad():
@@ -496,7 +500,8 @@ def run_other_configs(dev, rank, world, barrier):
                     x = x / x.norm(dim=1, keepdim=True)
                 x = x.to(dev)
                 inner = density.module
-            graphed = None if image else GraphedTrainStep(inner, tm, bucket)
+            # hutch_with_cg draws its probes and runs a host-side CG loop: eager
+            graphed = None if hutch else GraphedTrainStep(inner, tm, bucket, warmup_iters=1 if image else 3)
 
             def step():
                 if graphed is not None:
@@ -520,7 +525,7 @@ def run_other_configs(dev, rank, world, barrier):
                 dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             ms = float(ms)
             out.append({"workload": name, "per_gpu_batch": B, "ms_per_step": ms, "samples_per_s": world * B / (ms * 1e-3),
-                        "timing": "eager" if image else "cuda-graph replay",
+                        "timing": "eager" if graphed is None else "cuda-graph replay",
                         "eager_fallbacks": 0 if graphed is None else graphed.eager_fallbacks})
             del density, bucket, graphed, x
             torch.cuda.empty_cache()
