@@ -45,6 +45,11 @@ SIGNATURES = {
     "cmf_flat_stack_fwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_flat_stack_bwd_partials": (_i, [_i]),
     "cmf_flat_stack_bwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_convin_usable": (_i, [_i, _i, _i, _i]),
+    "cmf_convin_wgrad_partials": (_i, [_i, _i, _i]),
+    "cmf_convin_fwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "cmf_convin_dgrad": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "cmf_convin_wgrad": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_resnet_tail_usable": (_i, [_i, _i]),
     "cmf_resnet_tail_partial_floats": (_ll, [_i, _i, _i, _i, _i, _i]),
     "cmf_resnet_tail_fwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -584,3 +584,47 @@ def resnet_tail_bwd(h: Tensor, Hv: Optional[Tensor], inv: Optional[Tensor], P: i
                    "cmf_resnet_tail_bwd")
     n = O * C
     return g_h, g_Hv, gp[:n].view(O, C), gp[n:n + O], gp[n + O:n + 2 * O], gp[n + 2 * O:]
+
+
+# ------------------------------------------------------------------------------------------------
+# first convolution of the image couplers' conditioner (C_in -> 64, 3x3, padding 1, no bias)
+# ------------------------------------------------------------------------------------------------
+def convin_usable(x: Tensor, weight: Tensor) -> bool:
+    return (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and weight.dim() == 4 and tuple(weight.shape[2:]) == (3, 3)
+            and weight.shape[1] == x.shape[1] and x.shape[0] <= 65535
+            and bool(_lib.load().cmf_convin_usable(int(weight.shape[1]), int(weight.shape[0]), int(x.shape[2]), int(x.shape[3]))))
+
+
+def convin_fwd(x: Tensor, weight: Tensor) -> Tensor:
+    lib = _lib.load()
+    x, weight = _req(x, "x"), _req(weight, "weight")
+    N, Cin, H, W = x.shape
+    y = torch.empty(N, weight.shape[0], H, W, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_convin_fwd(N, Cin, H, W, _ptr(x), _ptr(weight), _ptr(y), _stream()), "cmf_convin_fwd")
+    return y
+
+
+def convin_dgrad(g_y: Tensor, weight: Tensor) -> Tensor:
+    lib = _lib.load()
+    g_y, weight = _req(g_y, "g_y"), _req(weight, "weight")
+    N, _, H, W = g_y.shape
+    Cin = weight.shape[1]
+    g_x = torch.empty(N, Cin, H, W, dtype=torch.float32, device=g_y.device)
+    with torch.cuda.device(g_y.device):
+        _lib.check(lib.cmf_convin_dgrad(N, Cin, H, W, _ptr(g_y), _ptr(weight), _ptr(g_x), _stream()), "cmf_convin_dgrad")
+    return g_x
+
+
+def convin_wgrad(x: Tensor, g_y: Tensor) -> Tensor:
+    """-> g_w (64, C_in, 3, 3): per-block partials reduced in block order"""
+    lib = _lib.load()
+    x, g_y = _req(x, "x"), _req(g_y, "g_y")
+    N, Cin, H, W = x.shape
+    Co = g_y.shape[1]
+    nparts = lib.cmf_convin_wgrad_partials(N, H, W)
+    partial = torch.empty(max(nparts, 1) * Co * Cin * 9, dtype=torch.float32, device=x.device)
+    g_w = torch.empty(Co, Cin, 3, 3, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_convin_wgrad(N, Cin, H, W, _ptr(x), _ptr(g_y), _ptr(partial), _ptr(g_w), _stream()), "cmf_convin_wgrad")
+    return g_w

@@ -32,6 +32,8 @@ _BWD_DRAIN = int(os.environ.get("CMF_BWD_DRAIN", "2"))
 _FWD_DRAIN = int(os.environ.get("CMF_FWD_DRAIN", "1"))
 
 
+# CMF_CONVIN=cudnn keeps the first (C_in -> 64) convolution of the image couplers on F.conv2d
+_CONVIN_OWN = os.environ.get("CMF_CONVIN", "own") != "cudnn"
 # CMF_TAIL=torch keeps the ReLU -> 1x1 conv -> scaled tanh tail of the image couplers on library ops
 _TAIL_FUSED = os.environ.get("CMF_TAIL", "fused") != "torch"
 # CMF_MLP=torch keeps the tanh-MLP conditioners of the flat couplers on F.linear + elementwise ops
@@ -360,9 +362,26 @@ class ScaledTanhResNet(nn.Module):
         self.weights = nn.Parameter(torch.ones(num_out, 1, 1))
         self.bias = nn.Parameter(torch.zeros(num_out, 1, 1))
 
+    def _convin_own(self, mod, x: Tensor) -> bool:
+        """the first convolution on the hand-written kernels (``ops.conv_in``)"""
+        from . import kernels
+        return (_CONVIN_OWN and library_convs.depth == 0 and isinstance(mod, nn.Conv2d) and mod.bias is None
+                and mod.padding == (1, 1) and mod.stride == (1, 1) and mod.dilation == (1, 1) and mod.groups == 1
+                and kernels.convin_usable(x, mod.weight))
+
+    def _body(self, x: Tensor) -> Tensor:
+        """everything before the last ReLU, on the primal alone"""
+        mods = list(self.module[:-2])
+        if mods and self._convin_own(mods[0], x):
+            from . import ops
+            x, mods = ops.conv_in(x, mods[0].weight), mods[1:]
+        for mod in mods:
+            x = mod(x)
+        return x
+
     def forward(self, x: Tensor) -> Tensor:
         if self._tail_fused(x):
-            return self._tail_apply(self.module[:-2](x), None, None)[0]
+            return self._tail_apply(self._body(x), None, None)[0]
         return self.weights * torch.tanh(self.module(x)) + self.bias
 
     # -- compact tail ------------------------------------------------------------------------
@@ -404,7 +423,7 @@ class ScaledTanhResNet(nn.Module):
     def forward_compact(self, x: Tensor, pos) -> Tensor:
         """x (B,C,H,W), pos = (idx int32 (P,), inv int32 (H*W,), pos int64 (P,)) -> y (B,O,P)."""
         if self._tail_fused(x):
-            return self._tail_apply(self.module[:-2](x), None, pos)[0]
+            return self._tail_apply(self._body(x), None, pos)[0]
         pos = pos[2]
         last = self._tail()
         h = self.module[:-2](x).flatten(2).index_select(2, pos)
@@ -429,6 +448,10 @@ class ScaledTanhResNet(nn.Module):
                     run.append(body[i])
                     i += 1
                 h, Hv = _residual_stack_jvp(run, h, Hv, d)
+            elif isinstance(mod, nn.Conv2d) and self._convin_own(mod, h) and Hv.shape[0] + h.shape[0] <= 65535:
+                from . import ops
+                both = ops.conv_in(torch.cat((Hv, h), 0), mod.weight)       # one launch for tangents + primal
+                Hv, h = both[: Hv.shape[0]], both[Hv.shape[0]:]
             elif isinstance(mod, nn.Conv2d):
                 Hv = F.conv2d(Hv, mod.weight, None, stride=mod.stride, padding=mod.padding)
                 h = mod(h)

@@ -437,3 +437,24 @@ def resnet_tail(h: Tensor, Hv: Optional[Tensor], inv: Optional[Tensor], P: int, 
     hidden activations h (B, C, HW) and the tangents Hv (B d, C, HW), at the positions ``inv`` selects:
     y (B, O, P), Y (B, d, O, P)."""
     return _ResnetTail.apply(h, Hv, inv, P, w2, b2, sw, sb)
+
+
+# ------------------------------------------------------------------ first convolution of the image couplers' conditioner (N1-i)
+class _ConvIn(Function):
+    @staticmethod
+    def forward(ctx, x, weight):
+        ctx.save_for_backward(x, weight)
+        return kernels.convin_fwd(x, weight)
+
+    @staticmethod
+    def backward(ctx, g_y):
+        x, weight = ctx.saved_tensors
+        g_y = g_y.contiguous()
+        g_x = kernels.convin_dgrad(g_y, weight) if ctx.needs_input_grad[0] else None
+        g_w = kernels.convin_wgrad(x, g_y) if ctx.needs_input_grad[1] else None
+        return g_x, g_w
+
+
+def conv_in(x: Tensor, weight: Tensor) -> Tensor:
+    """3x3 convolution C_in -> 64, padding 1, no bias (`networks.py:131-139`): x (N, C_in, H, W) -> (N, 64, H, W)."""
+    return _ConvIn.apply(x, weight)

@@ -303,3 +303,71 @@ def test_activation_recompute_gives_identical_gradients():
     for a, b in zip(*results):
         assert torch.equal(a, b)
     assert saved_bytes[1] < 0.4 * saved_bytes[0], saved_bytes
+
+
+# ------------------------------------------------------------------------------------------------
+# first convolution of the conditioner (cmf_convin_fwd / _dgrad / _wgrad)
+# ------------------------------------------------------------------------------------------------
+CONVIN_SHAPES = [  # N, C_in, H, W
+    (3, 1, 28, 28), (5, 2, 14, 14), (2, 3, 32, 32), (2, 4, 16, 16), (7, 1, 8, 8), (1, 2, 7, 5), (4, 3, 12, 64), (130, 1, 28, 28),
+]
+
+
+@pytest.mark.parametrize("N,Cin,H,W", CONVIN_SHAPES)
+def test_convin_fwd_dgrad_wgrad(N, Cin, H, W):
+    """C_in -> 64 3x3 convolution (`networks.py:131-139`) against F.conv2d in fp64: output, data gradient, weight gradient."""
+    import torch.nn.functional as F
+    import cmf_b200.kernels as K
+    g = torch.Generator().manual_seed(N + Cin + H + W)
+    x = torch.randn(N, Cin, H, W, generator=g, dtype=torch.float64)
+    w = torch.randn(64, Cin, 3, 3, generator=g, dtype=torch.float64) / (3 * Cin ** 0.5)
+    gy = torch.randn(N, 64, H, W, generator=g, dtype=torch.float64)
+    xr, wr = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    yr = F.conv2d(xr, wr, padding=1)
+    yr.backward(gy)
+    xd, wd, gyd = x.float().cuda(), w.float().cuda(), gy.float().cuda()
+    assert K.convin_usable(xd, wd)
+    rel = lambda a, b: float((a.double().cpu() - b).abs().max() / b.abs().max())
+    assert rel(K.convin_fwd(xd, wd), yr.detach()) < 2e-6
+    assert rel(K.convin_dgrad(gyd, wd), xr.grad) < 3e-6
+    g_w = K.convin_wgrad(xd, gyd)
+    assert rel(g_w, wr.grad) < 1e-5
+    assert torch.equal(g_w, K.convin_wgrad(xd, gyd))              # fixed reduction order
+
+
+def test_convin_at_the_step_size_and_in_the_conditioner():
+    """N = 3250 images of 28x28 (the step's joint batch) against cuDNN FP32, and ScaledTanhResNet with / without the own
+    first convolution through autograd."""
+    import torch.nn.functional as F
+    import cmf_b200.kernels as K
+    from cmf_b200 import networks
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    torch.manual_seed(0)
+    x = torch.randn(3250, 1, 28, 28, device="cuda")
+    w = torch.randn(64, 1, 3, 3, device="cuda") / 3
+    gy = torch.randn(3250, 64, 28, 28, device="cuda")
+    rel = lambda a, b: float((a.double() - b.double()).abs().max() / b.double().abs().max())
+    assert rel(K.convin_fwd(x, w), F.conv2d(x, w, padding=1)) < 5e-6
+    assert rel(K.convin_dgrad(gy, w), torch.nn.grad.conv2d_input(x.shape, w, gy, padding=1)) < 1e-5
+    ref_w = torch.nn.grad.conv2d_weight(x.double(), w.shape, gy.double(), padding=1)
+    assert rel(K.convin_wgrad(x, gy), ref_w) < 2e-5
+    net = networks.ScaledTanhResNet(2, [64, 64], 4).cuda()
+    xs = torch.randn(3, 2, 14, 14, device="cuda", requires_grad=True)
+    V = torch.randn(3, 5, 2, 14, 14, device="cuda", requires_grad=True)
+    res = []
+    for own in (True, False):
+        networks._CONVIN_OWN = own
+        try:
+            for t in (xs, V, *net.parameters()):
+                t.grad = None
+            y, Y = net.jvp_batched(xs, V)
+            gen = torch.Generator(device="cuda").manual_seed(1)
+            ((y * torch.randn(y.shape, device="cuda", generator=gen)).sum() + (Y * torch.randn(Y.shape, device="cuda", generator=gen)).sum()).backward()
+            res.append((y.detach(), Y.detach(), xs.grad.clone(), V.grad.clone(), [q.grad.clone() for q in net.parameters()], net(xs.detach())))
+        finally:
+            networks._CONVIN_OWN = True
+    for a, b in zip(res[0][:4] + (res[0][5],), res[1][:4] + (res[1][5],)):
+        assert rel(a, b) < 1e-4
+    for a, b in zip(res[0][4], res[1][4]):
+        assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max()) + 1e-6
