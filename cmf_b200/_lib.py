@@ -45,6 +45,8 @@ SIGNATURES = {
     "cmf_flat_stack_fwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_flat_stack_bwd_partials": (_i, [_i]),
     "cmf_flat_stack_bwd": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "cmf_channel_sum_splits": (_i, [_i, _i]),
+    "cmf_channel_sum": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     "cmf_convin_usable": (_i, [_i, _i, _i, _i]),
     "cmf_convin_wgrad_partials": (_i, [_i, _i, _i]),
     "cmf_convin_fwd": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp]),

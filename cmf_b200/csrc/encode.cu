@@ -190,3 +190,64 @@ extern "C" int cmf_sumsq_diff_bwd(int B, int n, const float* a, const float* c, 
     CMF_CHECK_LAUNCH();
     return 0;
 }
+
+// ---- per-channel sum over images and pixels: the bias gradient of a convolution -------------------------
+// out[c] = sum_{n, p} x[n, c, p]   (autograd's `g_y.sum(dim = (0, 2, 3))` behind every biased Conv2d of
+// cmf/models/components/networks.py:35-94; a generic torch reduction, 11 us per call in the step).
+// One block per channel, fixed summation order (thread-strided partial sums, then a tree): reproducible.
+namespace cmf {
+namespace {
+// stage 1: block (c, s) sums images n = s, s + S, ... of channel c; stage 2: the S partials in order
+__global__ void __launch_bounds__(256) channel_sum_kernel(int N, int C, int HW, const float* __restrict__ x, float* __restrict__ partial) {
+    __shared__ float r[256];
+    const int c = blockIdx.x, S = gridDim.y, t = threadIdx.x;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    const int hw4 = (HW % 4 == 0) ? HW / 4 : 0;
+    for (int n = blockIdx.y; n < N; n += S) {
+        const float* row = x + ((long long)n * C + c) * HW;
+        if (hw4) {
+            const float4* row4 = reinterpret_cast<const float4*>(row);
+            for (int i = t; i < hw4; i += 256) {
+                const float4 v = __ldg(row4 + i);
+                s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+            }
+        } else {
+            for (int i = t; i < HW; i += 256) s0 += __ldg(row + i);
+        }
+    }
+    r[t] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if (t < w) r[t] += r[t + w];
+        __syncthreads();
+    }
+    if (t == 0) partial[c * S + blockIdx.y] = r[0];
+}
+__global__ void channel_sum_final_kernel(int C, int S, const float* __restrict__ partial, float* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float s = 0.f;
+    for (int i = 0; i < S; ++i) s += partial[c * S + i];
+    out[c] = s;
+}
+}  // namespace
+}  // namespace cmf
+
+extern "C" int cmf_channel_sum_splits(int N, int C) {
+    if (N <= 0 || C <= 0) return 1;
+    int s = (4 * cmf::kNumSMs + C - 1) / C;          // ~4 blocks per SM
+    return s < 1 ? 1 : (s > N ? N : s);
+}
+
+extern "C" int cmf_channel_sum(int N, int C, int HW, const float* x, float* partial, float* out, cmf_stream_t stream) {
+    using namespace cmf;
+    CMF_REQUIRE(N >= 0 && C >= 1 && C <= 65535 && HW >= 1 && out && partial, "channel_sum: N = %d, C = %d, HW = %d", N, C, HW);
+    CMF_REQUIRE(N == 0 || x, "channel_sum: null pointer");
+    CMF_REQUIRE(N == 0 || HW % 4 != 0 || aligned16(x), "channel_sum: x must be 16-byte aligned");
+    const int S = cmf_channel_sum_splits(N, C);
+    channel_sum_kernel<<<dim3(C, S), 256, 0, (cudaStream_t)stream>>>(N, C, HW, x, partial);
+    CMF_CHECK_LAUNCH();
+    channel_sum_final_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(C, S, partial, out);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}

@@ -628,3 +628,16 @@ def convin_wgrad(x: Tensor, g_y: Tensor) -> Tensor:
     with torch.cuda.device(x.device):
         _lib.check(lib.cmf_convin_wgrad(N, Cin, H, W, _ptr(x), _ptr(g_y), _ptr(partial), _ptr(g_w), _stream()), "cmf_convin_wgrad")
     return g_w
+
+
+def channel_sum(x: Tensor) -> Tensor:
+    """x (N, C, ...) -> (C,): sum over the batch and every trailing dimension (the bias gradient of a convolution)"""
+    lib = _lib.load()
+    x = _req(x, "x")
+    N, C = x.shape[0], x.shape[1]
+    HW = x[0, 0].numel() if N else 1
+    buf = torch.empty(C * (1 + lib.cmf_channel_sum_splits(N, C)), dtype=torch.float32, device=x.device)
+    out, partial = buf[:C], buf[C:]
+    with torch.cuda.device(x.device):
+        _lib.check(lib.cmf_channel_sum(N, C, HW, _ptr(x), _ptr(partial), _ptr(out), _stream()), "cmf_channel_sum")
+    return out

@@ -312,11 +312,11 @@ class _ResidualStackJoint(torch.autograd.Function):
         for k in reversed(range(K)):
             A0, A1 = saved[2 * k], saved[2 * k + 1]
             grads[4 * k + 2] = kernels.conv3x3_c64_wgrad(A1, g)
-            grads[4 * k + 3] = g[Nt:].sum(dim=(0, 2, 3))
+            grads[4 * k + 3] = kernels.channel_sum(g[Nt:])
             gC1 = kernels.conv3x3_c64(g, kernels.conv3x3_c64_prep(w2s[k], True), None, mask_src=hbits[k], mask_div=d,
                                       mask_first=True, drain=_BWD_DRAIN, tail=Nt)
             grads[4 * k + 0] = kernels.conv3x3_c64_wgrad(A0, gC1)
-            grads[4 * k + 1] = gC1[Nt:].sum(dim=(0, 2, 3))
+            grads[4 * k + 1] = kernels.channel_sum(gC1[Nt:])
             g = kernels.conv3x3_c64(gC1, kernels.conv3x3_c64_prep(w1s[k], True), None, mask_src=xbits[k], mask_div=d,
                                     mask_first=True, res=g, drain=_BWD_DRAIN, tail=Nt)
         return (g[Nt:], g[:Nt], None, *grads)

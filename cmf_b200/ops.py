@@ -291,7 +291,7 @@ class _Conv3x3C64(Function):
         elif need_w:
             g_w = torch.ops.aten.convolution_backward(g_y, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
                                                       (False, True, False))[1]
-        g_b = g_y.sum(dim=(0, 2, 3)) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        g_b = kernels.channel_sum(g_y) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
         return g_x, g_w, g_b, None
 
 

@@ -352,6 +352,14 @@ int cmf_convin_dgrad(int N, int Cin, int H, int W, const float* g_y, const float
 int cmf_convin_wgrad(int N, int Cin, int H, int W, const float* x, const float* g_y, float* partial, float* g_w,
                      cmf_stream_t stream);
 
+/* ---- bias gradient of a convolution ----------------------------------------------------------------------
+ * out[c] = sum over n, p of x[n, c, p]; x (N, C, HW) contiguous (a batch slice of a larger tensor is fine).
+ * Replaces autograd's g_y.sum(dim = (0, 2, 3)) behind every biased Conv2d of the coupler ResNet
+ * (cmf/models/components/networks.py:35-94 at cmf/trainer.py:216).  partial: C x cmf_channel_sum_splits(N, C)
+ * floats of scratch (no zeroing needed).  Fixed summation order. */
+int cmf_channel_sum_splits(int N, int C);
+int cmf_channel_sum(int N, int C, int HW, const float* x, float* partial, float* out, cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

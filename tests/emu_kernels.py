@@ -313,6 +313,10 @@ def flat_stack_bwd(desc, z, params, g_G, g_x):
     return (torch.zeros_like(z) if gz is None else gz), (torch.zeros_like(params) if gp is None else gp)
 
 
+def channel_sum(x):
+    return x.sum(dim=[0] + list(range(2, x.dim())))
+
+
 def convin_usable(x, weight):
     return (x.dtype == torch.float32 and x.dim() == 4 and weight.dim() == 4 and tuple(weight.shape[2:]) == (3, 3)
             and weight.shape[0] == 64 and weight.shape[1] == x.shape[1] <= 4 and x.shape[3] <= 64)
@@ -427,7 +431,7 @@ def mlp_jvp_bwd(x, V, wpack, widths, saved, g_st, g_ST):
     return g_x, g_V, gr[:n], gr[n:]
 
 
-ALL = ["convin_usable", "convin_fwd", "convin_dgrad", "convin_wgrad", "resnet_tail_usable", "resnet_tail_fwd", "resnet_tail_bwd", "mlp_usable", "mlp_pack", "mlp_jvp_fwd", "mlp_jvp_bwd", "flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
+ALL = ["channel_sum", "convin_usable", "convin_fwd", "convin_dgrad", "convin_wgrad", "resnet_tail_usable", "resnet_tail_fwd", "resnet_tail_bwd", "mlp_usable", "mlp_pack", "mlp_jvp_fwd", "mlp_jvp_bwd", "flat_stack_usable", "flat_stack_fwd", "flat_stack_bwd", "preproc_logit_fwd", "coupling_x_to_z_fwd", "coupling_x_to_z_bwd", "sumsq_diff_fwd", "sumsq_diff_bwd",
        "rqs_coupling_jvp_fwd", "rqs_coupling_jvp_bwd", "coupling_jvp_fwd", "coupling_jvp_bwd", "gather_rows", "gram_fwd", "gram_fwd2", "gram_bwd",
        "chol_logdet_fwd", "chol_logdet_bwd", "conv3x3_c64_usable", "conv3x3_c64_prep", "conv3x3_c64", "relu_mask_pack",
        "conv3x3_c64_wgrad_usable", "conv3x3_c64_wgrad"]

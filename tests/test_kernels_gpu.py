@@ -501,3 +501,16 @@ def test_resnet_tail_in_the_conditioner():
         _close(gx1, gx0, rtol=1e-4, what="g_x"); _close(gV1, gV0, rtol=1e-4, what="g_V")
         for a, b in zip(gp1, gp0):
             _close(a, b, rtol=1e-4, atol=1e-6 + 1e-5 * float(b.abs().max()), what="g_param")
+
+
+@pytest.mark.parametrize("shape", [(50, 64, 28, 28), (3, 64, 14, 14), (7, 5, 3, 3), (0, 4, 2, 2), (2, 1, 1, 1), (9, 64, 7, 5)])
+def test_channel_sum(shape):
+    """bias gradient of a convolution (sum over images and pixels), incl. a batch slice of a larger tensor"""
+    import cmf_b200.kernels as K
+    x = _rand(shape[0] + 2, *shape[1:], seed=3)
+    xd = x.float().to(DEV)
+    out = K.channel_sum(xd[2:])
+    ref = x[2:].sum(dim=(0, 2, 3))
+    err = float((out.double().cpu() - ref).abs().max())
+    assert err <= 1e-6 * (float(x[2:].abs().sum(dim=(0, 2, 3)).max()) + 1e-30) + 1e-12
+    assert torch.equal(out, K.channel_sum(xd[2:]))
