@@ -99,11 +99,23 @@ __global__ void __launch_bounds__(kTailThreads) tail_fwd_kernel(TailParams P) {
         float acc[OMAX];
 #pragma unroll
         for (int o = 0; o < OMAX; ++o) acc[o] = 0.f;
-#pragma unroll 16
-        for (int c = 0; c < P.C; ++c) {
-            const float v = ((bits >> c) & 1ull) ? __ldcs(src + (long long)c * P.HW) : 0.f;
+        if (P.C == kTailC) {
+            // all 64 loads of the tangent image in flight before the first use (the kernel is bound by memory
+            // latency: ncu showed 1.15 TB/s with 16 loads in flight per thread)
+            float v[kTailC];
 #pragma unroll
-            for (int o = 0; o < OMAX; ++o) acc[o] = fmaf(w_s[c * OMAX + o], v, acc[o]);
+            for (int c = 0; c < kTailC; ++c) v[c] = ((bits >> c) & 1ull) ? __ldcs(src + (long long)c * P.HW) : 0.f;
+#pragma unroll
+            for (int c = 0; c < kTailC; ++c)
+#pragma unroll
+                for (int o = 0; o < OMAX; ++o) acc[o] = fmaf(w_s[c * OMAX + o], v[c], acc[o]);
+        } else {
+#pragma unroll 8
+            for (int c = 0; c < P.C; ++c) {
+                const float v = ((bits >> c) & 1ull) ? __ldcs(src + (long long)c * P.HW) : 0.f;
+#pragma unroll
+                for (int o = 0; o < OMAX; ++o) acc[o] = fmaf(w_s[c * OMAX + o], v, acc[o]);
+            }
         }
         float* dst = P.Y + ((long long)(b * P.d + k) * P.O) * P.P + p;
 #pragma unroll
@@ -171,18 +183,37 @@ __global__ void __launch_bounds__(kTailThreads) tail_bwd_tangent_kernel(TailPara
         }
         const float* src = P.Hv + n * P.C * P.HW + q;
         float* dst = P.g_Hv + n * P.C * P.HW + q;
-#pragma unroll 8
-        for (int c = 0; c < P.C; ++c) {
-            const bool live = on && ((bits >> c) & 1ull);
-            const float v = live ? __ldcs(src + (long long)c * P.HW) : 0.f;
-            float g = 0.f;
+        if (P.C == kTailC) {
+            // every load of the tangent image in flight before the first use (memory-latency bound otherwise)
+            float v[kTailC];
 #pragma unroll
-            for (int o = 0; o < OMAX; ++o) {
-                acc[o] = fmaf(w_s[c * OMAX + o], v, acc[o]);
-                g = fmaf(w_s[c * OMAX + o], gz[o], g);
+            for (int c = 0; c < kTailC; ++c) v[c] = (on && ((bits >> c) & 1ull)) ? __ldcs(src + (long long)c * P.HW) : 0.f;
+#pragma unroll
+            for (int c = 0; c < kTailC; ++c) {
+                const bool live = on && ((bits >> c) & 1ull);
+                float g = 0.f;
+#pragma unroll
+                for (int o = 0; o < OMAX; ++o) {
+                    acc[o] = fmaf(w_s[c * OMAX + o], v[c], acc[o]);
+                    g = fmaf(w_s[c * OMAX + o], gz[o], g);
+                }
+                v_s[c * kVPitch + t] = v[c];
+                if (inside) __stcs(dst + (long long)c * P.HW, live ? g : 0.f);
             }
-            v_s[c * kVPitch + t] = v;
-            if (inside) __stcs(dst + (long long)c * P.HW, live ? g : 0.f);
+        } else {
+#pragma unroll 8
+            for (int c = 0; c < P.C; ++c) {
+                const bool live = on && ((bits >> c) & 1ull);
+                const float v = live ? __ldcs(src + (long long)c * P.HW) : 0.f;
+                float g = 0.f;
+#pragma unroll
+                for (int o = 0; o < OMAX; ++o) {
+                    acc[o] = fmaf(w_s[c * OMAX + o], v, acc[o]);
+                    g = fmaf(w_s[c * OMAX + o], gz[o], g);
+                }
+                v_s[c * kVPitch + t] = v;
+                if (inside) __stcs(dst + (long long)c * P.HW, live ? g : 0.f);
+            }
         }
 #pragma unroll
         for (int o = 0; o < OMAX; ++o) gdy[o] = fmaf(gY[o], acc[o], gdy[o]);
