@@ -198,6 +198,10 @@ def conv_kernel_times(step, dev):
             return out
         return inner
 
+    # one plain step first: the graph-timed runs before this released their memory pools (empty_cache), and a
+    # cudaMalloc inside a launcher's output allocation would land inside the event bracket of that launch
+    step()
+    torch.cuda.synchronize()
     K.conv3x3_c64, K.conv3x3_c64_wgrad = wrap("conv3x3_tc_kernel", orig_f), wrap("conv3x3_wgrad_tc_kernel", orig_w)
     try:
         step()

@@ -1,7 +1,7 @@
 #!/bin/bash
 # plain run first (must exit 0), then the launch list of one (eager) step, then full captures of the two conv
 # kernels and the coupling adjoint
-R=${1:-r02}
+R=${1:-r02c}
 export PYTHONPATH=.
 set -x
 python bench.py --steps 5 --warmup 3 > gpurun_out/${R}_bench.json 2> gpurun_out/${R}_bench.err || exit 1
@@ -21,4 +21,9 @@ timeout 400 ncu --set full --clock-control none --import-source on -k regex:mlp_
     -o gpurun_out/${R}_mlp_fwd python scripts/one_mlp.py > gpurun_out/ncu5.log 2>&1
 timeout 400 ncu --set full --clock-control none --import-source on -k regex:mlp_bwd_kernel -s 1 -c 1 -f \
     -o gpurun_out/${R}_mlp_bwd python scripts/one_mlp.py > gpurun_out/ncu6.log 2>&1
+timeout 100 python scripts/one_tail.py || exit 1
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:tail_fwd_kernel -s 2 -c 1 -f \
+    -o gpurun_out/${R}_tail_fwd python scripts/one_tail.py > gpurun_out/ncu7.log 2>&1
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:tail_bwd_tangent -s 2 -c 1 -f \
+    -o gpurun_out/${R}_tail_bwd python scripts/one_tail.py > gpurun_out/ncu8.log 2>&1
 ls -la gpurun_out/ | tail -12
