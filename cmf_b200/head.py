@@ -25,6 +25,21 @@ Tensor = torch.Tensor
 
 # CMF_FLAT_STACK=0 keeps the small flat configs on the per-layer program (A/B measurements)
 _FLAT_STACK = os.environ.get("CMF_FLAT_STACK", "1") != "0"
+# CMF_CG_GRAPH=0: the J^T J product inside the CG loop of hutch_with_cg is launched eagerly instead of replayed
+_CG_GRAPH = os.environ.get("CMF_CG_GRAPH", "1") != "0"
+
+
+class _GraphSlot:
+    """holder of a captured CUDA graph that copy.deepcopy / pickling of the module leave behind (empty)"""
+
+    def __init__(self):
+        self.entry = None
+
+    def __deepcopy__(self, memo):
+        return _GraphSlot()
+
+    def __reduce__(self):
+        return (_GraphSlot, ())
 
 
 class FusedNonSquareHeadDensity(Density):
@@ -49,6 +64,8 @@ class FusedNonSquareHeadDensity(Density):
         self.log_jacobian_method = log_jacobian_method
         self._program: Optional[LayerProgram] = None
         self.last_cholesky_attempts = 1
+        self._cg_slot = _GraphSlot()   # entry: (key, graph, static latent, static vector, static result)
+        self.cg_graph_replays = 0
 
     # ------------------------------------------------------------------ program cache
     def _load_from_state_dict(self, *args, **kwargs):
@@ -231,6 +248,47 @@ class FusedNonSquareHeadDensity(Density):
                 return jtj(latent.detach())
         return jtj(latent)
 
+    def _cg_product(self, latent: Tensor):
+        """v -> J^T J v at ``latent`` for the CG loop (`non_square.py:241-247`: detached, no graph).  Every CG
+        iteration issues the same ~1000 small launches (conditioners on B m images): on a GPU they are captured
+        once into a CUDA graph (static latent / vector / result buffers; the parameters are read in place, so
+        the graph stays valid across optimizer steps) and replayed per iteration -- bit-identical kernels."""
+        eager = lambda v: self._jac_transpose_jac_vec(latent, v, create_graph=False)[0]
+        if not (_CG_GRAPH and latent.is_cuda) or torch.cuda.is_current_stream_capturing():
+            return eager
+        key = (tuple(latent.shape), latent.dtype, latent.device, self.training,
+               tuple(p.data_ptr() for p in self.parameters()))
+        if self._cg_slot.entry is None or self._cg_slot.entry[0] != key:
+            lat = latent.detach().clone()
+            vec = torch.zeros_like(lat)
+            try:
+                side = torch.cuda.Stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):             # warm-up off the capture stream (allocator, library plans)
+                    for _ in range(2):
+                        self._jac_transpose_jac_vec(lat, vec, create_graph=False)
+                torch.cuda.current_stream().wait_stream(side)
+                torch.cuda.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    out = self._jac_transpose_jac_vec(lat, vec, create_graph=False)[0]
+            except Exception:                              # capture is an optimisation: never a reason to fail the step
+                self._cg_slot.entry = (key, None, None, None, None)
+                torch.cuda.synchronize()
+                return eager
+            self._cg_slot.entry = (key, graph, lat, vec, out)
+        _, graph, lat, vec, out = self._cg_slot.entry
+        if graph is None:
+            return eager
+        lat.copy_(latent.detach())
+
+        def replay(v):
+            vec.copy_(v)
+            graph.replay()
+            self.cg_graph_replays += 1
+            return out.clone()
+        return replay
+
     def _approx_log_det_jac_and_reconstruction(self, latent: Tensor, hutchinson_samples: Optional[Tensor] = None):
         """`non_square.py:203-258`.  ``hutchinson_samples`` (B,d,m) may be injected for parity tests."""
         B, d = latent.shape
@@ -242,8 +300,10 @@ class FusedNonSquareHeadDensity(Density):
         def to_vec(t): return t.transpose(1, 2).reshape(B * m, d)
         def to_ten(v): return v.reshape(B, m, d).transpose(1, 2)
 
+        product = self._cg_product(repeated)
+
         def closure(t):
-            return to_ten(self._jac_transpose_jac_vec(repeated, to_vec(t), create_graph=False)[0])
+            return to_ten(product(to_vec(t)))
 
         inv = linear_cg_batched(closure, hutchinson_samples, max_iter=self.max_cg_iterations,
                                 tolerance=self.cg_tolerance).detach()

@@ -461,3 +461,35 @@ def test_cuda_graph_step_is_bit_identical_to_eager(name):
             assert torch.equal(loss_g, loss_e)
             assert torch.equal(bucket.flat, ref)
     assert step.eager_fallbacks == 0 and len(step._graphs) == 1
+
+
+def test_hutch_cg_product_graph_replay_is_bit_identical():
+    """The CG loop of hutch_with_cg replays its J^T J product as a CUDA graph: same kernels, same bits as eager
+    launches, loss and every parameter gradient; and the graph survives an in-place parameter update."""
+    import copy
+    import cmf_b200.head as H
+    g = load_golden("img8_hutch_d8")
+    results = []
+    for use_graph in (True, False):
+        H._CG_GRAPH = use_graph
+        try:
+            density = build_product(g, "cuda")
+            head, _ = find_head(strip_wrappers(density))
+            loss, grads = run_loss(g, density, "cuda")
+            if use_graph:
+                assert head.cg_graph_replays > 0, "the CG product was not replayed from a graph"
+                with torch.no_grad():
+                    for p in density.parameters():
+                        p.mul_(1.01)
+                n0 = head.cg_graph_replays
+                loss_b, _ = run_loss(g, density, "cuda")
+                assert head.cg_graph_replays > n0 and torch.isfinite(loss_b)
+                copy.deepcopy(density)                      # the captured graph must not get in the way
+            results.append((loss.detach().clone(), {k: v.clone() for k, v in grads.items()}))
+        finally:
+            H._CG_GRAPH = True
+    (l1, g1), (l0, g0) = results
+    assert torch.equal(l1, l0)                               # the whole CG solve enters the loss: bit-identical
+    assert set(g1) == set(g0)
+    for k in g0:                                             # (library weight gradients are not bitwise reproducible run to run)
+        assert_close(g1[k], g0[k], rtol=1e-5, atol=1e-7, what=k)
