@@ -23,10 +23,12 @@ namespace {
 
 constexpr int kCo = 64;
 constexpr int kThreads = 256;
-constexpr int kMaxCin = CMF_CONVIN_MAX_CIN;     // 4
+constexpr int kMaxCin = CMF_CONVIN_MAX_CIN;     // 16
+constexpr int kChunk = 4;                       // input channels per pass of the gradient kernels
 
 struct InParams {
     int N, Cin, H, W, R, nb;       // R rows per band, nb bands per image
+    int CinT, ci0;                 // channels of the whole tensor / first channel of this pass (data + weight gradient run in passes of <= 4)
     const float* x;                // (N, Cin, H, W)
     const float* w;                // (64, Cin, 3, 3)
     float* y;                      // (N, 64, H, W)
@@ -38,12 +40,12 @@ struct InParams {
 };
 
 // ------------------------------------------------------------------------------------------------ forward
-template <int CIN>
 __global__ void __launch_bounds__(kThreads) convin_fwd_kernel(InParams P) {
-    __shared__ __align__(16) float w_s[9 * CIN * kCo];          // [ci * 9 + tap][co]
-    for (int i = threadIdx.x; i < 9 * CIN * kCo; i += kThreads) {
+    extern __shared__ __align__(16) float w_s[];                // [ci * 9 + tap][co]
+    const int Cin = P.Cin;
+    for (int i = threadIdx.x; i < 9 * Cin * kCo; i += kThreads) {
         const int k = i / kCo, co = i - k * kCo;
-        w_s[i] = __ldg(P.w + co * CIN * 9 + k);
+        w_s[i] = __ldg(P.w + co * Cin * 9 + k);
     }
     __syncthreads();
     const int n = blockIdx.y, r0 = blockIdx.x * P.R;
@@ -55,9 +57,9 @@ __global__ void __launch_bounds__(kThreads) convin_fwd_kernel(InParams P) {
     float acc[kCo];
 #pragma unroll
     for (int co = 0; co < kCo; ++co) acc[co] = 0.f;
-    const float* xn = P.x + (long long)n * CIN * hw;
-#pragma unroll
-    for (int ci = 0; ci < CIN; ++ci)
+    const float* xn = P.x + (long long)n * Cin * hw;
+#pragma unroll 1
+    for (int ci = 0; ci < Cin; ++ci)
 #pragma unroll
         for (int tap = 0; tap < 9; ++tap) {
             const int rr = r + tap / 3 - 1, cc = c + tap % 3 - 1;
@@ -86,7 +88,7 @@ __global__ void __launch_bounds__(kThreads) convin_dgrad_kernel(InParams P) {
     float* z_s = dyn + kCo * kKp;                       // [k][(R + 2) * W]
     for (int i = threadIdx.x; i < kCo * kKp; i += kThreads) {
         const int co = i / kKp, k = i - co * kKp;
-        w_s[i] = k < kK ? __ldg(P.w + co * kK + k) : 0.f;
+        w_s[i] = k < kK ? __ldg(P.w + (co * P.CinT + P.ci0) * 9 + k) : 0.f;
     }
     __syncthreads();
     const int n = blockIdx.y, r0 = blockIdx.x * P.R;
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(kThreads) convin_dgrad_kernel(InParams P) {
     __syncthreads();
     if (t >= rows * P.W) return;
     const int lr = t / P.W, c = t % P.W;                // local row of the band; its z row is lr + 1
-    float* go = P.g_x + (long long)n * CIN * hw + (r0 + lr) * P.W + c;
+    float* go = P.g_x + ((long long)n * P.CinT + P.ci0) * hw + (r0 + lr) * P.W + c;
 #pragma unroll
     for (int ci = 0; ci < CIN; ++ci) {
         float s = 0.f;
@@ -179,7 +181,7 @@ __global__ void __launch_bounds__(kThreads) convin_wgrad_kernel(InParams P) {
                 }
             }
             float* xs = buf + gy_elems;
-            const float* xn = P.x + (long long)n * CIN * hw;
+            const float* xn = P.x + ((long long)n * P.CinT + P.ci0) * hw;
             for (int i = threadIdx.x; i < CIN * (rows + 2) * xw; i += kThreads) {
                 const int ci = i / ((rows + 2) * xw), rem = i - ci * (rows + 2) * xw;
                 const int rr = r0 - 1 + rem / xw, cc = rem % xw - 1;
@@ -245,19 +247,21 @@ __global__ void __launch_bounds__(kThreads) convin_wgrad_kernel(InParams P) {
     }
 }
 
-__global__ void convin_reduce_kernel(int nparts, int n, const float* __restrict__ partial, float* __restrict__ out) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// partial[b][co][ci of the pass][tap] summed over the blocks in order -> g_w[co][ci0 + ci][tap] of the full tensor
+__global__ void convin_reduce_kernel(int nparts, int cin, int cint, int ci0, const float* __restrict__ partial, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, n = kCo * cin * 9;
     if (i >= n) return;
     float s = 0.f;
     for (int b = 0; b < nparts; ++b) s += partial[(long long)b * n + i];
-    out[i] = s;
+    const int co = i / (cin * 9), rem = i - co * cin * 9;
+    out[(co * cint + ci0) * 9 + rem] = s;
 }
 
 int fill(InParams& P, const char* who, int N, int Cin, int H, int W) {
     CMF_REQUIRE(N >= 0, "%s: N = %d", who, N);
     CMF_REQUIRE(Cin >= 1 && Cin <= kMaxCin && H >= 1 && W >= 1 && W <= 64 && H <= 256, "%s: C_in = %d (1..%d), H = %d, W = %d (W <= 64)", who,
                 Cin, kMaxCin, H, W);
-    P.N = N; P.Cin = Cin; P.H = H; P.W = W;
+    P.N = N; P.Cin = Cin; P.CinT = Cin; P.ci0 = 0; P.H = H; P.W = W;
     return 0;
 }
 
@@ -311,7 +315,7 @@ int set_attrs() {
 using namespace cmf;
 
 #define CMF_CIN_DISPATCH(CALL)          \
-    switch (Cin) {                      \
+    switch (P.Cin) {                    \
         case 1: CALL(1); break;         \
         case 2: CALL(2); break;         \
         case 3: CALL(3); break;         \
@@ -339,9 +343,7 @@ int cmf_convin_fwd(int N, int Cin, int H, int W, const float* x, const float* w,
     P.x = x; P.w = w; P.y = y;
     P.nb = bands(H, W, kThreads, 0, &P.R);
     const dim3 grid(P.nb, N);
-#define CALL(C) convin_fwd_kernel<C><<<grid, kThreads, 0, (cudaStream_t)stream>>>(P)
-    CMF_CIN_DISPATCH(CALL)
-#undef CALL
+    convin_fwd_kernel<<<grid, kThreads, (size_t)9 * Cin * kCo * sizeof(float), (cudaStream_t)stream>>>(P);
     CMF_CHECK_LAUNCH();
     return 0;
 }
@@ -356,10 +358,13 @@ int cmf_convin_dgrad(int N, int Cin, int H, int W, const float* g_y, const float
     P.g_y = g_y; P.w = w; P.g_x = g_x;
     P.nb = bands(H, W, kThreads, 2, &P.R);
     const dim3 grid(P.nb, N);
+    for (int ci0 = 0; ci0 < Cin; ci0 += kChunk) {           // input channels are independent: passes of <= 4
+        P.CinT = Cin; P.ci0 = ci0; P.Cin = Cin - ci0 < kChunk ? Cin - ci0 : kChunk;
 #define CALL(C) convin_dgrad_kernel<C><<<grid, kThreads, dgrad_smem<C>(P.R, W), (cudaStream_t)stream>>>(P)
-    CMF_CIN_DISPATCH(CALL)
+        CMF_CIN_DISPATCH(CALL)
 #undef CALL
-    CMF_CHECK_LAUNCH();
+        CMF_CHECK_LAUNCH();
+    }
     return 0;
 }
 
@@ -367,7 +372,6 @@ int cmf_convin_wgrad(int N, int Cin, int H, int W, const float* x, const float* 
     InParams P{};
     if (int rc = fill(P, "convin_wgrad", N, Cin, H, W)) return rc;
     CMF_REQUIRE(g_w, "convin_wgrad: null gradient");
-    const int n = kCo * Cin * 9;
     const int nparts = cmf_convin_wgrad_partials(N, H, W);
     if (N > 0) {
         CMF_REQUIRE(x && g_y && partial, "convin_wgrad: null pointer");
@@ -378,15 +382,21 @@ int cmf_convin_wgrad(int N, int Cin, int H, int W, const float* x, const float* 
         P.gpitch = wgrad_pitch(P.R, W);
         const int last = H - (P.nb - 1) * P.R;           // rows of the last band
         P.vec16 = ((long long)H * W) % 4 == 0 && (P.R * W) % 4 == 0 && (last * W) % 4 == 0 && aligned16(g_y);
-        const size_t smem = wgrad_smem(Cin, P.R, W);
-        CMF_REQUIRE(smem <= 96 * 1024, "convin_wgrad: %zu bytes of shared memory", smem);
+    }
+    for (int ci0 = 0; ci0 < Cin; ci0 += kChunk) {           // input channels are independent: passes of <= 4
+        P.CinT = Cin; P.ci0 = ci0; P.Cin = Cin - ci0 < kChunk ? Cin - ci0 : kChunk;
+        if (N > 0) {
+            const size_t smem = wgrad_smem(P.Cin, P.R, W);
+            CMF_REQUIRE(smem <= 96 * 1024, "convin_wgrad: %zu bytes of shared memory", smem);
 #define CALL(C) convin_wgrad_kernel<C><<<nparts, kThreads, smem, (cudaStream_t)stream>>>(P)
-        CMF_CIN_DISPATCH(CALL)
+            CMF_CIN_DISPATCH(CALL)
 #undef CALL
+            CMF_CHECK_LAUNCH();
+        }
+        const int n = kCo * P.Cin * 9;
+        convin_reduce_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>(nparts, P.Cin, Cin, ci0, partial, g_w);
         CMF_CHECK_LAUNCH();
     }
-    convin_reduce_kernel<<<(unsigned)ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>(nparts, n, partial, g_w);
-    CMF_CHECK_LAUNCH();
     return 0;
 }
 

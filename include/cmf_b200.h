@@ -341,10 +341,11 @@ int cmf_resnet_tail_bwd(int B, int d, int C, int HW, int P, int O, const float* 
  * C_in -> 64 channels, 3 x 3, padding 1, no bias; x (N, C_in, H, W), w (64, C_in, 3, 3), y (N, 64, H, W).
  * Replaces cmf/models/components/networks.py:131-139 (first get_conv of get_resnet) and its JVP rule
  * jvp_layers.py:49-64 (the same convolution on every tangent image), forward / data gradient / weight
- * gradient (cuDNN in the reference).  C_in <= 4, W <= 64, H <= 256, N <= 65535 per call.
- * cmf_convin_wgrad: partial = cmf_convin_wgrad_partials(N, H, W) x 64 * C_in * 9 floats of scratch (no zeroing
+ * gradient (cuDNN in the reference).  C_in <= 16 (the gradients run in passes of <= 4 input channels),
+ * W <= 64, H <= 256, N <= 65535 per call.
+ * cmf_convin_wgrad: partial = cmf_convin_wgrad_partials(N, H, W) x 64 * min(C_in, 4) * 9 floats of scratch (no zeroing
  * needed); g_w (64, C_in, 3, 3) = the partials summed in block order (bitwise reproducible). */
-#define CMF_CONVIN_MAX_CIN 4
+#define CMF_CONVIN_MAX_CIN 16
 int cmf_convin_usable(int Cin, int Cout, int H, int W);
 int cmf_convin_wgrad_partials(int N, int H, int W);
 int cmf_convin_fwd(int N, int Cin, int H, int W, const float* x, const float* w, float* y, cmf_stream_t stream);

@@ -319,7 +319,7 @@ def channel_sum(x):
 
 def convin_usable(x, weight):
     return (x.dtype == torch.float32 and x.dim() == 4 and weight.dim() == 4 and tuple(weight.shape[2:]) == (3, 3)
-            and weight.shape[0] == 64 and weight.shape[1] == x.shape[1] <= 4 and x.shape[3] <= 64)
+            and weight.shape[0] == 64 and weight.shape[1] == x.shape[1] <= 16 and x.shape[3] <= 64)
 
 
 def convin_fwd(x, weight):

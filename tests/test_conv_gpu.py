@@ -309,7 +309,7 @@ def test_activation_recompute_gives_identical_gradients():
 # first convolution of the conditioner (cmf_convin_fwd / _dgrad / _wgrad)
 # ------------------------------------------------------------------------------------------------
 CONVIN_SHAPES = [  # N, C_in, H, W
-    (3, 1, 28, 28), (5, 2, 14, 14), (2, 3, 32, 32), (2, 4, 16, 16), (7, 1, 8, 8), (1, 2, 7, 5), (4, 3, 12, 64), (130, 1, 28, 28),
+    (3, 1, 28, 28), (5, 2, 14, 14), (2, 3, 32, 32), (2, 4, 16, 16), (7, 1, 8, 8), (1, 2, 7, 5), (4, 3, 12, 64), (130, 1, 28, 28), (5, 6, 16, 16), (3, 12, 8, 8), (2, 16, 9, 11), (2, 5, 32, 32),
 ]
 
 
