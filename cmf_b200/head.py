@@ -25,6 +25,10 @@ Tensor = torch.Tensor
 
 # CMF_FLAT_STACK=0 keeps the small flat configs on the per-layer program (A/B measurements)
 _FLAT_STACK = os.environ.get("CMF_FLAT_STACK", "1") != "0"
+# The CG loop of hutch_with_cg needs ~12 products J^T J v (gpytorch's exit rule with the shipped cg_tolerance); each
+# is a full network pass on B m images.  For small latents ONE d-column pass under no_grad builds G = J^T J outright
+# (the tangent-batched program this package is about) and the products become 64 x 64 mat-vecs.  auto: d <= 128.
+_CG_EXPLICIT = os.environ.get("CMF_CG_EXPLICIT", "auto")
 # CMF_CG_GRAPH=0: the J^T J product inside the CG loop of hutch_with_cg is launched eagerly instead of replayed
 _CG_GRAPH = os.environ.get("CMF_CG_GRAPH", "1") != "0"
 
@@ -64,7 +68,7 @@ class FusedNonSquareHeadDensity(Density):
         self.log_jacobian_method = log_jacobian_method
         self._program: Optional[LayerProgram] = None
         self.last_cholesky_attempts = 1
-        self._cg_slot = _GraphSlot()   # entry: (key, graph, static latent, static vector, static result)
+        self._cg_slot = _GraphSlot()   # entry: {key: (graph, static latent, static vector, static result)}
         self.cg_graph_replays = 0
 
     # ------------------------------------------------------------------ program cache
@@ -258,28 +262,29 @@ class FusedNonSquareHeadDensity(Density):
             return eager
         key = (tuple(latent.shape), latent.dtype, latent.device, self.training,
                tuple(p.data_ptr() for p in self.parameters()))
-        if self._cg_slot.entry is None or self._cg_slot.entry[0] != key:
+        cache = self._cg_slot.entry = self._cg_slot.entry or {}        # a few shapes / modes (train and validation batches)
+        if key not in cache:
             lat = latent.detach().clone()
             vec = torch.zeros_like(lat)
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):                 # warm-up off the capture stream (allocator, library plans)
+                for _ in range(2):
+                    self._jac_transpose_jac_vec(lat, vec, create_graph=False)
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
             try:
-                side = torch.cuda.Stream()
-                side.wait_stream(torch.cuda.current_stream())
-                with torch.cuda.stream(side):             # warm-up off the capture stream (allocator, library plans)
-                    for _ in range(2):
-                        self._jac_transpose_jac_vec(lat, vec, create_graph=False)
-                torch.cuda.current_stream().wait_stream(side)
-                torch.cuda.synchronize()
-                graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
                     out = self._jac_transpose_jac_vec(lat, vec, create_graph=False)[0]
-            except Exception:                              # capture is an optimisation: never a reason to fail the step
-                self._cg_slot.entry = (key, None, None, None, None)
-                torch.cuda.synchronize()
-                return eager
-            self._cg_slot.entry = (key, graph, lat, vec, out)
-        _, graph, lat, vec, out = self._cg_slot.entry
-        if graph is None:
-            return eager
+            except Exception as e:
+                # a failed capture can leave torch's CUDA RNG / allocator in capture state: fail loudly, do not limp on
+                raise RuntimeError("cmf_b200: CUDA-graph capture of the hutch_with_cg J^T J product failed "
+                                   f"({type(e).__name__}: {e}); set CMF_CG_GRAPH=0 to launch it eagerly") from e
+            if len(cache) >= 4:
+                cache.pop(next(iter(cache)))
+            cache[key] = (graph, lat, vec, out)
+        graph, lat, vec, out = cache[key]
         lat.copy_(latent.detach())
 
         def replay(v):
@@ -300,10 +305,20 @@ class FusedNonSquareHeadDensity(Density):
         def to_vec(t): return t.transpose(1, 2).reshape(B * m, d)
         def to_ten(v): return v.reshape(B, m, d).transpose(1, 2)
 
-        product = self._cg_product(repeated)
+        explicit = _CG_EXPLICIT == "1" or (_CG_EXPLICIT == "auto" and d <= 128 and latent.is_cuda)
+        if explicit:
+            # same operator, formed once: G v instead of J^T (J v) per iteration (rounding-level differences only;
+            # the solution is detached either way, `non_square.py:247`)
+            with torch.no_grad():
+                G = self._get_full_jac_transpose_jac(latent.detach(), create_graph=False)[0]
 
-        def closure(t):
-            return to_ten(product(to_vec(t)))
+            def closure(t):
+                return torch.bmm(G, t)
+        else:
+            product = self._cg_product(repeated)
+
+            def closure(t):
+                return to_ten(product(to_vec(t)))
 
         inv = linear_cg_batched(closure, hutchinson_samples, max_iter=self.max_cg_iterations,
                                 tolerance=self.cg_tolerance).detach()

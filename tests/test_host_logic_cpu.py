@@ -140,3 +140,13 @@ def test_fused_preprocessing_equals_the_node_chain(emu, monkeypatch):
     while "low-dim-x" not in fused:
         fused, depth = fused["prior-dict"], depth + 1
     assert depth >= 4          # mult, add, logit, head ... nested like the reference's result dicts
+
+
+def test_hutch_cg_on_explicit_gram_cpu(emu, monkeypatch):
+    """host logic of the explicit-G CG path (one d-column pass, then mat-vecs) against the reference fixture"""
+    import cmf_b200.head as H
+    monkeypatch.setattr(H, "_CG_EXPLICIT", "1")
+    g = load_golden("hepmass_hutch_d10")
+    density = build_product(g)
+    loss, grads = run_loss(g, density)
+    check_against_golden(g, loss, grads, rtol=1e-4)

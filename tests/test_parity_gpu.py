@@ -471,7 +471,7 @@ def test_hutch_cg_product_graph_replay_matches_eager():
     g = load_golden("img8_hutch_d8")
     results = []
     for use_graph in (True, False):
-        H._CG_GRAPH = use_graph
+        H._CG_GRAPH, H._CG_EXPLICIT = use_graph, "0"          # the implicit products (the explicit-G path has its own test)
         try:
             density = build_product(g, "cuda")
             head, _ = find_head(strip_wrappers(density))
@@ -487,11 +487,35 @@ def test_hutch_cg_product_graph_replay_matches_eager():
                 copy.deepcopy(density)                      # the captured graph must not get in the way
             results.append((loss.detach().clone(), {k: v.clone() for k, v in grads.items()}))
         finally:
-            H._CG_GRAPH = True
+            H._CG_GRAPH, H._CG_EXPLICIT = True, "auto"
     (l1, g1), (l0, g0) = results
     # same kernels either way; the fixture's 8-channel conditioners run on cuDNN, whose data-gradient algorithms are
     # not bitwise reproducible run to run, and CG amplifies that: 1e-5, not torch.equal
     assert abs(float(l1) - float(l0)) <= 1e-5 * abs(float(l0))
     assert set(g1) == set(g0)
     for k in g0:                                             # (library weight gradients are not bitwise reproducible run to run)
+        assert_close(g1[k], g0[k], rtol=1e-4, atol=1e-7, what=k)
+
+
+@pytest.mark.parametrize("name", ["hepmass_hutch_d10", "img8_hutch_d8"])
+def test_hutch_cg_on_explicit_gram_matches_implicit_products(name):
+    """For small latents the CG loop runs on G = J^T J built by one d-column pass instead of ~12 network passes
+    (head._CG_EXPLICIT): same operator, so the same loss and gradients as the implicit products, and the same
+    reference fixture within the contract tolerance."""
+    import cmf_b200.head as H
+    g = load_golden(name)
+    results = []
+    for mode in ("1", "0"):
+        H._CG_EXPLICIT = mode
+        try:
+            density = build_product(g, "cuda")
+            loss, grads = run_loss(g, density, "cuda")
+            if mode == "1":
+                check_against_golden(g, loss, grads, rtol=1e-4)
+            results.append((loss, grads))
+        finally:
+            H._CG_EXPLICIT = "auto"
+    (l1, g1), (l0, g0) = results
+    assert abs(float(l1) - float(l0)) <= 1e-5 * abs(float(l0))
+    for k in g0:
         assert_close(g1[k], g0[k], rtol=1e-4, atol=1e-7, what=k)
