@@ -472,7 +472,7 @@ OTHER_CONFIGS = [
 def run_other_configs(dev, rank, world, barrier):
     """ms/step and whole-job samples/s of each shape: loss + backward + gradient all-reduce on a
     batch resident in HBM, every rank its own shard (weak scaling), max over ranks.  The flat shapes
-    run as one CUDA graph (cmf_b200.graphed) like the headline step; hutch_with_cg (host-side CG loop) runs eagerly."""
+    run as one CUDA graph (cmf_b200.graphed) like the headline step."""
     import torch.distributed as dist
     from cmf_b200.config import get_config, get_schema
     from cmf_b200.factory import get_density
@@ -504,8 +504,10 @@ def run_other_configs(dev, rank, world, barrier):
                     x = x / x.norm(dim=1, keepdim=True)
                 x = x.to(dev)
                 inner = density.module
-            # hutch_with_cg draws its probes and runs a host-side CG loop: eager
-            graphed = None if hutch else GraphedTrainStep(inner, tm, bucket, warmup_iters=1 if image else 3)
+            # hutch_with_cg with d <= 128 runs its CG on an explicitly built G with device-side exits under capture
+            # (cmf_b200.cg), so the whole step is one graph too; larger latents keep the host-driven loop: eager
+            graphed = (None if (hutch and cfg["latent_dimension"] > 128)
+                       else GraphedTrainStep(inner, tm, bucket, warmup_iters=1 if image else 3))
 
             def step():
                 if graphed is not None:

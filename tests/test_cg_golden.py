@@ -21,3 +21,18 @@ def test_cg_matches_gpytorch(name, impl):
     sol = fn(lambda t: c["A"] @ t, c["rhs"], max_iter=c["max_iter"], tolerance=c["tolerance"])
     err = float((sol - c["solution"]).abs().max() / c["solution"].abs().max())
     assert err < 1e-8, err
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_cg_sync_free_form_equals_the_host_loop(name):
+    """Under CUDA-graph capture the early exits become a device-side flag (cmf_b200.cg._cg, sync_free=True):
+    bit-identical solutions, on the gpytorch cases (early exit, frozen columns, zero right-hand side, capped)."""
+    from cmf_b200.cg import _cg
+    c = load_golden("cg_gpytorch")[name]
+    mm = lambda t: c["A"] @ t
+    a = _cg(mm, c["rhs"], c["max_iter"], c["tolerance"], 1e-10, 1e-10, False)
+    b = _cg(mm, c["rhs"], c["max_iter"], c["tolerance"], 1e-10, 1e-10, True)
+    assert torch.equal(a, b)
+    a32 = _cg(lambda t: c["A"].float() @ t, c["rhs"].float(), c["max_iter"], c["tolerance"], 1e-10, 1e-10, False)
+    b32 = _cg(lambda t: c["A"].float() @ t, c["rhs"].float(), c["max_iter"], c["tolerance"], 1e-10, 1e-10, True)
+    assert torch.equal(a32, b32)
