@@ -70,6 +70,7 @@ SIGNATURES = {
     "cmf_conv3x3_c64_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "cmf_conv3x3_c64_fused": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "cmf_relu_mask_pack": (_i, [_i, _i, _vp, _vp, _vp]),
+    "cmf_relu_and_pack": (_i, [_i, _i, _vp, _vp, _vp, _vp]),
     "cmf_conv3x3_c64_fused_bits": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "cmf_conv3x3_c64_joint": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "cmf_conv3x3_c64_wgrad_usable": (_i, [_i, _i, _i]),

@@ -251,3 +251,41 @@ extern "C" int cmf_channel_sum(int N, int C, int HW, const float* x, float* part
     CMF_CHECK_LAUNCH();
     return 0;
 }
+
+// ---- ReLU of a primal activation together with its packed sign bits ------------------------------------
+// relu_out[n, c, p] = max(x[n, c, p], 0) and bits[n, p] = the 64 sign bits of cmf_relu_mask_pack, in one pass
+// over x (networks.py:62-79: every residual block applies the ReLU to the primal and, by jvp_layers.py:38-46,
+// its 0/1 pattern to the tangents; the step ran a clamp kernel and a pack kernel over the same tensor).
+namespace cmf {
+namespace {
+__global__ void relu_and_pack_kernel(long long total, int hw, const float* __restrict__ x, uint2* __restrict__ bits,
+                                     float* __restrict__ relu_out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;      // = n * hw + p
+    if (i >= total) return;
+    const long long n = i / hw;
+    const long long off = (n * 64) * hw + (i - n * hw);
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+        const float a = __ldg(x + off + (long long)e * hw), b = __ldg(x + off + (long long)(32 + e) * hw);
+        lo |= (a > 0.f ? 1u : 0u) << e;
+        hi |= (b > 0.f ? 1u : 0u) << e;
+        relu_out[off + (long long)e * hw] = fmaxf(a, 0.f);
+        relu_out[off + (long long)(32 + e) * hw] = fmaxf(b, 0.f);
+    }
+    bits[i] = make_uint2(lo, hi);
+}
+}  // namespace
+}  // namespace cmf
+
+extern "C" int cmf_relu_and_pack(int N, int HW, const float* x, uint32_t* bits, float* relu_out, cmf_stream_t stream) {
+    using namespace cmf;
+    CMF_REQUIRE(N >= 0 && HW >= 0, "relu_and_pack: negative size");
+    if (N == 0 || HW == 0) return 0;
+    CMF_REQUIRE(x && bits && relu_out, "relu_and_pack: null pointer");
+    CMF_REQUIRE((reinterpret_cast<uintptr_t>(bits) & 7u) == 0, "relu_and_pack: bits must be 8-byte aligned");
+    const long long total = (long long)N * HW;
+    relu_and_pack_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(total, HW, x, reinterpret_cast<uint2*>(bits), relu_out);
+    CMF_CHECK_LAUNCH();
+    return 0;
+}

@@ -242,16 +242,22 @@ def conv3x3_c64_prep(weight: Tensor, transpose: bool) -> Tensor:
     return out
 
 
-def relu_mask_pack(x: Tensor) -> Tensor:
+def relu_mask_pack(x: Tensor, relu_out: Optional[Tensor] = None) -> Tensor:
     """x (N,64,H,W) primal activations -> packed signs (N, H*W, 2) int32 for ``conv3x3_c64(mask_src=...)``:
-    bit e of word 0 / 1 = (x[n, e, p] > 0) / (x[n, 32 + e, p] > 0)."""
+    bit e of word 0 / 1 = (x[n, e, p] > 0) / (x[n, 32 + e, p] > 0).  With ``relu_out`` (same shape, contiguous, not
+    x itself) the same pass also writes max(x, 0) there."""
     lib = _lib.load()
     x = _req(x, "x")
     N, C, H, W = x.shape
     assert C == 64
     bits = torch.empty(N, H * W, 2, dtype=torch.int32, device=x.device)
     with torch.cuda.device(x.device):
-        _lib.check(lib.cmf_relu_mask_pack(N, H * W, _ptr(x), _ptr(bits), _stream()), "cmf_relu_mask_pack")
+        if relu_out is None:
+            _lib.check(lib.cmf_relu_mask_pack(N, H * W, _ptr(x), _ptr(bits), _stream()), "cmf_relu_mask_pack")
+        else:
+            assert relu_out.is_cuda and relu_out.dtype == torch.float32 and relu_out.is_contiguous() and relu_out.shape == x.shape
+            assert relu_out.data_ptr() != x.data_ptr()
+            _lib.check(lib.cmf_relu_and_pack(N, H * W, _ptr(x), _ptr(bits), _ptr(relu_out), _stream()), "cmf_relu_and_pack")
     return bits
 
 

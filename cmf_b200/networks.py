@@ -254,25 +254,22 @@ class _ResidualStackJoint(torch.autograd.Function):
         shape = (Nt + B, *h.shape[1:])
         x, S = h.contiguous(), V.contiguous()
         new = lambda: torch.empty(shape, dtype=h.dtype, device=h.device)
-        xb = kernels.relu_mask_pack(x)
         A0 = new()
-        torch.clamp_min(x, 0, out=A0[Nt:])
+        xb = kernels.relu_mask_pack(x, relu_out=A0[Nt:])
         torch.mul(S.view(B, d, *S.shape[1:]), _bcast((x > 0).to(S.dtype)), out=A0[:Nt].view(B, d, *S.shape[1:]))
         xbits, hbits, saved = [], [], []
         for k in range(K):
             w1, b1, w2, b2 = tensors[4 * k:4 * k + 4]
             ws1, ws2 = kernels.conv3x3_c64_prep(w1, False), kernels.conv3x3_c64_prep(w2, False)
             h1 = kernels.conv3x3_c64(A0[Nt:], ws1, b1, drain=_FWD_DRAIN)                 # primal, one launch ahead
-            hb = kernels.relu_mask_pack(h1)
             A1 = new()
-            torch.clamp_min(h1, 0, out=A1[Nt:])
+            hb = kernels.relu_mask_pack(h1, relu_out=A1[Nt:])
             kernels.conv3x3_c64(A0[:Nt], ws1, None, mask_src=hb, mask_div=d, mask_first=True, out=A1[:Nt], drain=_FWD_DRAIN)
             x = kernels.conv3x3_c64(A1[Nt:], ws2, b2, res=x, drain=_FWD_DRAIN)
             xbits.append(xb); hbits.append(hb); saved += [A0, A1]
             if k + 1 < K:
-                xb = kernels.relu_mask_pack(x)
                 A0 = new()
-                torch.clamp_min(x, 0, out=A0[Nt:])
+                xb = kernels.relu_mask_pack(x, relu_out=A0[Nt:])
                 S, _ = kernels.conv3x3_c64(A1[:Nt], ws2, None, mask_src=xb, mask_div=d, res=S, second=True, out2=A0[:Nt],
                                            drain=_FWD_DRAIN)
             else:

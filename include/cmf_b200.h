@@ -361,6 +361,12 @@ int cmf_convin_wgrad(int N, int Cin, int H, int W, const float* x, const float* 
 int cmf_channel_sum_splits(int N, int C);
 int cmf_channel_sum(int N, int C, int HW, const float* x, float* partial, float* out, cmf_stream_t stream);
 
+/* ---- ReLU + packed sign bits in one pass ----------------------------------------------------------------
+ * relu_out (N, 64, HW) = max(x, 0) and bits as cmf_relu_mask_pack writes them, from one read of x (N, 64, HW):
+ * the primal side of every residual block (cmf/models/components/networks.py:62-79) and the mask its tangents
+ * take (jvp_layers.py:38-46).  relu_out may be a batch slice of a larger tensor; it must not alias x. */
+int cmf_relu_and_pack(int N, int HW, const float* x, uint32_t* bits, float* relu_out, cmf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -109,9 +109,11 @@ def conv3x3_c64_prep(weight, transpose):
     return (weight.flip(2, 3).transpose(0, 1) if transpose else weight).contiguous()
 
 
-def relu_mask_pack(x):
-    """(N,64,H,W) -> (N, H*W, 2) int32, bit e of word h = x[n, 32 h + e, p] > 0"""
+def relu_mask_pack(x, relu_out=None):
+    """(N,64,H,W) -> (N, H*W, 2) int32, bit e of word h = x[n, 32 h + e, p] > 0; relu_out (optional) <- max(x, 0)"""
     N, C, H, W = x.shape
+    if relu_out is not None:
+        torch.clamp_min(x, 0, out=relu_out)
     pos = (x > 0).flatten(2).view(N, 2, 32, H * W).to(torch.int64)                 # (N, word, bit, p)
     words = (pos << torch.arange(32, device=x.device).view(1, 1, 32, 1)).sum(2)      # (N, 2, p), 0 .. 2^32-1
     words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)

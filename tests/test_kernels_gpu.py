@@ -514,3 +514,13 @@ def test_channel_sum(shape):
     err = float((out.double().cpu() - ref).abs().max())
     assert err <= 1e-6 * (float(x[2:].abs().sum(dim=(0, 2, 3)).max()) + 1e-30) + 1e-12
     assert torch.equal(out, K.channel_sum(xd[2:]))
+
+
+def test_relu_and_pack_in_one_pass():
+    """max(x, 0) into a batch slice of a larger buffer + the packed sign bits, against the two separate kernels"""
+    import cmf_b200.kernels as K
+    x = _rand(5, 64, 14, 14, seed=11).float().to(DEV)
+    big = torch.full((9, 64, 14, 14), 7.0, device=DEV)
+    bits = K.relu_mask_pack(x, relu_out=big[4:])
+    assert torch.equal(bits, K.relu_mask_pack(x))
+    assert torch.equal(big[4:], torch.clamp_min(x, 0)) and bool((big[:4] == 7.0).all())
