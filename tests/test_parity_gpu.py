@@ -49,7 +49,11 @@ def test_cuda_intermediates_match_reference_golden(name):
         assert_close(l1d, g["l1_diag"], RTOL, what="l1 diag")
 
 
-@pytest.mark.parametrize("name,batch", [("sphere_gij_d3", 257), ("hepmass_gij_d10_warm", 33), ("img8_gij_d8", 5)])
+@pytest.mark.parametrize("name,batch", [("sphere_gij_d3", 257), ("hepmass_gij_d10_warm", 33), ("img8_gij_d8", 5),
+                                        # the reference's full per-GPU batches of the flat configs (two_d.py:77, tabular.py:290-296):
+                                        # 1000 samples through the whole-stack kernel, 5000 / 750 through the one-launch MLP conditioner
+                                        # (278 / 69 row tiles over persistent CTAs)
+                                        ("sphere_gij_d3", 1000), ("power_gij_d6", 5000), ("hepmass_gij_d10_warm", 750)])
 def test_cuda_path_matches_oracle_on_fresh_inputs(name, batch):
     """Different weights (salt) and inputs than the fixtures; oracle in fp64 as the tighter checker."""
     g = load_golden(name)
