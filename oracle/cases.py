@@ -57,6 +57,11 @@ CASES = {
     "img12_c64_gij_d16": dict(dataset="mnist", x_shape=(1, 12, 12), batch=3, epoch=60, data="pixels",
                               overrides=dict(g_ij_loss=True, latent_dimension=16, g_hidden_channels=[64, 64],
                                              prior_num_density_layers=2, **COMMON)),
+    # the same for the 3-channel (CIFAR-shape) architecture: first convolutions with 3 / 6 / 12 input channels, conditioner
+    # tails with 6 / 12 / 24 outputs, 64 -> 64 convolutions at 8x8 / 4x4 / 2x2
+    "img8c3_c64_gij_d16": dict(dataset="cifar10", x_shape=(3, 8, 8), batch=3, epoch=60, data="pixels",
+                               overrides=dict(g_ij_loss=True, latent_dimension=16, g_hidden_channels=[64, 64],
+                                              prior_num_density_layers=2, **COMMON)),
     # log_jacobian_method=hutch_with_cg (the image-config default, config/images.py:148) with the Hutchinson
     # probes injected (``hutch=True``: gen_golden.py replaces torch.randn inside the reference's draw,
     # non_square.py:206, by the deterministic tensor of ``hutch_eps``).  With g_ij_loss the reference
