@@ -77,6 +77,11 @@ CASES = {
     "img8_hutch_d8": dict(dataset="mnist", x_shape=(1, 8, 8), batch=4, epoch=60, data="pixels", hutch=True,
                           overrides=dict(g_ij_loss=True, latent_dimension=8, g_hidden_channels=[8, 8],
                                          prior_num_density_layers=2, log_jacobian_method="hutch_with_cg")),
+    # the image configs' default method at the shipped hidden width: the m-column JVP and the explicit G of the CG loop run
+    # on the tcgen05 / first-conv / tail kernels, the doubly differentiated VJP on library convolutions
+    "img12_c64_hutch_d16": dict(dataset="mnist", x_shape=(1, 12, 12), batch=3, epoch=60, data="pixels", hutch=True,
+                                overrides=dict(g_ij_loss=True, latent_dimension=16, g_hidden_channels=[64, 64],
+                                               prior_num_density_layers=2, log_jacobian_method="hutch_with_cg")),
     # north_star's "rational-quadratic-spline coupling" layers ON the JVP stack (nsf-c):
     # schema_type nsf with the coupling variant and no LU-linear layers.  The reference has no spline
     # _jvp; oracle/gen_golden.py gives its bijection class the autograd JVP of the nsf transform
