@@ -524,3 +524,27 @@ def test_relu_and_pack_in_one_pass():
     bits = K.relu_mask_pack(x, relu_out=big[4:])
     assert torch.equal(bits, K.relu_mask_pack(x))
     assert torch.equal(big[4:], torch.clamp_min(x, 0)) and bool((big[:4] == 7.0).all())
+
+
+def test_empty_batches_of_the_conditioner_kernels():
+    """B = 0 through the MLP, tail and first-convolution entry points: empty outputs, zero parameter gradients, no launch error"""
+    import cmf_b200.kernels as K
+    z = lambda *s: torch.zeros(*s, device=DEV)
+    # MLP
+    ws, bs = [torch.randn(16, 3, device=DEV), torch.randn(4, 16, device=DEV)], [torch.randn(16, device=DEV), torch.randn(4, device=DEV)]
+    wpack, widths = K.mlp_pack(ws, bs)
+    st, ST, saved = K.mlp_jvp_fwd(z(0, 3), z(0, 2, 3), wpack, widths, save=True)
+    assert st.shape == (0, 4) and ST.shape == (0, 2, 4)
+    g_x, g_V, g_W, g_b = K.mlp_jvp_bwd(z(0, 3), z(0, 2, 3), wpack, widths, saved, z(0, 4), z(0, 2, 4))
+    assert g_x.shape == (0, 3) and all(float(g.abs().max()) == 0 for g in g_W + g_b)
+    # tail
+    w2, b2, sw, sb = torch.randn(2, 64, device=DEV), z(2), torch.ones(2, device=DEV), z(2)
+    y, Y = K.resnet_tail_fwd(z(0, 64, 16), z(0, 64, 16), None, 16, w2, b2, sw, sb)
+    assert y.shape == (0, 2, 16)
+    out = K.resnet_tail_bwd(z(0, 64, 16), None, None, 16, w2, b2, sw, sb, z(0, 2, 16), None)
+    assert float(out[2].abs().max()) == 0 and float(out[3].abs().max()) == 0
+    # first convolution
+    w = torch.randn(64, 2, 3, 3, device=DEV)
+    assert K.convin_fwd(z(0, 2, 8, 8), w).shape == (0, 64, 8, 8)
+    assert K.convin_dgrad(z(0, 64, 8, 8), w).shape == (0, 2, 8, 8)
+    assert float(K.convin_wgrad(z(0, 2, 8, 8), z(0, 64, 8, 8)).abs().max()) == 0
