@@ -40,9 +40,12 @@ struct InParams {
 };
 
 // ------------------------------------------------------------------------------------------------ forward
+// CIN > 0: the channel loop is unrolled (C_in <= 4, the shapes of the benchmarked step: 104 registers);
+// CIN == 0: run-time channel count (5 .. 16 input channels; with the loop unrolled only over the taps)
+template <int CIN>
 __global__ void __launch_bounds__(kThreads) convin_fwd_kernel(InParams P) {
     extern __shared__ __align__(16) float w_s[];                // [ci * 9 + tap][co]
-    const int Cin = P.Cin;
+    const int Cin = CIN > 0 ? CIN : P.Cin;
     for (int i = threadIdx.x; i < 9 * Cin * kCo; i += kThreads) {
         const int k = i / kCo, co = i - k * kCo;
         w_s[i] = __ldg(P.w + co * Cin * 9 + k);
@@ -58,8 +61,7 @@ __global__ void __launch_bounds__(kThreads) convin_fwd_kernel(InParams P) {
 #pragma unroll
     for (int co = 0; co < kCo; ++co) acc[co] = 0.f;
     const float* xn = P.x + (long long)n * Cin * hw;
-#pragma unroll 1
-    for (int ci = 0; ci < Cin; ++ci)
+    auto one_channel = [&](int ci) {
 #pragma unroll
         for (int tap = 0; tap < 9; ++tap) {
             const int rr = r + tap / 3 - 1, cc = c + tap % 3 - 1;
@@ -74,6 +76,14 @@ __global__ void __launch_bounds__(kThreads) convin_fwd_kernel(InParams P) {
                 acc[4 * q + 3] = fmaf(wv.w, v, acc[4 * q + 3]);
             }
         }
+    };
+    if (CIN > 0) {
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci) one_channel(ci);
+    } else {
+#pragma unroll 1
+        for (int ci = 0; ci < Cin; ++ci) one_channel(ci);
+    }
     float* yo = P.y + (long long)n * kCo * hw + r * P.W + c;
 #pragma unroll
     for (int co = 0; co < kCo; ++co) yo[co * hw] = acc[co];
@@ -343,7 +353,15 @@ int cmf_convin_fwd(int N, int Cin, int H, int W, const float* x, const float* w,
     P.x = x; P.w = w; P.y = y;
     P.nb = bands(H, W, kThreads, 0, &P.R);
     const dim3 grid(P.nb, N);
-    convin_fwd_kernel<<<grid, kThreads, (size_t)9 * Cin * kCo * sizeof(float), (cudaStream_t)stream>>>(P);
+    const size_t smem = (size_t)9 * Cin * kCo * sizeof(float);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (Cin) {
+        case 1: convin_fwd_kernel<1><<<grid, kThreads, smem, st>>>(P); break;
+        case 2: convin_fwd_kernel<2><<<grid, kThreads, smem, st>>>(P); break;
+        case 3: convin_fwd_kernel<3><<<grid, kThreads, smem, st>>>(P); break;
+        case 4: convin_fwd_kernel<4><<<grid, kThreads, smem, st>>>(P); break;
+        default: convin_fwd_kernel<0><<<grid, kThreads, smem, st>>>(P); break;
+    }
     CMF_CHECK_LAUNCH();
     return 0;
 }
