@@ -305,8 +305,8 @@ extern "C" int cmf_gram_bwd_path(int B, int d, int n, const float* V, const floa
         const bool ok = gram_tc_bwd_usable(B, d, n, V, g_G, g_V);
         CMF_REQUIRE(ok || path == CMF_GRAM_AUTO,
                     "gram_bwd: tensor-core path needs d >= 16, d %% 4 == 0, n >= 32, n %% 4 == 0 and 16-byte aligned V, g_G (d=%d n=%d)", d, n);
-        // at d <= 64 the FP32 FMA kernel is as fast (HBM-bound either way); the tensor core wins above
-        if (ok && (path == CMF_GRAM_TC || d > 64)) return gram_tc_bwd_launch(B, d, n, V, g_G, g_V, (cudaStream_t)stream);
+        // measured (scripts/gram_probe.py): the persistent tensor-core kernel wins from d = 32 up, the FP32 FMA kernel at d = 16
+        if (ok && (path == CMF_GRAM_TC || d >= 32)) return gram_tc_bwd_launch(B, d, n, V, g_G, g_V, (cudaStream_t)stream);
     }
     if (d <= kSmallD && n % 4 == 0 && aligned16(V) && aligned16(g_V) && B <= 65535 * 32) {
         static DeviceOnce attr_set;

@@ -11,9 +11,9 @@
 //              computed and dropped: an M=64 MMA costs the same tensor cycles as M=128).
 //   d  > 128 : tiles (tr, tc <= tr) of one sample, SYRK style; the mirror is written from the same
 //              accumulator, diagonal tiles write their lower triangle twice, so G is bitwise symmetric.
-// Pipeline (448 threads): warp 0 = TMA producer (one lane; 128-byte-swizzled boxes of 32 k-columns),
-// warp 1 = TMEM allocation + MMA issue (one lane), warps 2..5 = split the landed tile in shared
-// memory (hi in place, lo beside it), warps 6..13 = drain (see "Accumulation precision") + epilogue.
+// Pipeline (512 threads): warp 0 = TMA producer (one lane; 128-byte-swizzled boxes of 32 k-columns),
+// warp 1 = TMEM allocation + MMA issue (one lane), warps 2..7 = split the landed tile in shared
+// memory (two groups on alternate stages; lo beside the raw tile, which is hi), warps 8..15 = drain (see "Accumulation precision") + epilogue.
 // HBM traffic: V read once (4 d n bytes / sample) + G written; 3 x 2 d^2 n tensor FLOP / sample.
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -27,7 +27,9 @@ constexpr int kKc = 32;               // k-columns per stage: 32 fp32 = one 128-
 constexpr int kTileBytes = kTile * kKc * 4;   // 16 KB
 constexpr int kMaxStages = 10;
 constexpr int kTmemCols = 512;        // [0,128) cross terms, [128,256) / [256,384) hi*hi ping-pong
-constexpr int kSplitWarps = 4, kDrainWarps = 8;
+constexpr int kLoDepth = 4;           // deepest lo ring (split -> MMA); deep enough that a split does not wait for the MMA two stages back
+constexpr int kSplitGroup = 3;        // warps per split group; two groups take the even / odd stages
+constexpr int kSplitWarps = 2 * kSplitGroup, kDrainWarps = 8;   // 16 warps: 128 registers each for the drain warps
 constexpr int kDrainEvery = 4;        // stages (of K = 32) accumulated on the tensor core per drain
 constexpr int kGramTcThreads = 32 * (2 + kSplitWarps + kDrainWarps);   // 448
 constexpr int kGsLd = kTile + 1;      // padded row of the epilogue staging tile (bank-conflict free)
@@ -39,9 +41,11 @@ struct GramTcParams {
     int T;          // 128-row tiles per sample (d > 128)
     int ntiles;     // T (T+1) / 2
     int nstages;    // raw ring depth
+    int nlo;        // lo ring depth (<= kLoDepth)
     int raw_bytes;  // bytes of one raw stage (one or two 16 KB tiles)
     int box_rows;
     int accumulate;
+    int ablate;     // timing experiments (CMF_GRAM_FWD_ABLATE): 1 no MMA, 2 no split
     float* G;
 };
 
@@ -62,7 +66,7 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
                    const GramTcParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages];
-    __shared__ __align__(8) uint64_t split_bar[2], lo_free[2], hh_full[2], hh_free[2], done_bar;
+    __shared__ __align__(8) uint64_t split_bar[kLoDepth], lo_free[kLoDepth], hh_full[2], hh_free[2], done_bar;
     __shared__ uint32_t tmem_base_smem;
 
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -88,17 +92,19 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
     // samples: G = V1 V1^T + V2 V2^T in one accumulation, one launch (the two halves of J^T)
     const int nk1 = (P.n + kKc - 1) / kKc;
     const int nk = nk1 + (P.n2 + kKc - 1) / kKc;
-    const int nst = P.nstages;
-    uint8_t* lo_ring = smem + (size_t)nst * P.raw_bytes;      // 2 x raw_bytes
+    const int nst = P.nstages, nlo = P.nlo;
+    uint8_t* lo_ring = smem + (size_t)nst * P.raw_bytes;      // nlo x raw_bytes
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nst; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(&split_bar[i], 32 * kSplitWarps);
+        for (int i = 0; i < P.nlo; ++i) {
+            mbar_init(&split_bar[i], 32 * kSplitGroup);
             mbar_init(&lo_free[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
             mbar_init(&hh_full[i], 1);
             mbar_init(&hh_free[i], 32 * kDrainWarps);
         }
@@ -134,9 +140,9 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         if (lane == 0) {
             const uint32_t idesc = umma_idesc_tf32(kTile, kTile);
             for (int kc = 0; kc < nk; ++kc) {
-                const int s = kc % nst, l = kc & 1;
+                const int s = kc % nst, l = kc % nlo;
                 const int g = kc / kDrainEvery, r = kc - g * kDrainEvery, pp = g & 1;
-                mbar_wait(&split_bar[l], (uint32_t)(kc >> 1) & 1u);
+                mbar_wait(&split_bar[l], (uint32_t)(kc / nlo) & 1u);
                 if (r == 0) mbar_wait(&hh_free[pp], ((uint32_t)(g >> 1) & 1u) ^ 1u);
                 tc_fence_after();
                 const uint32_t a_hi = smem_u32(smem + (size_t)s * P.raw_bytes);
@@ -146,13 +152,15 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
                 const uint32_t t_hh = tmem_base + 128u + 128u * (uint32_t)pp;
 #pragma unroll
                 for (int k = 0; k < kKc / 8; ++k)            // UMMA K = 8 for tf32 (32 bytes)
-                    umma_tf32(t_hh, umma_desc_sw128(a_hi + k * 32), umma_desc_sw128(b_hi + k * 32), idesc, (r | k) != 0);
+                    if (!(P.ablate & 1)) umma_tf32(t_hh, umma_desc_sw128(a_hi + k * 32), umma_desc_sw128(b_hi + k * 32), idesc, (r | k) != 0);
                 if (r == kDrainEvery - 1 || kc == nk - 1) umma_commit(&hh_full[pp]);   // drain warps may read hh[pp]
 #pragma unroll
-                for (int k = 0; k < kKc / 8; ++k) {
+                for (int k = 0; k < ((P.ablate & 1) ? 0 : kKc / 8); ++k) {
                     umma_tf32(tmem_base, umma_desc_sw128(a_lo + k * 32), umma_desc_sw128(b_hi + k * 32), idesc,
                               (kc | k) != 0);
-                    umma_tf32(tmem_base, umma_desc_sw128(a_hi + k * 32), umma_desc_sw128(b_lo + k * 32), idesc, 1);
+                    // both operands are the same rows: hi lo^T is the transpose of lo hi^T and is added in the epilogue
+                    // (the kernel is bound by the MMAs' shared-memory operand reads, 8 KB each)
+                    if (!same) umma_tf32(tmem_base, umma_desc_sw128(a_hi + k * 32), umma_desc_sw128(b_lo + k * 32), idesc, 1);
                 }
                 umma_commit(&empty_bar[s]);                  // raw slot and lo slot free once these retire
                 umma_commit(&lo_free[l]);
@@ -160,22 +168,24 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
             umma_commit(&done_bar);                          // cross accumulator complete
         }
     } else if (warp < 2 + kSplitWarps) {
-        // ===== splitter warps: hi in place, lo into the 2-deep lo ring
-        const int t = threadIdx.x - 64;                      // 0..127
+        // ===== splitter warps: lo = v - trunc(v) into the lo ring.  hi is the landed tile itself: kind::tf32 reads the top
+        // 19 bits of each word (G is bit-identical with and without clearing the low 13 bits in shared memory).
+        // A stage's split is a latency chain for one warp per scheduler (LDS -> ALU -> STS -> proxy fence -> arrive,
+        // ~1200 cycles measured): two groups work on alternate stages, group g owns slot g of the lo ring
+        const int t = (threadIdx.x - 64) % (32 * kSplitGroup);   // thread within the group
         const int nvec = (same ? 1 : 2) * (kTileBytes / 16); // float4 per stage of raw data
-        for (int kc = 0; kc < nk; ++kc) {
-            const int s = kc % nst, l = kc & 1;
+        for (int kc = (warp - 2) / kSplitGroup; kc < nk; kc += 2) {
+            const int s = kc % nst, l = kc % nlo;
             mbar_wait(&full_bar[s], (uint32_t)(kc / nst) & 1u);
-            mbar_wait(&lo_free[l], ((uint32_t)(kc >> 1) & 1u) ^ 1u);
+            mbar_wait(&lo_free[l], ((uint32_t)(kc / nlo) & 1u) ^ 1u);
             float4* raw = reinterpret_cast<float4*>(smem + (size_t)s * P.raw_bytes);
             float4* lo = reinterpret_cast<float4*>(lo_ring + (size_t)l * P.raw_bytes);
 #pragma unroll 4
-            for (int i = t; i < nvec; i += 32 * kSplitWarps) {
+            for (int i = t; i < ((P.ablate & 2) ? 0 : nvec); i += 32 * kSplitGroup) {
                 const float4 v = raw[i];
                 float4 h, w;
                 split_tf32(v.x, h.x, w.x); split_tf32(v.y, h.y, w.y);
                 split_tf32(v.z, h.z, w.z); split_tf32(v.w, h.w, w.w);
-                raw[i] = h;
                 lo[i] = w;
             }
             fence_proxy_async_smem();
@@ -206,7 +216,7 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
             const int pp = g & 1;
             mbar_wait(&hh_full[pp], (uint32_t)(g >> 1) & 1u);
             tc_fence_after();
-            if (needed) {
+            if (needed && !(P.ablate & 8)) {
                 const uint32_t t_hh = tmem_base + 128u + 128u * (uint32_t)pp + (uint32_t)(half * 64);
 #pragma unroll
                 for (int ch = 0; ch < 2; ++ch) {
@@ -230,7 +240,8 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
                 float v[32];
                 tmem_ld_32x32(tmem_base + lane_addr + (uint32_t)c0, v);
 #pragma unroll
-                for (int u = 0; u < 32; ++u) Gs[i * kGsLd + c0 + u] = acc[ch][u] + v[u];
+                for (int u = 0; u < 32; ++u)     // same rows: T = H / 2 + C, G = T + T^T below
+                    Gs[i * kGsLd + c0 + u] = same ? fmaf(acc[ch][u], 0.5f, v[u]) : acc[ch][u] + v[u];
             }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kDrainWarps) : "memory");
@@ -244,8 +255,7 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
             for (int e = t; e < total; e += 32 * kDrainWarps) {
                 const int s = e / dd, rem = e - s * dd;
                 const int li = rem / d, j = rem - li * d;
-                const int hi_ = max(li, j), lo_ = min(li, j); // lower triangle is the source of both
-                const float g = Gs[(s * d + hi_) * kGsLd + s * d + lo_];
+                const float g = Gs[(s * d + li) * kGsLd + s * d + j] + Gs[(s * d + j) * kGsLd + s * d + li];
                 Gb[e] = accm ? Gb[e] + g : g;
             }
         } else {
@@ -254,7 +264,7 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
                 const int r = e >> 7, c = e & 127;
                 const int gi = tr * kTile + r, gj = tc * kTile + c;
                 if (gi < d && gj < d) {
-                    const float g = (tr != tc || c <= r) ? Gs[r * kGsLd + c] : Gs[c * kGsLd + r];
+                    const float g = tr != tc ? Gs[r * kGsLd + c] : Gs[r * kGsLd + c] + Gs[c * kGsLd + r];
                     float* p = Gb + (size_t)gi * d + gj;
                     *p = accm ? *p + g : g;
                 }
@@ -339,16 +349,18 @@ int gram_tc_fwd_launch(int B, int d, int n, const float* V, int n2, const float*
                        cudaStream_t stream) {
     GramTcParams P{};
     P.B = B; P.d = d; P.n = n; P.n2 = n2; P.G = G; P.accumulate = accumulate;
+    static const int ablate_env = [] { const char* e = getenv("CMF_GRAM_FWD_ABLATE"); return e ? atoi(e) : 0; }();
+    P.ablate = ablate_env;
     long long grid;
     if (d <= kTile) {
         P.S = kTile / d; P.T = 1; P.ntiles = 1;
         P.box_rows = P.S * d;
-        P.nstages = 8; P.raw_bytes = kTileBytes;
+        P.nstages = 8; P.nlo = 2; P.raw_bytes = kTileBytes;
         grid = ceil_div(B, P.S);
     } else {
         P.S = 0; P.T = (int)ceil_div(d, kTile); P.ntiles = P.T * (P.T + 1) / 2;
         P.box_rows = kTile;
-        P.nstages = 4; P.raw_bytes = 2 * kTileBytes;
+        P.nstages = 4; P.nlo = 2; P.raw_bytes = 2 * kTileBytes;
         grid = (long long)B * P.ntiles;
     }
     CMF_REQUIRE(grid < (1LL << 31), "gram_tc: grid too large");
@@ -360,7 +372,7 @@ int gram_tc_fwd_launch(int B, int d, int n, const float* V, int n2, const float*
         rc = make_tmap_2d_f32(&tmap2, V2, (uint64_t)B * d, (uint64_t)n2, (uint64_t)n2, (uint32_t)P.box_rows, 0);
         if (rc != 0) return rc;
     }
-    const size_t smem = (size_t)(P.nstages + 2) * P.raw_bytes + 1024;     // raw ring + 2-deep lo ring
+    const size_t smem = (size_t)(P.nstages + P.nlo) * P.raw_bytes + 1024;     // raw ring + lo ring
     static DeviceOnce attr_set;
     if (!attr_set.done()) {
         cudaError_t e = cudaFuncSetAttribute(gram_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -556,6 +568,248 @@ gram_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Persistent adjoint for d <= 128 (one j tile).  A work item is (sample, 128-wide n tile) with only ceil(d / 32) K
+// stages, so a CTA per item (the kernel above, still used for d > 128) spends its life in the prologue (barrier init,
+// TMEM allocation, first TMA round trip) and the epilogue: ~8 us per wave of 148 CTAs, 14 waves at B = 512, n = 392.
+// Here one CTA per SM walks a contiguous range of items:
+//   * B operand: S = g_G + g_G^T (hi | lo, K-major 128B-swizzled chunks of 32 k) is built ONCE per sample into one of
+//     nS buffers from X / Y tiles that land in a small ring of their own, and is reused by the sample's n tiles;
+//   * A operand: a ring stage is the raw 16 KB V tile (= hi: the tensor core reads the top 19 bits of a word), lo goes
+//     to a 2-deep ring that spans split -> MMA; two split groups of four warps take alternate stages (a stage's split
+//     is a ~600-cycle latency chain for one warp per scheduler, and was the longest per-item chain with one group);
+//   * the accumulator is double-buffered in TMEM (2 x 128 columns): eight epilogue warps write item i while the
+//     splitters and the tensor core work on item i + 1.
+// Measured (scripts/gram_probe.py, B = 512, d = 64, n = 392): CTA per item 110 us, FP32 FMA kernel 59 us, this kernel
+// see profiles/r02_summary.md.  Not kept: cp.async.bulk.prefetch of the V boxes ahead of the ring (slower: the TMA
+// unit, not the DRAM latency, paces the 4 KB boxes).
+// ------------------------------------------------------------------------------------------------
+constexpr int kBwdSplitGroups = 2;
+constexpr int kBwdEpiWarps = 8;        // two per TMEM lane quarter (even / odd 32-column chunks of the accumulator): the
+                                       // epilogue is a latency chain per warp, 4 warps 48 us, 8 warps 43 us, 16 warps x 16 columns 44.5 us
+constexpr int kBwdPThreads = 32 * (2 + 4 * kBwdSplitGroups + kBwdEpiWarps);   // TMA, MMA, 2 x 4 split warps, epilogue warps
+constexpr int kBwdPTmemCols = 256;
+
+struct GramBwdCParams {
+    int B, d, n, n_tiles, N, nk;
+    int nst;            // raw V stages (16 KB each)
+    int nS, ngl;        // S buffers, landing slots for the X / Y tiles
+    int s_bytes;        // one S buffer: 2 * nk * N * 128
+    int ablate;         // timing experiments (CMF_GRAM_BWD_ABLATE): 1 no MMA, 2 no S build, 4 no A split, 8 no stores
+    float* gV;
+};
+constexpr int kBwdCLo = 2;
+
+__global__ void __launch_bounds__(kBwdPThreads, 1)
+gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapX,
+                          const __grid_constant__ CUtensorMap tmapY, const GramBwdCParams P) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages];
+    __shared__ __align__(8) uint64_t split_bar[kBwdCLo], lo_free[kBwdCLo], g_full[2], g_free[2], s_full[2], s_free[2];
+    __shared__ __align__(8) uint64_t acc_full[2], acc_free[2];
+    __shared__ uint32_t tmem_base_smem;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int d = P.d, N = P.N, nst = P.nst, nk = P.nk, nS = P.nS, ngl = P.ngl;
+    const long long total = (long long)P.B * P.n_tiles;
+    const int w_begin = (int)(total * blockIdx.x / gridDim.x), w_end = (int)(total * (blockIdx.x + 1) / gridDim.x);
+    // shared-memory map: S buffers | X/Y landing slots | lo ring | raw ring
+    const int chunk_bytes = N * 128;                          // one hi (or lo) chunk of S; X and Y are as large
+    uint8_t* S_base = smem;
+    uint8_t* gl_base = S_base + (size_t)nS * P.s_bytes;
+    uint8_t* lo_base = gl_base + (size_t)ngl * 2 * chunk_bytes;
+    uint8_t* raw_base = lo_base + (size_t)kBwdCLo * kTileBytes;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nst; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&split_bar[i], 128);
+            mbar_init(&lo_free[i], 1);
+            mbar_init(&g_full[i], 1);
+            mbar_init(&g_free[i], 128 * kBwdSplitGroups);
+            mbar_init(&s_full[i], 128 * kBwdSplitGroups);
+            mbar_init(&s_free[i], 1);
+            mbar_init(&acc_full[i], 1);
+            mbar_init(&acc_free[i], 32 * kBwdEpiWarps);
+        }
+        mbar_fence_init();
+        prefetch_tmap(&tmap);
+        prefetch_tmap(&tmapX);
+        prefetch_tmap(&tmapY);
+    }
+    if (warp == 1) tmem_alloc<kBwdPTmemCols>(&tmem_base_smem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int gs = 0, gg = 0, b_prev = -1;
+            for (int w = w_begin; w < w_end; ++w) {
+                const int b = w / P.n_tiles, n0 = (w - b * P.n_tiles) * kTile;
+                const int ngrp = min(4, (P.n - n0 + 31) / 32);      // 32-wide n groups that hold data
+                if (b != b_prev) {                                   // the sample's g_G tiles, one landing slot per chunk
+                    b_prev = b;
+                    for (int kc = 0; kc < nk; ++kc, ++gg) {
+                        const int gl = gg % ngl;
+                        mbar_wait(&g_free[gl], (((uint32_t)(gg / ngl)) & 1u) ^ 1u);
+                        uint8_t* dst = gl_base + (size_t)gl * 2 * chunk_bytes;
+                        mbar_arrive_expect_tx(&g_full[gl], (uint32_t)(2 * chunk_bytes));
+                        tma_load_2d(dst, &tmapX, &g_full[gl], kc * kKc, b * d);
+                        tma_load_2d(dst + chunk_bytes, &tmapY, &g_full[gl], 0, b * d + kc * kKc);
+                    }
+                }
+                for (int kc = 0; kc < nk; ++kc, ++gs) {
+                    const int s = gs % nst;
+                    mbar_wait(&empty_bar[s], (((uint32_t)(gs / nst)) & 1u) ^ 1u);
+                    uint8_t* st = raw_base + (size_t)s * kTileBytes;
+                    mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(ngrp * 4096));
+                    for (int g = 0; g < ngrp; ++g)
+                        tma_load_2d(st + g * 4096, &tmap, &full_bar[s], n0 + g * 32, b * d + kc * kKc);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_tf32(kTile, N) | (1u << 15);     // A is MN-major
+            int gs = 0, it = 0, sidx = -1, b_prev = -1;
+            for (int w = w_begin; w < w_end; ++w, ++it) {
+                const int b = w / P.n_tiles;
+                if (b != b_prev) {
+                    b_prev = b;
+                    ++sidx;
+                    mbar_wait(&s_full[sidx % nS], ((uint32_t)(sidx / nS)) & 1u);
+                }
+                const uint32_t s_addr = smem_u32(S_base + (size_t)(sidx % nS) * P.s_bytes);
+                const int buf = it & 1;
+                mbar_wait(&acc_free[buf], (((uint32_t)(it >> 1)) & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t t_acc = tmem_base + 128u * (uint32_t)buf;
+                for (int kc = 0; kc < nk; ++kc, ++gs) {
+                    const int s = gs % nst, l = gs % kBwdCLo;
+                    mbar_wait(&split_bar[l], ((uint32_t)(gs / kBwdCLo)) & 1u);
+                    tc_fence_after();
+                    const uint32_t a_hi = smem_u32(raw_base + (size_t)s * kTileBytes);
+                    const uint32_t a_lo = smem_u32(lo_base + (size_t)l * kTileBytes);
+                    const uint32_t b_hi = s_addr + (uint32_t)(kc * chunk_bytes);
+                    const uint32_t b_lo = s_addr + (uint32_t)((nk + kc) * chunk_bytes);
+                    const int ksteps = min(kKc, d - kc * kKc + 7) / 8;
+                    for (int k = 0; k < ((P.ablate & 1) ? 0 : ksteps); ++k) {
+                        const uint64_t dah = umma_desc_sw128_mn(a_hi + k * 1024, 4096), dal = umma_desc_sw128_mn(a_lo + k * 1024, 4096);
+                        const uint64_t dbh = umma_desc_sw128(b_hi + k * 32), dbl = umma_desc_sw128(b_lo + k * 32);
+                        umma_tf32(t_acc, dal, dbh, idesc, (kc | k) != 0);
+                        umma_tf32(t_acc, dah, dbl, idesc, 1);
+                        umma_tf32(t_acc, dah, dbh, idesc, 1);
+                    }
+                    umma_commit(&empty_bar[s]);
+                    umma_commit(&lo_free[l]);
+                }
+                umma_commit(&acc_full[buf]);
+                if (w + 1 == w_end || (w + 1) / P.n_tiles != b) umma_commit(&s_free[sidx % nS]);   // last tile of the sample here
+            }
+        }
+    } else if (warp < 2 + 4 * kBwdSplitGroups) {
+        const int ts = threadIdx.x - 64;                     // thread among all splitters (the S build is shared)
+        const int grp = ts >> 7, t = ts & 127;               // group and thread within it (a group owns the stages gs = grp mod 2)
+        int gs = 0, gg = 0, sidx = -1, b_prev = -1;
+        for (int w = w_begin; w < w_end; ++w) {
+            const int b = w / P.n_tiles, n0 = (w - b * P.n_tiles) * kTile;
+            const int ngrp = min(4, (P.n - n0 + 31) / 32);
+            if (b != b_prev) {
+                // S = g_G + g_G^T of the sample: hi | lo chunks in the operand layout; k >= d masked
+                b_prev = b;
+                ++sidx;
+                const int sb = sidx % nS;
+                mbar_wait(&s_free[sb], (((uint32_t)(sidx / nS)) & 1u) ^ 1u);
+                uint8_t* Sb = S_base + (size_t)sb * P.s_bytes;
+                for (int kc = 0; kc < nk; ++kc, ++gg) {
+                    const int gl = gg % ngl;
+                    mbar_wait(&g_full[gl], ((uint32_t)(gg / ngl)) & 1u);
+                    const uint8_t* X = gl_base + (size_t)gl * 2 * chunk_bytes;
+                    const float* Y = reinterpret_cast<const float*>(X + chunk_bytes);
+                    uint8_t* bh = Sb + (size_t)kc * chunk_bytes;
+                    uint8_t* bl = Sb + (size_t)(nk + kc) * chunk_bytes;
+                    const int kvalid = d - kc * kKc;
+                    for (int i = ts; i < ((P.ablate & 2) ? 0 : N * 8); i += 128 * kBwdSplitGroups) {
+                        const int c = i / N, j = i - c * N;  // lanes run along j: conflict-free everywhere
+                        const uint32_t off = (uint32_t)j * 128u + (((uint32_t)c ^ ((uint32_t)j & 7u)) << 4);
+                        float4 x = *reinterpret_cast<const float4*>(X + off);
+                        const int k = 4 * c;
+                        x.x = (k + 0 < kvalid) ? x.x + Y[(k + 0) * N + j] : 0.f;
+                        x.y = (k + 1 < kvalid) ? x.y + Y[(k + 1) * N + j] : 0.f;
+                        x.z = (k + 2 < kvalid) ? x.z + Y[(k + 2) * N + j] : 0.f;
+                        x.w = (k + 3 < kvalid) ? x.w + Y[(k + 3) * N + j] : 0.f;
+                        float4 h, l;
+                        split_tf32(x.x, h.x, l.x); split_tf32(x.y, h.y, l.y);
+                        split_tf32(x.z, h.z, l.z); split_tf32(x.w, h.w, l.w);
+                        *reinterpret_cast<float4*>(bh + off) = h;
+                        *reinterpret_cast<float4*>(bl + off) = l;
+                    }
+                    mbar_arrive(&g_free[gl]);
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(&s_full[sb]);
+            }
+            for (int kc = 0; kc < nk; ++kc, ++gs) {
+                if ((gs & (kBwdSplitGroups - 1)) != grp) continue;
+                const int s = gs % nst, l = gs % kBwdCLo;
+                mbar_wait(&full_bar[s], ((uint32_t)(gs / nst)) & 1u);
+                mbar_wait(&lo_free[l], (((uint32_t)(gs / kBwdCLo)) & 1u) ^ 1u);
+                float4* raw = reinterpret_cast<float4*>(raw_base + (size_t)s * kTileBytes);
+                float4* lo = reinterpret_cast<float4*>(lo_base + (size_t)l * kTileBytes);
+                // the n groups that hold data (the others feed output rows that are never stored)
+#pragma unroll 4
+                for (int i = t; i < ((P.ablate & 4) ? 0 : ngrp * 256); i += 128) {
+                    const float4 v = raw[i];
+                    float4 h, w4;
+                    split_tf32(v.x, h.x, w4.x); split_tf32(v.y, h.y, w4.y);
+                    split_tf32(v.z, h.z, w4.z); split_tf32(v.w, h.w, w4.w);
+                    lo[i] = w4;
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(&split_bar[l]);
+            }
+        }
+    } else {
+        // epilogue warps (any four consecutive warps cover the four TMEM lane quarters): TMEM lane = n, column = j; every store of a warp is one 128-byte line
+        const int q = warp & 3;
+        const int ew = (warp - (2 + 4 * kBwdSplitGroups)) >> 2;   // which of the quarter's warps
+        int it = 0;
+        for (int w = w_begin; w < w_end; ++w, ++it) {
+            const int b = w / P.n_tiles, n0 = (w - b * P.n_tiles) * kTile;
+            const int buf = it & 1;
+            mbar_wait(&acc_full[buf], ((uint32_t)(it >> 1)) & 1u);
+            tc_fence_after();
+            const int nn = n0 + q * 32 + lane;
+            float* Ob = P.gV + (size_t)b * d * P.n;
+            const bool live = n0 + q * 32 < P.n;             // warp-uniform
+            for (int c0 = 32 * ew; c0 < N; c0 += 32 * (kBwdEpiWarps / 4)) {
+                if (live) {
+                    float v[32];
+                    tmem_ld_32x32(tmem_base + 128u * (uint32_t)buf + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+                    if (nn < P.n && !(P.ablate & 8)) {
+#pragma unroll
+                        for (int u = 0; u < 32; ++u)
+                            if (c0 + u < d) Ob[(size_t)(c0 + u) * P.n + nn] = v[u];
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&acc_free[buf]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kBwdPTmemCols>(tmem_base);
+    }
+}
+
 bool gram_tc_bwd_usable(int B, int d, int n, const float* V, const float* gG, const float* gV) {
     return B > 0 && d >= 16 && (d & 3) == 0 && n >= kKc && (n & 3) == 0 && aligned16(V) && aligned16(gG) && gV &&
            (long long)B * d < (1LL << 31);
@@ -580,6 +834,30 @@ int gram_tc_bwd_launch(int B, int d, int n, const float* V, const float* gG, flo
     if (rc != 0) return rc;
     rc = make_tmap_2d_plain_f32(&tmapY, gG, (uint64_t)B * d, (uint64_t)d, (uint64_t)d, (uint32_t)P.N, 32);
     if (rc != 0) return rc;
+    static const bool persist_off = [] { const char* e = getenv("CMF_GRAM_BWD_PERSIST"); return e && e[0] == '0'; }();
+    if (P.j_tiles == 1 && !persist_off) {
+        static const int ablate_env = [] { const char* e = getenv("CMF_GRAM_BWD_ABLATE"); return e ? atoi(e) : 0; }();
+        GramBwdCParams C{};
+        C.B = B; C.d = d; C.n = n; C.n_tiles = P.n_tiles; C.N = P.N; C.nk = (int)ceil_div(d, kKc);
+        C.s_bytes = 2 * C.nk * C.N * 128;
+        C.nS = d <= 64 ? 2 : 1;
+        C.ngl = d <= 64 ? 2 : 1;
+        C.ablate = ablate_env; C.gV = gV;
+        const long long fixed = (long long)C.nS * C.s_bytes + (long long)C.ngl * 2 * C.N * 128 + (long long)kBwdCLo * kTileBytes;
+        C.nst = (int)min((long long)kMaxStages, (225LL * 1024 - fixed) / kTileBytes);
+        CMF_REQUIRE(C.nst >= 2, "gram_tc_bwd: no room for the V ring (d=%d)", d);
+        const size_t smem_c = (size_t)fixed + (size_t)C.nst * kTileBytes + 1024;
+        static DeviceOnce attr_set_c;
+        if (!attr_set_c.done()) {
+            cudaError_t e = cudaFuncSetAttribute(gram_tc_bwd_cached_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+            if (e != cudaSuccess) { set_error("gram_tc_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
+            attr_set_c.mark();
+        }
+        const unsigned ctas = (unsigned)min(grid, (long long)kNumSMs);
+        gram_tc_bwd_cached_kernel<<<ctas, kBwdPThreads, smem_c, stream>>>(tmap, tmapX, tmapY, C);
+        CMF_CHECK_LAUNCH();
+        return 0;
+    }
     const size_t smem = (size_t)P.nstages * P.stage_bytes + 1024;
     static DeviceOnce attr_set;
     if (!attr_set.done()) {
