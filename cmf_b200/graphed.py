@@ -18,12 +18,17 @@ Contract
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Dict, Tuple
 
 import torch
 
 from . import ops
 from .parallel import GradientBucket
+
+
+# CMF_GRAPH_STEAL_GRADS=0: accumulate into the zeroed bucket inside the graph (one add kernel per parameter) instead
+_STEAL_GRADS = os.environ.get("CMF_GRAPH_STEAL_GRADS", "1") != "0"
 
 
 class GraphedTrainStep:
@@ -53,9 +58,15 @@ class GraphedTrainStep:
         graph = torch.cuda.CUDAGraph()
         with ops.defer_pd_check() as pending:
             with torch.cuda.graph(graph):
-                self.bucket.flat.zero_()
+                if _STEAL_GRADS:
+                    for p in self.bucket.params:      # autograd keeps the incoming tensors: no per-parameter add kernels
+                        p.grad = None
+                else:
+                    self.bucket.flat.zero_()
                 loss = self.train_metrics(self.density, static_x, epoch)["loss"]
                 loss.backward()
+                if _STEAL_GRADS:
+                    self.bucket.gather_fresh()        # one multi-tensor copy into bucket.flat
                 static_loss = loss.detach()
             infos = list(pending)
         info_all = torch.stack([i.view(()) for i in infos]) if infos else None

@@ -150,3 +150,27 @@ def test_hutch_cg_on_explicit_gram_cpu(emu, monkeypatch):
     density = build_product(g)
     loss, grads = run_loss(g, density)
     check_against_golden(g, loss, grads, rtol=1e-4)
+
+
+def test_gradient_bucket_gathers_fresh_gradients():
+    """GradientBucket.gather_fresh (the CUDA-graph capture's way of filling the bucket): gradients that autograd
+    allocated itself are copied into their slices, parameters without a gradient get zeros, views are restored."""
+    from cmf_b200.parallel import GradientBucket
+    torch.manual_seed(0)
+    lin, unused = torch.nn.Linear(5, 3), torch.nn.Linear(2, 2)
+    params = list(lin.parameters()) + list(unused.parameters())
+    bucket = GradientBucket(params)
+    bucket.flat.fill_(7.0)                                    # stale content must not survive
+    for p in params:
+        p.grad = None
+    x = torch.randn(4, 5)
+    lin(x).square().sum().backward()
+    want = torch.cat([lin.weight.grad.flatten(), lin.bias.grad.flatten(), torch.zeros(6)])
+    bucket.gather_fresh()
+    assert torch.equal(bucket.flat, want)
+    off = 0
+    for p in params:
+        assert p.grad.data_ptr() == bucket.flat[off:].data_ptr() and p.grad.shape == p.shape
+        off += p.numel()
+    bucket.gather_fresh()                                     # already aliased: nothing to copy, nothing changes
+    assert torch.equal(bucket.flat, want)
