@@ -571,41 +571,52 @@ gram_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
 // ------------------------------------------------------------------------------------------------
 // Persistent adjoint for d <= 128 (one j tile).  A work item is (sample, 128-wide n tile) with only ceil(d / 32) K
 // stages, so a CTA per item (the kernel above, still used for d > 128) spends its life in the prologue (barrier init,
-// TMEM allocation, first TMA round trip) and the epilogue: ~8 us per wave of 148 CTAs, 14 waves at B = 512, n = 392.
-// Here one CTA per SM walks a contiguous range of items:
+// TMEM allocation, first TMA round trip) and the epilogue: ~8 us per wave of 148 CTAs, 14 waves at B = 512, n = 392
+// (110 us; the FP32 FMA kernel needs 59).  Here one CTA per SM walks a contiguous range of items:
 //   * B operand: S = g_G + g_G^T (hi | lo, K-major 128B-swizzled chunks of 32 k) is built ONCE per sample into one of
 //     nS buffers from X / Y tiles that land in a small ring of their own, and is reused by the sample's n tiles;
-//   * A operand: a ring stage is the raw 16 KB V tile (= hi: the tensor core reads the top 19 bits of a word), lo goes
-//     to a 2-deep ring that spans split -> MMA; two split groups of four warps take alternate stages (a stage's split
-//     is a ~600-cycle latency chain for one warp per scheduler, and was the longest per-item chain with one group);
-//   * the accumulator is double-buffered in TMEM (2 x 128 columns): eight epilogue warps write item i while the
-//     splitters and the tensor core work on item i + 1.
-// Measured (scripts/gram_probe.py, B = 512, d = 64, n = 392): CTA per item 110 us, FP32 FMA kernel 59 us, this kernel
-// see profiles/r02_summary.md.  Not kept: cp.async.bulk.prefetch of the V boxes ahead of the ring (slower: the TMA
-// unit, not the DRAM latency, paces the 4 KB boxes).
+//   * A operand: the V tile goes to TENSOR MEMORY.  A first persistent form kept it in shared memory (MN-major SS-mode
+//     MMAs, four swizzled 4 KB TMA boxes per stage): 43 us, paced by its MMAs -- 24 per item at ~86 cycles, each
+//     reading 4 KB of A + 2 KB of B from shared memory, every V tile three times (lo S_hi, hi S_lo, hi S_hi).  Now, as
+//     in the convolution kernels, a split thread owns one TMEM lane (= one n position): it reads its column of the
+//     landed [32 k][128 n] tile (plain row-major: ONE 16 KB TMA box per stage), splits it and writes hi | lo into a
+//     staging slot of tensor memory with tcgen05.st; the MMAs read only the S chunks (2 KB) from shared memory.  The
+//     ring stage is free as soon as the split warps have read it; there is no lo ring and no MN-major descriptor;
+//   * two MMA issuers (even / odd items = accumulator 0 / 1, each with its own pair of staging slots): one thread
+//     issues a tcgen05.mma per ~50-80 cycles, more than the 32 cycles an M = 128, N = 64 MMA occupies the tensor pipe;
+//   * the accumulator pair is double-buffered in TMEM: eight epilogue warps take item i while item i + 1 is split and
+//     multiplied; for d <= 64 they stage the [d][128] tile in shared memory and ONE TMA store writes it (columns past
+//     n are dropped by the tensor map), for larger d (no room for the staging pair) they store 128-byte lines.
+// Measured (scripts/gram_probe.py, B = 512, d = 64, n = 392, us): CTA per item 110, FMA 59, SS-mode persistent 43,
+// V in TMEM 41, + second issuer 36, + TMA store 30.  Not kept: cp.async.bulk.prefetch of the V boxes ahead of the ring.
 // ------------------------------------------------------------------------------------------------
 constexpr int kBwdSplitGroups = 2;
 constexpr int kBwdEpiWarps = 8;        // two per TMEM lane quarter (even / odd 32-column chunks of the accumulator): the
-                                       // epilogue is a latency chain per warp, 4 warps 48 us, 8 warps 43 us, 16 warps x 16 columns 44.5 us
+                                       // epilogue is a latency chain per warp (4 warps 48 us, 8 warps 43 us, 16 x 16 columns 44.5 us)
 constexpr int kBwdPThreads = 32 * (2 + 4 * kBwdSplitGroups + kBwdEpiWarps);   // TMA, MMA, 2 x 4 split warps, epilogue warps
-constexpr int kBwdPTmemCols = 256;
 
 struct GramBwdCParams {
     int B, d, n, n_tiles, N, nk;
-    int nst;            // raw V stages (16 KB each)
+    int nst;            // raw V stages (16 KB each; even, see the split warps)
     int nS, ngl;        // S buffers, landing slots for the X / Y tiles
     int s_bytes;        // one S buffer: 2 * nk * N * 128
-    int ablate;         // timing experiments (CMF_GRAM_BWD_ABLATE): 1 no MMA, 2 no S build, 4 no A split, 8 no stores
+    int ablate;         // timing experiments (CMF_GRAM_BWD_ABLATE): 1 no MMA, 2 no S build, 4 no V split, 8 no stores
+    int tma_out;        // g_V leaves through a staged tile and TMA stores (d <= 64: there is room for the staging pair)
     float* gV;
 };
-constexpr int kBwdCLo = 2;
 
-__global__ void __launch_bounds__(kBwdPThreads, 1)
-gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapX,
-                          const __grid_constant__ CUtensorMap tmapY, const GramBwdCParams P) {
+constexpr int kBwdTsTmemCols = 512;   // [0, 256) two accumulators of <= 128 columns, [256, 512) per issuer 2 x (32 hi | 32 lo) staging
+constexpr uint32_t kBwdTsStg = 256;
+constexpr int kBwdTsIssuer2 = 2 + 4 * kBwdSplitGroups + kBwdEpiWarps;   // the second MMA issuer is the last warp
+constexpr int kBwdTsThreads = kBwdPThreads + 32;
+
+__global__ void __launch_bounds__(kBwdTsThreads, 1)
+gram_tc_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapX,
+                      const __grid_constant__ CUtensorMap tmapY, const __grid_constant__ CUtensorMap tmapO,
+                      const GramBwdCParams P) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages];
-    __shared__ __align__(8) uint64_t split_bar[kBwdCLo], lo_free[kBwdCLo], g_full[2], g_free[2], s_full[2], s_free[2];
+    __shared__ __align__(8) uint64_t a_full[4], a_free[4], g_full[2], g_free[2], s_full[2], s_free[2];
     __shared__ __align__(8) uint64_t acc_full[2], acc_free[2];
     __shared__ uint32_t tmem_base_smem;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -613,25 +624,27 @@ gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid
     const int d = P.d, N = P.N, nst = P.nst, nk = P.nk, nS = P.nS, ngl = P.ngl;
     const long long total = (long long)P.B * P.n_tiles;
     const int w_begin = (int)(total * blockIdx.x / gridDim.x), w_end = (int)(total * (blockIdx.x + 1) / gridDim.x);
-    // shared-memory map: S buffers | X/Y landing slots | lo ring | raw ring
-    const int chunk_bytes = N * 128;                          // one hi (or lo) chunk of S; X and Y are as large
+    // shared-memory map: S buffers | X/Y landing slots | raw ring
+    const int chunk_bytes = N * 128;
     uint8_t* S_base = smem;
     uint8_t* gl_base = S_base + (size_t)nS * P.s_bytes;
-    uint8_t* lo_base = gl_base + (size_t)ngl * 2 * chunk_bytes;
-    uint8_t* raw_base = lo_base + (size_t)kBwdCLo * kTileBytes;
+    uint8_t* out_base = gl_base + (size_t)ngl * 2 * chunk_bytes;          // tma_out: 2 x [d][128] output tiles
+    uint8_t* raw_base = out_base + (P.tma_out ? (size_t)2 * d * kTile * 4 : 0);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nst; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], 128);
+        }
+        for (int i = 0; i < 4; ++i) {           // staging ring of issuer i / 2, slot i % 2
+            mbar_init(&a_full[i], 128);
+            mbar_init(&a_free[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
-            mbar_init(&split_bar[i], 128);
-            mbar_init(&lo_free[i], 1);
             mbar_init(&g_full[i], 1);
             mbar_init(&g_free[i], 128 * kBwdSplitGroups);
             mbar_init(&s_full[i], 128 * kBwdSplitGroups);
-            mbar_init(&s_free[i], 1);
+            mbar_init(&s_free[i], 2);
             mbar_init(&acc_full[i], 1);
             mbar_init(&acc_free[i], 32 * kBwdEpiWarps);
         }
@@ -639,8 +652,9 @@ gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid
         prefetch_tmap(&tmap);
         prefetch_tmap(&tmapX);
         prefetch_tmap(&tmapY);
+        if (P.tma_out) prefetch_tmap(&tmapO);
     }
-    if (warp == 1) tmem_alloc<kBwdPTmemCols>(&tmem_base_smem);
+    if (warp == 1) tmem_alloc<kBwdTsTmemCols>(&tmem_base_smem);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -651,7 +665,6 @@ gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid
             int gs = 0, gg = 0, b_prev = -1;
             for (int w = w_begin; w < w_end; ++w) {
                 const int b = w / P.n_tiles, n0 = (w - b * P.n_tiles) * kTile;
-                const int ngrp = min(4, (P.n - n0 + 31) / 32);      // 32-wide n groups that hold data
                 if (b != b_prev) {                                   // the sample's g_G tiles, one landing slot per chunk
                     b_prev = b;
                     for (int kc = 0; kc < nk; ++kc, ++gg) {
@@ -666,59 +679,67 @@ gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid
                 for (int kc = 0; kc < nk; ++kc, ++gs) {
                     const int s = gs % nst;
                     mbar_wait(&empty_bar[s], (((uint32_t)(gs / nst)) & 1u) ^ 1u);
-                    uint8_t* st = raw_base + (size_t)s * kTileBytes;
-                    mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(ngrp * 4096));
-                    for (int g = 0; g < ngrp; ++g)
-                        tma_load_2d(st + g * 4096, &tmap, &full_bar[s], n0 + g * 32, b * d + kc * kKc);
+                    mbar_arrive_expect_tx(&full_bar[s], (uint32_t)kTileBytes);
+                    tma_load_2d(raw_base + (size_t)s * kTileBytes, &tmap, &full_bar[s], n0, b * d + kc * kKc);
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == kBwdTsIssuer2) {
+        // two issuers (even / odd items = accumulator 0 / 1): a single thread issues one tcgen05.mma per ~50-80 cycles,
+        // more than the 32 cycles an M = 128, N = 64 MMA occupies the tensor pipe
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_tf32(kTile, N) | (1u << 15);     // A is MN-major
-            int gs = 0, it = 0, sidx = -1, b_prev = -1;
+            const int me = warp == 1 ? 0 : 1;
+            const uint32_t idesc = umma_idesc_tf32(kTile, N);
+            int it = 0, sidx = -1, b_prev = -1;
+            bool mine_in_sample = false;
             for (int w = w_begin; w < w_end; ++w, ++it) {
                 const int b = w / P.n_tiles;
                 if (b != b_prev) {
                     b_prev = b;
                     ++sidx;
-                    mbar_wait(&s_full[sidx % nS], ((uint32_t)(sidx / nS)) & 1u);
+                    mine_in_sample = false;
                 }
-                const uint32_t s_addr = smem_u32(S_base + (size_t)(sidx % nS) * P.s_bytes);
-                const int buf = it & 1;
-                mbar_wait(&acc_free[buf], (((uint32_t)(it >> 1)) & 1u) ^ 1u);
-                tc_fence_after();
-                const uint32_t t_acc = tmem_base + 128u * (uint32_t)buf;
-                for (int kc = 0; kc < nk; ++kc, ++gs) {
-                    const int s = gs % nst, l = gs % kBwdCLo;
-                    mbar_wait(&split_bar[l], ((uint32_t)(gs / kBwdCLo)) & 1u);
-                    tc_fence_after();
-                    const uint32_t a_hi = smem_u32(raw_base + (size_t)s * kTileBytes);
-                    const uint32_t a_lo = smem_u32(lo_base + (size_t)l * kTileBytes);
-                    const uint32_t b_hi = s_addr + (uint32_t)(kc * chunk_bytes);
-                    const uint32_t b_lo = s_addr + (uint32_t)((nk + kc) * chunk_bytes);
-                    const int ksteps = min(kKc, d - kc * kKc + 7) / 8;
-                    for (int k = 0; k < ((P.ablate & 1) ? 0 : ksteps); ++k) {
-                        const uint64_t dah = umma_desc_sw128_mn(a_hi + k * 1024, 4096), dal = umma_desc_sw128_mn(a_lo + k * 1024, 4096);
-                        const uint64_t dbh = umma_desc_sw128(b_hi + k * 32), dbl = umma_desc_sw128(b_lo + k * 32);
-                        umma_tf32(t_acc, dal, dbh, idesc, (kc | k) != 0);
-                        umma_tf32(t_acc, dah, dbl, idesc, 1);
-                        umma_tf32(t_acc, dah, dbh, idesc, 1);
+                const int sb = sidx % nS;
+                if ((it & 1) == me) {
+                    if (!mine_in_sample) mbar_wait(&s_full[sb], ((uint32_t)(sidx / nS)) & 1u);
+                    mine_in_sample = true;
+                    const uint32_t s_addr = smem_u32(S_base + (size_t)sb * P.s_bytes);
+                    mbar_wait(&acc_free[me], (((uint32_t)(it >> 1)) & 1u) ^ 1u);
+                    const uint32_t t_acc = tmem_base + 128u * (uint32_t)me;
+                    for (int kc = 0; kc < nk; ++kc) {
+                        const int par = kc & 1, ab = 2 * me + par;       // staging slot; u = how often it was used before
+                        const int u = (it >> 1) * ((nk + 1 - par) >> 1) + (kc >> 1);
+                        mbar_wait(&a_full[ab], (uint32_t)u & 1u);
+                        tc_fence_after();
+                        const uint32_t a_hi = tmem_base + kBwdTsStg + 64u * (uint32_t)ab, a_lo = a_hi + 32u;
+                        const uint64_t dbh = umma_desc_sw128(s_addr + (uint32_t)(kc * chunk_bytes));
+                        const uint64_t dbl = umma_desc_sw128(s_addr + (uint32_t)((nk + kc) * chunk_bytes));
+                        const int ksteps = min(kKc, d - kc * kKc + 7) / 8;
+                        for (int k = 0; k < ((P.ablate & 1) ? 0 : ksteps); ++k) {   // +32 bytes along K = +2 in the address field
+                            umma_tf32_ts(t_acc, a_hi + k * 8, dbl + 2 * k, idesc, (kc | k) != 0);
+                            umma_tf32_ts(t_acc, a_lo + k * 8, dbh + 2 * k, idesc, 1);
+                            umma_tf32_ts(t_acc, a_hi + k * 8, dbh + 2 * k, idesc, 1);
+                        }
+                        umma_commit(&a_free[ab]);
                     }
-                    umma_commit(&empty_bar[s]);
-                    umma_commit(&lo_free[l]);
+                    umma_commit(&acc_full[me]);
                 }
-                umma_commit(&acc_full[buf]);
-                if (w + 1 == w_end || (w + 1) / P.n_tiles != b) umma_commit(&s_free[sidx % nS]);   // last tile of the sample here
+                // end of the sample's tiles in this CTA: both issuers release the S buffer, each after its own MMAs
+                if (w + 1 == w_end || (w + 1) / P.n_tiles != b) {
+                    if (mine_in_sample) umma_commit(&s_free[sb]); else mbar_arrive(&s_free[sb]);
+                }
             }
         }
     } else if (warp < 2 + 4 * kBwdSplitGroups) {
         const int ts = threadIdx.x - 64;                     // thread among all splitters (the S build is shared)
-        const int grp = ts >> 7, t = ts & 127;               // group and thread within it (a group owns the stages gs = grp mod 2)
-        int gs = 0, gg = 0, sidx = -1, b_prev = -1;
-        for (int w = w_begin; w < w_end; ++w) {
+        const int grp = ts >> 7;                             // group g owns the stages gs = g mod 2
+        const int q = warp & 3;                              // TMEM lane quarter of this warp
+        const int nl = q * 32 + lane;                        // n position within the tile = TMEM lane
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        int gs = 0, gg = 0, sidx = -1, b_prev = -1, it = 0;
+        for (int w = w_begin; w < w_end; ++w, ++it) {
             const int b = w / P.n_tiles, n0 = (w - b * P.n_tiles) * kTile;
-            const int ngrp = min(4, (P.n - n0 + 31) / 32);
+            const bool live = n0 + q * 32 < P.n;             // warp-uniform: this quarter holds data
             if (b != b_prev) {
                 // S = g_G + g_G^T of the sample: hi | lo chunks in the operand layout; k >= d masked
                 b_prev = b;
@@ -756,28 +777,41 @@ gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid
             }
             for (int kc = 0; kc < nk; ++kc, ++gs) {
                 if ((gs & (kBwdSplitGroups - 1)) != grp) continue;
-                const int s = gs % nst, l = gs % kBwdCLo;
+                const int s = gs % nst;
+                // staging slot (issuer it & 1, parity of kc) and its use count: with an even ring depth a ring slot, and with
+                // this slot rule a staging slot, is always served by the same split group, so every barrier is waited on in
+                // phase order by one group (a waiter two phases ahead would pass on the parity of the phase before)
+                const int par = kc & 1, ab = 2 * (it & 1) + par;
+                const int u = (it >> 1) * ((nk + 1 - par) >> 1) + (kc >> 1);
                 mbar_wait(&full_bar[s], ((uint32_t)(gs / nst)) & 1u);
-                mbar_wait(&lo_free[l], (((uint32_t)(gs / kBwdCLo)) & 1u) ^ 1u);
-                float4* raw = reinterpret_cast<float4*>(raw_base + (size_t)s * kTileBytes);
-                float4* lo = reinterpret_cast<float4*>(lo_base + (size_t)l * kTileBytes);
-                // the n groups that hold data (the others feed output rows that are never stored)
-#pragma unroll 4
-                for (int i = t; i < ((P.ablate & 4) ? 0 : ngrp * 256); i += 128) {
-                    const float4 v = raw[i];
-                    float4 h, w4;
-                    split_tf32(v.x, h.x, w4.x); split_tf32(v.y, h.y, w4.y);
-                    split_tf32(v.z, h.z, w4.z); split_tf32(v.w, h.w, w4.w);
-                    lo[i] = w4;
+                const float* raw = reinterpret_cast<const float*>(raw_base + (size_t)s * kTileBytes) + nl;   // [32 k][128 n]
+                float hi[32], lo[32];
+                if (live && !(P.ablate & 4)) {
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) {
+                        const float v = raw[k * kTile];
+                        split_tf32(v, hi[k], lo[k]);
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 32; ++k) hi[k] = lo[k] = 0.f;
                 }
-                fence_proxy_async_smem();
-                mbar_arrive(&split_bar[l]);
+                mbar_arrive(&empty_bar[s]);                  // the values are in registers: the ring stage may be refilled
+                mbar_wait(&a_free[ab], ((uint32_t)u & 1u) ^ 1u);
+                tc_fence_after();
+                const uint32_t stg = tmem_base + kBwdTsStg + 64u * (uint32_t)ab + lane_addr;
+                tmem_st_32x32(stg, hi);
+                tmem_st_32x32(stg + 32u, lo);
+                tmem_st_wait();
+                tc_fence_before();
+                mbar_arrive(&a_full[ab]);
             }
         }
-    } else {
-        // epilogue warps (any four consecutive warps cover the four TMEM lane quarters): TMEM lane = n, column = j; every store of a warp is one 128-byte line
+    } else if (warp < kBwdTsIssuer2) {
+        // epilogue warps (any four consecutive warps cover the four TMEM lane quarters): TMEM lane = n
         const int q = warp & 3;
         const int ew = (warp - (2 + 4 * kBwdSplitGroups)) >> 2;   // which of the quarter's warps
+        const bool elected = warp == 2 + 4 * kBwdSplitGroups && lane == 0;
         int it = 0;
         for (int w = w_begin; w < w_end; ++w, ++it) {
             const int b = w / P.n_tiles, n0 = (w - b * P.n_tiles) * kTile;
@@ -785,28 +819,54 @@ gram_tc_bwd_cached_kernel(const __grid_constant__ CUtensorMap tmap, const __grid
             mbar_wait(&acc_full[buf], ((uint32_t)(it >> 1)) & 1u);
             tc_fence_after();
             const int nn = n0 + q * 32 + lane;
-            float* Ob = P.gV + (size_t)b * d * P.n;
             const bool live = n0 + q * 32 < P.n;             // warp-uniform
-            for (int c0 = 32 * ew; c0 < N; c0 += 32 * (kBwdEpiWarps / 4)) {
-                if (live) {
-                    float v[32];
-                    tmem_ld_32x32(tmem_base + 128u * (uint32_t)buf + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-                    if (nn < P.n && !(P.ablate & 8)) {
+            if (P.tma_out) {
+                // accumulator -> registers -> staged [d][128] tile -> one TMA store (columns past n are dropped by the
+                // tensor map): the warps are done with the item after 32 shared-memory stores instead of 32 global ones
+                float v[32];
+                const int c0 = 32 * ew;                       // d <= 64: one 32-column chunk per warp
+                const bool has = live && c0 < N;
+                if (has) tmem_ld_32x32(tmem_base + 128u * (uint32_t)buf + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+                tc_fence_before();
+                mbar_arrive(&acc_free[buf]);                  // the accumulator is in registers
+                float* stg = reinterpret_cast<float*>(out_base + (size_t)buf * d * kTile * 4) + q * 32 + lane;
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * kBwdEpiWarps) : "memory");   // the store two items back has read this tile
+                if (has && !(P.ablate & 8)) {
 #pragma unroll
-                        for (int u = 0; u < 32; ++u)
-                            if (c0 + u < d) Ob[(size_t)(c0 + u) * P.n + nn] = v[u];
+                    for (int u = 0; u < 32; ++u)
+                        if (c0 + u < d) stg[(c0 + u) * kTile] = v[u];
+                }
+                fence_proxy_async_smem();
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * kBwdEpiWarps) : "memory");
+                if (elected) {
+                    if (!(P.ablate & 8)) tma_store_2d(&tmapO, out_base + (size_t)buf * d * kTile * 4, n0, b * d);
+                    bulk_commit();
+                    bulk_wait_read<1>();                      // the other tile (next item's) is free again
+                }
+            } else {
+                float* Ob = P.gV + (size_t)b * d * P.n;
+                for (int c0 = 32 * ew; c0 < N; c0 += 32 * (kBwdEpiWarps / 4)) {
+                    if (live) {
+                        float v[32];
+                        tmem_ld_32x32(tmem_base + 128u * (uint32_t)buf + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+                        if (nn < P.n && !(P.ablate & 8)) {
+#pragma unroll
+                            for (int u = 0; u < 32; ++u)
+                                if (c0 + u < d) Ob[(size_t)(c0 + u) * P.n + nn] = v[u];
+                        }
                     }
                 }
+                tc_fence_before();
+                mbar_arrive(&acc_free[buf]);
             }
-            tc_fence_before();
-            mbar_arrive(&acc_free[buf]);
         }
+        if (P.tma_out && elected) bulk_wait_all();
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<kBwdPTmemCols>(tmem_base);
+        tmem_dealloc<kBwdTsTmemCols>(tmem_base);
     }
 }
 
@@ -837,24 +897,34 @@ int gram_tc_bwd_launch(int B, int d, int n, const float* V, const float* gG, flo
     static const bool persist_off = [] { const char* e = getenv("CMF_GRAM_BWD_PERSIST"); return e && e[0] == '0'; }();
     if (P.j_tiles == 1 && !persist_off) {
         static const int ablate_env = [] { const char* e = getenv("CMF_GRAM_BWD_ABLATE"); return e ? atoi(e) : 0; }();
+        static const bool tma_out_off = [] { const char* e = getenv("CMF_GRAM_BWD_TMA_OUT"); return e && e[0] == '0'; }();
         GramBwdCParams C{};
         C.B = B; C.d = d; C.n = n; C.n_tiles = P.n_tiles; C.N = P.N; C.nk = (int)ceil_div(d, kKc);
         C.s_bytes = 2 * C.nk * C.N * 128;
         C.nS = d <= 64 ? 2 : 1;
         C.ngl = d <= 64 ? 2 : 1;
         C.ablate = ablate_env; C.gV = gV;
-        const long long fixed = (long long)C.nS * C.s_bytes + (long long)C.ngl * 2 * C.N * 128 + (long long)kBwdCLo * kTileBytes;
-        C.nst = (int)min((long long)kMaxStages, (225LL * 1024 - fixed) / kTileBytes);
+        C.tma_out = d <= 64 && !tma_out_off;
+        CUtensorMap tmapV;                   // plain [32 k][128 n] boxes
+        rc = make_tmap_2d_plain_f32(&tmapV, V, (uint64_t)B * d, (uint64_t)n, (uint64_t)n, kTile, kKc);
+        if (rc != 0) return rc;
+        CUtensorMap tmapO = tmapV;           // g_V as [d rows][128 n] boxes of one sample (never crosses into the next one)
+        if (C.tma_out) {
+            rc = make_tmap_2d_plain_f32(&tmapO, gV, (uint64_t)B * d, (uint64_t)n, (uint64_t)n, kTile, (uint32_t)d);
+            if (rc != 0) return rc;
+        }
+        const long long fixed = (long long)C.nS * C.s_bytes + (long long)C.ngl * 2 * C.N * 128 + (C.tma_out ? 2LL * d * kTile * 4 : 0);
+        C.nst = (int)min((long long)kMaxStages, (225LL * 1024 - fixed) / kTileBytes) & ~1;   // even: see the split warps
         CMF_REQUIRE(C.nst >= 2, "gram_tc_bwd: no room for the V ring (d=%d)", d);
-        const size_t smem_c = (size_t)fixed + (size_t)C.nst * kTileBytes + 1024;
-        static DeviceOnce attr_set_c;
-        if (!attr_set_c.done()) {
-            cudaError_t e = cudaFuncSetAttribute(gram_tc_bwd_cached_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+        const size_t smem_ts = (size_t)fixed + (size_t)C.nst * kTileBytes + 1024;
+        static DeviceOnce attr_set_ts;
+        if (!attr_set_ts.done()) {
+            cudaError_t e = cudaFuncSetAttribute(gram_tc_bwd_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
             if (e != cudaSuccess) { set_error("gram_tc_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-            attr_set_c.mark();
+            attr_set_ts.mark();
         }
         const unsigned ctas = (unsigned)min(grid, (long long)kNumSMs);
-        gram_tc_bwd_cached_kernel<<<ctas, kBwdPThreads, smem_c, stream>>>(tmap, tmapX, tmapY, C);
+        gram_tc_bwd_ts_kernel<<<ctas, kBwdTsThreads, smem_ts, stream>>>(tmapV, tmapX, tmapY, tmapO, C);
         CMF_CHECK_LAUNCH();
         return 0;
     }

@@ -28,6 +28,7 @@ for H in (28, 14):
     for name, fn in [("plain", lambda: K.conv3x3_c64(x, ws, None, out=y)),
                      ("mask", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=64, mask_first=True, out=y)),
                      ("mask+res+second", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=64, res=res, second=True, out=y, out2=y2)),
+                     ("mask drain2", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=64, mask_first=True, drain=2, out=y)),
                      ("mask+res drain2", lambda: K.conv3x3_c64(x, ws, None, mask_src=bits, mask_div=64, mask_first=True, res=res, drain=2, out=y))]:
         ms = timed(fn)
         out[f"{H}x{H} {name}"] = (round(ms, 4), round(fl / ms / 1e9, 1))

@@ -145,6 +145,19 @@ def test_gram_tc_matches_fp64_and_fma(B, d, n):
     _close(g_tc, K.gram_bwd(Vd, gG.float().to(DEV), path="fma"), rtol=1e-5, what="g_V tc vs fma")
 
 
+@pytest.mark.parametrize("B,d,n", [(300, 64, 392), (200, 96, 392), (260, 128, 260), (400, 32, 200), (180, 72, 520), (700, 16, 136)])
+def test_gram_bwd_persistent_kernel_many_items_per_cta(B, d, n):
+    """The persistent tcgen05 adjoint (d <= 128) with several (sample, n tile) items per CTA: every ring (V stages, the
+    per-sample S buffers, the TMEM staging slots of the two issuers, the accumulator pair) wraps many times; odd and even
+    numbers of K stages per item (d = 96, 72: three), ragged last tiles, d not a multiple of 32.  Twice: the same bits."""
+    import cmf_b200.kernels as K
+    V, gG = _rand(B, d, n, seed=21), _rand(B, d, d, seed=22)
+    Vd, gd = V.float().to(DEV), gG.float().to(DEV)
+    got = K.gram_bwd(Vd, gd, path="tc")
+    _close(got, E.gram_bwd(V, gG), rtol=1e-5, what="g_V persistent")
+    assert torch.equal(got, K.gram_bwd(Vd, gd, path="tc")), "not reproducible"
+
+
 @pytest.mark.parametrize("B,d,n1,n2", [(5, 64, 392, 392), (3, 64, 392, 40), (2, 200, 36, 260), (9, 48, 100, 32),
                                        (3, 64, 392, 8), (2, 6, 12, 20), (4, 130, 64, 64)])
 def test_gram_two_blocks_in_one_launch(B, d, n1, n2):
