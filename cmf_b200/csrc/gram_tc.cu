@@ -291,6 +291,228 @@ gram_tc_fwd_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
 }
 
 // ------------------------------------------------------------------------------------------------
+// Panel form of the forward kernel for d <= 128: persistent, A operand in tensor memory.
+// The kernel above is bound by shared-memory wavefronts (per K = 32 stage: 64 KB of SS-mode operand reads, the split's
+// 16 KB read + 16 KB write, TMA's 16 KB) and pays ~10 us of prologue + epilogue per wave of 148 CTAs.  Here
+//   * a split thread owns one row of the panel (= one TMEM lane): it reads its 128 bytes of the landed, swizzled tile,
+//     and writes hi | lo into a staging slot of tensor memory (tcgen05.st); the MMAs take A from there and only B (the
+//     landed tile itself = hi, 4 KB per MMA) from shared memory: hi hi^T into the ping-pong accumulator, lo hi^T into
+//     the cross accumulator (the transpose is added in the epilogue) -- 48 KB of shared-memory traffic per stage;
+//   * one CTA per SM walks the panels blockIdx.x, blockIdx.x + gridDim.x, ...: all rings keep rolling (phases are
+//     functions of the global stage / group / panel counters), the drain warps write panel i (staging tile of their
+//     own, coalesced rows) while the producer, the split warps and the tensor core are up to two drain groups into
+//     panel i + 1.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPanelSplitGroups = 1;                      // groups of 4 split warps (one TMEM lane quarter each) on alternate stages
+constexpr int kPanelIssuer2 = 2 + 4 * kPanelSplitGroups + kDrainWarps;   // second MMA issuer: the last warp
+constexpr int kPanelThreads = 32 * (kPanelIssuer2 + 1);   // TMA, MMA (hi hi^T), split warps, 8 drain warps, MMA (lo hi^T)
+constexpr uint32_t kPanelStg = 384;                       // TMEM: [0,128) cross, [128,384) hi hi^T ping-pong, [384,512) 2 x (32 hi | 32 lo)
+
+struct GramPanelParams {
+    int B, d, n, n2, S, npanels, nst, box_rows, accumulate;
+    float* G;
+};
+
+__global__ void __launch_bounds__(kPanelThreads, 1)
+gram_tc_fwd_panel_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap2,
+                         const GramPanelParams P) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t full_bar[kMaxStages], empty_bar[kMaxStages];
+    __shared__ __align__(8) uint64_t a_full[2], a_free[2], hh_full[2], hh_free[2], cross_full, cross_free;
+    __shared__ uint32_t tmem_base_smem;
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int d = P.d, nst = P.nst;
+    const int nk1 = (P.n + kKc - 1) / kKc;
+    const int nk = nk1 + (P.n2 + kKc - 1) / kKc;
+    const int ngroups = (nk + kDrainEvery - 1) / kDrainEvery;
+    const int nit = (P.npanels - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;    // panels of this CTA (>= 1)
+    float* Gs = reinterpret_cast<float*>(smem + (size_t)nst * kTileBytes);                  // [128][kGsLd] staging of the epilogue
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nst; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 2);                // both issuers' MMAs on the stage have retired
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&a_full[i], 128);
+            mbar_init(&a_free[i], 2);
+            mbar_init(&hh_full[i], 1);
+            mbar_init(&hh_free[i], 32 * kDrainWarps);
+        }
+        mbar_init(&cross_full, 1);
+        mbar_init(&cross_free, 32 * kDrainWarps);
+        mbar_fence_init();
+        prefetch_tmap(&tmap);
+        if (P.n2 > 0) prefetch_tmap(&tmap2);
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(&tmem_base_smem);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+
+    if (warp == 0) {
+        // ===== TMA producer
+        if (lane == 0) {
+            const uint32_t tx = (uint32_t)P.box_rows * kKc * 4;
+            int gs = 0;
+            for (int it = 0; it < nit; ++it) {
+                const int row0 = ((int)blockIdx.x + it * (int)gridDim.x) * P.S * d;
+                for (int kc = 0; kc < nk; ++kc, ++gs) {
+                    const int s = gs % nst;
+                    mbar_wait(&empty_bar[s], (((uint32_t)(gs / nst)) & 1u) ^ 1u);
+                    mbar_arrive_expect_tx(&full_bar[s], tx);
+                    const CUtensorMap* tm = kc < nk1 ? &tmap : &tmap2;
+                    tma_load_2d(smem + (size_t)s * kTileBytes, tm, &full_bar[s], (kc < nk1 ? kc : kc - nk1) * kKc, row0);
+                }
+            }
+        }
+    } else if (warp == 1 || warp == kPanelIssuer2) {
+        // ===== MMA issuers: warp 1 the hi hi^T products (ping-pong accumulator), the last warp the lo hi^T products (cross
+        // accumulator).  One thread issues a tcgen05.mma per ~80 cycles; an M = N = 128 MMA occupies the tensor pipe for 64.
+        if (lane == 0) {
+            const bool hh = warp == 1;
+            const uint32_t idesc = umma_idesc_tf32(kTile, kTile);
+            int gs = 0, gg = 0;
+            for (int it = 0; it < nit; ++it) {
+                if (!hh && it > 0) mbar_wait(&cross_free, ((uint32_t)(it - 1)) & 1u);   // the drain warps have read the cross accumulator
+                for (int kc = 0; kc < nk; ++kc, ++gs) {
+                    const int s = gs % nst, ab = gs & 1;
+                    const int g = kc / kDrainEvery, r = kc - g * kDrainEvery;
+                    const int pp = (gg + g) & 1;
+                    mbar_wait(&a_full[ab], ((uint32_t)(gs >> 1)) & 1u);              // implies the tile has landed
+                    if (hh && r == 0) mbar_wait(&hh_free[pp], (((uint32_t)((gg + g) >> 1)) & 1u) ^ 1u);
+                    tc_fence_after();
+                    const uint64_t db = umma_desc_sw128(smem_u32(smem + (size_t)s * kTileBytes));
+                    const uint32_t a_hi = tmem_base + kPanelStg + 64u * (uint32_t)ab, a_lo = a_hi + 32u;
+                    if (hh) {
+                        const uint32_t t_hh = tmem_base + 128u + 128u * (uint32_t)pp;
+#pragma unroll
+                        for (int k = 0; k < kKc / 8; ++k) umma_tf32_ts(t_hh, a_hi + k * 8, db + 2 * k, idesc, (r | k) != 0);
+                        if (r == kDrainEvery - 1 || kc == nk - 1) umma_commit(&hh_full[pp]);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < kKc / 8; ++k) umma_tf32_ts(tmem_base, a_lo + k * 8, db + 2 * k, idesc, (kc | k) != 0);
+                    }
+                    umma_commit(&empty_bar[s]);
+                    umma_commit(&a_free[ab]);
+                }
+                if (!hh) umma_commit(&cross_full);
+                gg += ngroups;
+            }
+        }
+    } else if (warp < 2 + 4 * kPanelSplitGroups) {
+        // ===== split warps: thread = panel row = TMEM lane; group g takes the stages gs = g mod kPanelSplitGroups
+        const int grp = (warp - 2) >> 2, q = warp & 3;
+        const int row = q * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        const int total = nit * nk;
+        for (int gs = grp; gs < total; gs += kPanelSplitGroups) {
+            const int s = gs % nst, ab = gs & 1;
+            mbar_wait(&full_bar[s], ((uint32_t)(gs / nst)) & 1u);
+            const uint8_t* rp = smem + (size_t)s * kTileBytes + row * 128;
+            // two halves of 16 k (register budget: 96 at 576 threads); chunk c of the row sits at position c ^ (row & 7)
+            float hi[16], lo[16];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float4 v = *reinterpret_cast<const float4*>(rp + ((c ^ (row & 7)) << 4));
+                split_tf32(v.x, hi[4 * c], lo[4 * c]);         split_tf32(v.y, hi[4 * c + 1], lo[4 * c + 1]);
+                split_tf32(v.z, hi[4 * c + 2], lo[4 * c + 2]); split_tf32(v.w, hi[4 * c + 3], lo[4 * c + 3]);
+            }
+            mbar_wait(&a_free[ab], (((uint32_t)(gs >> 1)) & 1u) ^ 1u);
+            tc_fence_after();
+            const uint32_t stg = tmem_base + kPanelStg + 64u * (uint32_t)ab + lane_addr;
+            tmem_st_32x16(stg, hi);
+            tmem_st_32x16(stg + 32u, lo);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float4 v = *reinterpret_cast<const float4*>(rp + (((c + 4) ^ (row & 7)) << 4));
+                split_tf32(v.x, hi[4 * c], lo[4 * c]);         split_tf32(v.y, hi[4 * c + 1], lo[4 * c + 1]);
+                split_tf32(v.z, hi[4 * c + 2], lo[4 * c + 2]); split_tf32(v.w, hi[4 * c + 3], lo[4 * c + 3]);
+            }
+            tmem_st_32x16(stg + 16u, hi);
+            tmem_st_32x16(stg + 48u, lo);
+            tmem_st_wait();
+            tc_fence_before();
+            mbar_arrive(&a_full[ab]);
+        }
+    } else if (warp < kPanelIssuer2) {
+        // ===== drain warps: FP32 round-to-nearest accumulation of hi hi^T, then the epilogue of the panel
+        const int dw = warp - (2 + 4 * kPanelSplitGroups);   // 0..7
+        const int q = warp & 3;
+        const int half = dw >> 2;                            // column half [64 half, 64 half + 64)
+        const int i = q * 32 + lane;
+        bool needed;
+        {
+            const int r0 = q * 32, r1 = q * 32 + 31;
+            const int c_lo = (r0 / d) * d, c_hi = min((r1 / d) * d + d, P.S * d);
+            needed = (r0 < P.S * d) && (half * 64 < c_hi) && (half * 64 + 64 > c_lo);
+        }
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        const int t = threadIdx.x - 32 * (2 + 4 * kPanelSplitGroups);   // 0..255
+        int gg = 0;
+        for (int it = 0; it < nit; ++it) {
+            float acc[2][32];
+#pragma unroll
+            for (int ch = 0; ch < 2; ++ch)
+#pragma unroll
+                for (int u = 0; u < 32; ++u) acc[ch][u] = 0.f;
+            for (int g = 0; g < ngroups; ++g) {
+                const int pp = (gg + g) & 1;
+                mbar_wait(&hh_full[pp], ((uint32_t)((gg + g) >> 1)) & 1u);
+                tc_fence_after();
+                if (needed) {
+                    const uint32_t t_hh = tmem_base + 128u + 128u * (uint32_t)pp + (uint32_t)(half * 64);
+#pragma unroll
+                    for (int ch = 0; ch < 4; ++ch) {
+                        float v[16];
+                        tmem_ld_32x16(t_hh + lane_addr + (uint32_t)(ch * 16), v);
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) acc[ch >> 1][(ch & 1) * 16 + u] += v[u];
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&hh_free[pp]);
+            }
+            gg += ngroups;
+            mbar_wait(&cross_full, (uint32_t)it & 1u);
+            tc_fence_after();
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * kDrainWarps) : "memory");     // the previous panel's rows have left Gs
+            if (needed) {
+#pragma unroll
+                for (int ch = 0; ch < 4; ++ch) {
+                    const int c0 = half * 64 + ch * 16;
+                    float v[16];
+                    tmem_ld_32x16(tmem_base + lane_addr + (uint32_t)c0, v);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) Gs[i * kGsLd + c0 + u] = fmaf(acc[ch >> 1][(ch & 1) * 16 + u], 0.5f, v[u]);   // T = H / 2 + C
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&cross_free);
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * kDrainWarps) : "memory");
+            const int b0 = ((int)blockIdx.x + it * (int)gridDim.x) * P.S;
+            const int dd = d * d;
+            const int total = min(P.S, P.B - b0) * dd;
+            float* Gb = P.G + (size_t)b0 * dd;               // the panel's samples are contiguous in G
+            for (int e = t; e < total; e += 32 * kDrainWarps) {
+                const int s = e / dd, rem = e - s * dd;
+                const int li = rem / d, j = rem - li * d;
+                const float gv = Gs[(s * d + li) * kGsLd + s * d + j] + Gs[(s * d + j) * kGsLd + s * d + li];   // G = T + T^T
+                Gb[e] = P.accumulate ? Gb[e] + gv : gv;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // host
 // ------------------------------------------------------------------------------------------------
 cmf_encode_tiled_fn get_encode_tiled() {
@@ -351,6 +573,31 @@ int gram_tc_fwd_launch(int B, int d, int n, const float* V, int n2, const float*
     P.B = B; P.d = d; P.n = n; P.n2 = n2; P.G = G; P.accumulate = accumulate;
     static const int ablate_env = [] { const char* e = getenv("CMF_GRAM_FWD_ABLATE"); return e ? atoi(e) : 0; }();
     P.ablate = ablate_env;
+    static const bool panel_off = [] { const char* e = getenv("CMF_GRAM_FWD_PANEL"); return e && e[0] == '0'; }();
+    if (d <= kTile && !panel_off) {
+        GramPanelParams Q{};
+        Q.B = B; Q.d = d; Q.n = n; Q.n2 = n2; Q.G = G; Q.accumulate = accumulate;
+        Q.S = kTile / d; Q.npanels = (int)ceil_div(B, Q.S); Q.box_rows = Q.S * d; Q.nst = 8;
+        CUtensorMap tm1, tm2;
+        int rc1 = make_tmap_2d_f32(&tm1, V, (uint64_t)B * d, (uint64_t)n, (uint64_t)n, (uint32_t)Q.box_rows, 0);
+        if (rc1 != 0) return rc1;
+        tm2 = tm1;
+        if (n2 > 0) {
+            rc1 = make_tmap_2d_f32(&tm2, V2, (uint64_t)B * d, (uint64_t)n2, (uint64_t)n2, (uint32_t)Q.box_rows, 0);
+            if (rc1 != 0) return rc1;
+        }
+        const size_t smem_p = (size_t)Q.nst * kTileBytes + (size_t)kTile * kGsLd * 4 + 1024;
+        static DeviceOnce attr_set_p;
+        if (!attr_set_p.done()) {
+            cudaError_t e = cudaFuncSetAttribute(gram_tc_fwd_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) { set_error("gram_tc attr: %s", cudaGetErrorString(e)); return (int)e; }
+            attr_set_p.mark();
+        }
+        const unsigned ctas = (unsigned)min((long long)Q.npanels, (long long)kNumSMs);
+        gram_tc_fwd_panel_kernel<<<ctas, kPanelThreads, smem_p, stream>>>(tm1, tm2, Q);
+        CMF_CHECK_LAUNCH();
+        return 0;
+    }
     long long grid;
     if (d <= kTile) {
         P.S = kTile / d; P.T = 1; P.ntiles = 1;
