@@ -308,9 +308,9 @@ coupling_bwd_finalize(int B, int M, int Q, int KC,
 
 // How many tangent chunks to spread over blockIdx.y so the grid fills the machine (>= ~2 waves of
 // 148 SMs x 2048 threads) even at the reference's default batch of 50.
-static int pick_kchunks(long long threads_x, int d) {
+static int pick_kchunks(long long threads_x, int d, long long resident_threads = 2048) {
     if (d <= 0) return 1;
-    const long long want = 2LL * kNumSMs * 2048;
+    const long long want = 2LL * kNumSMs * resident_threads;
     long long kc = ceil_div(want, threads_x > 0 ? threads_x : 1);
     const long long kc_max = ceil_div(d, kUnroll);  // at least one unrolled batch per chunk
     if (kc > kc_max) kc = kc_max;
@@ -359,7 +359,11 @@ extern "C" int cmf_coupling_jvp_fwd(int B, int d, int M, int Q,
 // The split over tangent chunks must be the same function of (B,d,M,Q) in the workspace query and
 // in the launch; vectorisation (which changes threads_x) depends on pointers, so size for the worst case.
 static int bwd_kchunks(int B, int d, int M, int Q, bool vec) {
-    return pick_kchunks(vec ? (long long)B * (M >> 2) : (long long)B * Q, d);
+    // the 128-bit adjoint holds 128 registers (two CTAs = 512 threads resident per SM): fewer, longer tangent chunks than
+    // the forward's rule -- measured at B = 512, d = 64 (10 launches of scope A): 2048 -> 0.503 ms, 1024 / 768 / 512 -> 0.494-0.495,
+    // 384 -> 0.508, 256 -> 0.525
+    static const long long res = [] { const char* e = getenv("CMF_CPL_BWD_RESIDENT"); return e ? atoll(e) : 1024LL; }();
+    return pick_kchunks(vec ? (long long)B * (M >> 2) : (long long)B * Q, d, vec ? res : 2048);
 }
 
 extern "C" size_t cmf_coupling_jvp_bwd_workspace(int B, int d, int M, int Q) {
