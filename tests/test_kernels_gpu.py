@@ -145,6 +145,24 @@ def test_gram_tc_matches_fp64_and_fma(B, d, n):
     _close(g_tc, K.gram_bwd(Vd, gG.float().to(DEV), path="fma"), rtol=1e-5, what="g_V tc vs fma")
 
 
+@pytest.mark.parametrize("B,d,n", [(700, 64, 392), (1000, 32, 200), (500, 128, 260), (641, 48, 100), (450, 96, 36), (1201, 16, 72)])
+def test_gram_fwd_panel_kernel_many_panels_per_cta(B, d, n):
+    """The persistent tcgen05 forward (d <= 128) with several panels per CTA: the stage ring, the TMEM staging slots, the
+    ping-pong accumulator (odd and even numbers of drain groups per panel: n = 260 -> 3, n = 36 -> 1) and the cross
+    accumulator hand over from panel to panel; ragged last panel (B not a multiple of the samples per panel), panels
+    of fewer than 128 rows (d = 48, 96).  Accumulate mode and the two-block launch on the same shapes."""
+    import cmf_b200.kernels as K
+    V = _rand(B, d, n, seed=31)
+    Vd = V.float().to(DEV)
+    ref = E.gram_fwd(V)
+    G = K.gram_fwd(Vd, path="tc")
+    _close(G, ref, rtol=2e-6 * max(1, n ** 0.5), what="G panel")
+    assert torch.equal(G, G.transpose(1, 2)), "G must be bitwise symmetric"
+    assert torch.equal(G, K.gram_fwd(Vd, path="tc")), "not reproducible"
+    G2 = K.gram_fwd2(Vd, Vd, G.clone())
+    _close(G2, 3 * ref, rtol=1e-5, what="G two blocks, accumulate")
+
+
 @pytest.mark.parametrize("B,d,n", [(300, 64, 392), (200, 96, 392), (260, 128, 260), (400, 32, 200), (180, 72, 520), (700, 16, 136)])
 def test_gram_bwd_persistent_kernel_many_items_per_cta(B, d, n):
     """The persistent tcgen05 adjoint (d <= 128) with several (sample, n tile) items per CTA: every ring (V stages, the
