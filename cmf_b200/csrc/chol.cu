@@ -308,7 +308,7 @@ chol_wide_fwd_kernel(int d, int ld, int tpr, int vec, const float* __restrict__ 
 }
 
 __global__ void __launch_bounds__(kWideBwdThreads)
-chol_wide_bwd_kernel(int d, int ld, int tpc, int vec, const float* __restrict__ L, const float* __restrict__ G,
+chol_wide_bwd_kernel(int d, int ld, int tpc, int vec, int blocked, const float* __restrict__ L, const float* __restrict__ G,
                      const float* __restrict__ g_logdet, const float* __restrict__ g_l1, int penalty,
                      float* __restrict__ gG) {
     extern __shared__ __align__(16) float smem[];
@@ -332,6 +332,62 @@ chol_wide_bwd_kernel(int d, int ld, int tpc, int vec, const float* __restrict__ 
     for (int e = t; e < d * ld; e += kWideBwdThreads) Ws[e] = 0.f;
     if (t < d) invd[t] = 1.f / __ldg(Lb + (size_t)t * d + t);
     __syncthreads();
+    if (blocked) {
+        // W = L^{-1} blockwise (d a multiple of 16): forward substitution is a chain of d - 1 dependent row steps (~450
+        // cycles each at d = 64: 34 us of latency per sample whatever the batch).  Here only the 16 x 16 diagonal blocks
+        // are inverted by substitution (15 steps, all blocks side by side); the blocks below the diagonal follow from
+        //     [A 0; B C]^{-1} = [A^{-1} 0; -C^{-1} B A^{-1}  C^{-1}]
+        // level by level (block size 16, 32, ...): two small matrix products per level, every element independent.
+        float* Ts = invd + d;                          // [d/2][ld] scratch: T = B A^{-1} of the current level
+        {
+            const int jl = (t & 63) >> 2, sub = t & 3; // 64 threads per diagonal block: 16 columns x 4 lanes
+            for (int blk = t >> 6; blk < d / 16; blk += kWideBwdThreads / 64) {
+                const int o = 16 * blk, j = o + jl;
+                if (sub == 0) Ws[j * ld + j] = invd[j];
+                for (int il = 1; il < 16; ++il) {
+                    const int i = o + il;
+                    float acc = 0.f;
+                    if (jl < il) {
+                        const float* ri = Ls + i * ld + o;
+                        for (int m = jl + sub; m < il; m += 4) acc = fmaf(ri[m], Ws[(o + m) * ld + j], acc);
+                    }
+                    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                    if (jl < il && sub == 0) Ws[i * ld + j] = -acc * invd[i];
+                    __syncwarp();
+                }
+            }
+        }
+        __syncthreads();
+        for (int bs = 16; bs < d; bs <<= 1) {
+            // pairs of diagonal blocks of size bs; an odd block at the end (d / bs odd) has no partner at this level and
+            // is merged at a later one -- d / 16 need not be a power of two: the pair (A, C) at offset c0 exists while
+            // c0 + bs < d, and C is then min(bs, d - c0 - bs) rows (already inverted as a whole by the earlier levels
+            // only if it is a full block; so require full pairs: handled by the host, which sets blocked only for d = 16 * 2^k)
+            const int npairs = d / (2 * bs);
+            const int per = bs * bs;
+            for (int e = t; e < npairs * per; e += kWideBwdThreads) {          // T = L_CA W_AA
+                const int pr = e / per, rem = e - pr * per;
+                const int r = rem / bs, c = rem - r * bs;
+                const int c0 = pr * 2 * bs;
+                const float* lrow = Ls + (c0 + bs + r) * ld + c0;
+                float acc = 0.f;
+                for (int m = c; m < bs; ++m) acc = fmaf(lrow[m], Ws[(c0 + m) * ld + c0 + c], acc);   // W_AA is lower triangular
+                Ts[(pr * bs + r) * ld + c] = acc;
+            }
+            __syncthreads();
+            for (int e = t; e < npairs * per; e += kWideBwdThreads) {          // W_CA = -W_CC T
+                const int pr = e / per, rem = e - pr * per;
+                const int r = rem / bs, c = rem - r * bs;
+                const int c0 = pr * 2 * bs;
+                const float* wrow = Ws + (c0 + bs + r) * ld + c0 + bs;
+                float acc = 0.f;
+                for (int m = 0; m <= r; ++m) acc = fmaf(wrow[m], Ts[(pr * bs + m) * ld + c], acc);    // W_CC is lower triangular
+                Ws[(c0 + bs + r) * ld + c0 + c] = -acc;
+            }
+            __syncthreads();
+        }
+    } else
     // column j of W by forward substitution, tpc lanes per column (adjacent lanes of one warp): they
     // split the dot product W[i][j] = -(sum_{m<i} L[i][m] W[m][j]) / L[i][i] by m mod tpc and combine
     // with xor shuffles -- a row step is a ~100-cycle chain instead of i dependent iterations.
@@ -572,7 +628,10 @@ extern "C" int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
     if (d >= kCholWideMinD) {
         const int ld = wide_ld(d);
         const int vec = (d % 4 == 0) && aligned16(L) && aligned16(g_G);
-        const size_t smem = ((size_t)2 * d * ld + d) * sizeof(float);
+        // blockwise inverse for d = 16 * 2^k (32, 64, 128): full pairs at every level
+        static const bool blocked_off = [] { const char* e = getenv("CMF_CHOL_BWD_BLOCKED"); return e && e[0] == '0'; }();
+        const int blocked = !blocked_off && d % 16 == 0 && ((d / 16) & (d / 16 - 1)) == 0;
+        const size_t smem = ((size_t)2 * d * ld + d + (blocked ? (size_t)(d / 2) * ld : 0)) * sizeof(float);
         int tpc = 8;
         while (d * tpc > kWideBwdThreads) tpc >>= 1;
         static bool wide_attr = false;
@@ -581,7 +640,7 @@ extern "C" int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
             if (e != cudaSuccess) { set_error("chol_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
             wide_attr = true;
         }
-        chol_wide_bwd_kernel<<<(unsigned)B, kWideBwdThreads, smem, (cudaStream_t)stream>>>(d, ld, tpc, vec, L, G, g_logdet, g_l1, penalty, g_G);
+        chol_wide_bwd_kernel<<<(unsigned)B, kWideBwdThreads, smem, (cudaStream_t)stream>>>(d, ld, tpc, vec, blocked, L, G, g_logdet, g_l1, penalty, g_G);
         CMF_CHECK_LAUNCH();
         return 0;
     }
