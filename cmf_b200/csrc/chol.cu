@@ -593,11 +593,11 @@ extern "C" int cmf_chol_logdet_fwd(int B, int d, const float* G, float* L, float
         const size_t smem = ((size_t)2 * d * ld + 8) * sizeof(float);
         int tpr = 8;
         while (d * tpr > kWideFwdThreads) tpr >>= 1;
-        static bool wide_attr = false;
-        if (!wide_attr) {
+        static DeviceOnce wide_attr;                   // the opt-in is per device
+        if (!wide_attr.done()) {
             cudaError_t e = cudaFuncSetAttribute(chol_wide_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) { set_error("chol_fwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-            wide_attr = true;
+            wide_attr.mark();
         }
         chol_wide_fwd_kernel<<<(unsigned)B, kWideFwdThreads, smem, (cudaStream_t)stream>>>(d, ld, tpr, vec, G, L, logdet, l1_off, l1_diag, info);
         CMF_CHECK_LAUNCH();
@@ -634,11 +634,11 @@ extern "C" int cmf_chol_logdet_bwd(int B, int d, const float* L, const float* G,
         const size_t smem = ((size_t)2 * d * ld + d + (blocked ? (size_t)(d / 2) * ld : 0)) * sizeof(float);
         int tpc = 8;
         while (d * tpc > kWideBwdThreads) tpc >>= 1;
-        static bool wide_attr = false;
-        if (!wide_attr) {
+        static DeviceOnce wide_attr;                   // the opt-in is per device
+        if (!wide_attr.done()) {
             cudaError_t e = cudaFuncSetAttribute(chol_wide_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
             if (e != cudaSuccess) { set_error("chol_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
-            wide_attr = true;
+            wide_attr.mark();
         }
         chol_wide_bwd_kernel<<<(unsigned)B, kWideBwdThreads, smem, (cudaStream_t)stream>>>(d, ld, tpc, vec, blocked, L, G, g_logdet, g_l1, penalty, g_G);
         CMF_CHECK_LAUNCH();
