@@ -135,22 +135,65 @@ __device__ __forceinline__ void finalize_store(float z, float e, float gx, float
 
 // identity map, 128-bit path.  grid = (ceil(B*M/4 / kThreads), KC)
 #ifndef CMF_CPL_BWD_MINB
-#define CMF_CPL_BWD_MINB 1
+#define CMF_CPL_BWD_MINB 2
 #endif
 #ifndef CMF_CPL_BWD_UNROLL
 #define CMF_CPL_BWD_UNROLL 4
 #endif
 constexpr int kUnrollB = CMF_CPL_BWD_UNROLL;
+// cache policy of the adjoint's streams (probe switches; scripts/cpl_probe.cu): loads 0 = ld.cs, 1 = ld.nc, 2 = ld.cg, 3 = ld.lu;
+// stores 0 = st.cs, 1 = st (write-back, normal eviction), 2 = st.cg, 3 = st.wt
+#ifndef CMF_CPL_BWD_LD
+#define CMF_CPL_BWD_LD 0
+#endif
+#ifndef CMF_CPL_BWD_ST
+#define CMF_CPL_BWD_ST 0
+#endif
+__device__ __forceinline__ float4 bwd_ld4(const float* p) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+#if CMF_CPL_BWD_LD == 0
+    return __ldcs(q);
+#elif CMF_CPL_BWD_LD == 1
+    return __ldg(q);
+#elif CMF_CPL_BWD_LD == 2
+    return __ldcg(q);
+#else
+    return __ldlu(q);
+#endif
+}
+__device__ __forceinline__ void bwd_st4(float* p, float4 v) {
+    float4* q = reinterpret_cast<float4*>(p);
+#if defined(CMF_CPL_BWD_NOSTORE)
+    if (v.x == 1.2345e-30f) *q = v;           // timing ablation only
+#elif CMF_CPL_BWD_ST == 0
+    __stcs(q, v);
+#elif CMF_CPL_BWD_ST == 1
+    *q = v;
+#elif CMF_CPL_BWD_ST == 2
+    __stcg(q, v);
+#else
+    __stwt(q, v);
+#endif
+}
 __global__ void __launch_bounds__(kThreads, CMF_CPL_BWD_MINB)
 coupling_bwd_vec4(int B, int d, int M, int kchunk,
                   const float* __restrict__ z_m, const float* __restrict__ V_m,
                   const float* __restrict__ st, const float* __restrict__ ST,
                   const float* __restrict__ g_x, const float* __restrict__ g_V,
                   float* __restrict__ g_z, float* __restrict__ g_Vin,
-                  float* __restrict__ g_st, float* __restrict__ g_ST, float* __restrict__ ws) {
+                  float* __restrict__ g_st, float* __restrict__ g_ST, float* __restrict__ ws, int S) {
+    // S > 1 (2, 4 or 8): the tangent range is split over the WARPS of the CTA instead of blockIdx.y -- warp c * (8 / S) + w
+    // owns chunk c of the CTA's column group w (32 consecutive 128-bit columns: 512 contiguous bytes per row, as in the
+    // blockIdx.y form), and the S partial (A, C) of a column meet in shared memory in chunk order: no workspace, no second launch
     const int Mv = M >> 2;
-    const long long t = (long long)blockIdx.x * kThreads + threadIdx.x;
-    if (t >= (long long)B * Mv) return;
+    const long long tg = (long long)blockIdx.x * kThreads + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int wpc = (kThreads / 32) / S;         // column groups per CTA
+    const int chunk = S > 1 ? warp / wpc : (int)blockIdx.y;
+    const long long t_ = S > 1 ? ((long long)blockIdx.x * wpc + (warp - chunk * wpc)) * 32 + lane : tg;
+    const bool live = t_ < (long long)B * Mv;
+    if (!live && S == 1) return;
+    const long long t = live ? t_ : 0;           // S > 1: idle threads still meet the barrier
     const int b = (int)(t / Mv);
     const int j = (int)(t % Mv) << 2;
     const float4 z = ldg4(z_m + (size_t)b * M + j);
@@ -160,8 +203,8 @@ coupling_bwd_vec4(int B, int d, int M, int kchunk,
     float4 ez;
     ez.x = -e.x * z.x; ez.y = -e.y * z.y; ez.z = -e.z * z.z; ez.w = -e.w * z.w;
     float4 A = make_float4(0.f, 0.f, 0.f, 0.f), C = A;
-    const int k0 = blockIdx.y * kchunk;
-    const int k1 = min(d, k0 + kchunk);
+    const int k0 = chunk * kchunk;
+    const int k1 = live ? min(d, k0 + kchunk) : k0;
     const float* gp = g_V + ((size_t)b * d + k0) * M + j;
     const float* vp = V_m + ((size_t)b * d + k0) * M + j;
     const float* sp = ST + ((size_t)b * d + k0) * 2 * M + M + j;
@@ -172,31 +215,51 @@ coupling_bwd_vec4(int B, int d, int M, int kchunk,
         float4 g[kUnrollB], v[kUnrollB], sd[kUnrollB];
 #pragma unroll
         for (int u = 0; u < kUnrollB; ++u) {
-            g[u] = ldcs4(gp + (size_t)u * M);
-            v[u] = ldcs4(vp + (size_t)u * M);
-            sd[u] = ldcs4(sp + (size_t)u * 2 * M);
+            g[u] = bwd_ld4(gp + (size_t)u * M);
+            v[u] = bwd_ld4(vp + (size_t)u * M);
+            sd[u] = bwd_ld4(sp + (size_t)u * 2 * M);
         }
 #pragma unroll
         for (int u = 0; u < kUnrollB; ++u) {
             A.x += sd[u].x * g[u].x; A.y += sd[u].y * g[u].y; A.z += sd[u].z * g[u].z; A.w += sd[u].w * g[u].w;
             C.x += v[u].x * g[u].x;  C.y += v[u].y * g[u].y;  C.z += v[u].z * g[u].z;  C.w += v[u].w * g[u].w;
-            stcs4(ovp + (size_t)u * M, make_float4(e.x * g[u].x, e.y * g[u].y, e.z * g[u].z, e.w * g[u].w));
-            stcs4(otp + (size_t)u * 2 * M, make_float4(-g[u].x, -g[u].y, -g[u].z, -g[u].w));
-            stcs4(otp + (size_t)u * 2 * M + M, make_float4(ez.x * g[u].x, ez.y * g[u].y, ez.z * g[u].z, ez.w * g[u].w));
+            bwd_st4(ovp + (size_t)u * M, make_float4(e.x * g[u].x, e.y * g[u].y, e.z * g[u].z, e.w * g[u].w));
+            bwd_st4(otp + (size_t)u * 2 * M, make_float4(-g[u].x, -g[u].y, -g[u].z, -g[u].w));
+            bwd_st4(otp + (size_t)u * 2 * M + M, make_float4(ez.x * g[u].x, ez.y * g[u].y, ez.z * g[u].z, ez.w * g[u].w));
         }
         gp += (size_t)kUnrollB * M; vp += (size_t)kUnrollB * M; sp += (size_t)kUnrollB * 2 * M;
         ovp += (size_t)kUnrollB * M; otp += (size_t)kUnrollB * 2 * M;
     }
     for (; k < k1; ++k) {
-        const float4 g = ldcs4(gp), v = ldcs4(vp), sd = ldcs4(sp);
+        const float4 g = bwd_ld4(gp), v = bwd_ld4(vp), sd = bwd_ld4(sp);
         A.x += sd.x * g.x; A.y += sd.y * g.y; A.z += sd.z * g.z; A.w += sd.w * g.w;
         C.x += v.x * g.x;  C.y += v.y * g.y;  C.z += v.z * g.z;  C.w += v.w * g.w;
-        stcs4(ovp, make_float4(e.x * g.x, e.y * g.y, e.z * g.z, e.w * g.w));
-        stcs4(otp, make_float4(-g.x, -g.y, -g.z, -g.w));
-        stcs4(otp + M, make_float4(ez.x * g.x, ez.y * g.y, ez.z * g.z, ez.w * g.w));
+        bwd_st4(ovp, make_float4(e.x * g.x, e.y * g.y, e.z * g.z, e.w * g.w));
+        bwd_st4(otp, make_float4(-g.x, -g.y, -g.z, -g.w));
+        bwd_st4(otp + M, make_float4(ez.x * g.x, ez.y * g.y, ez.z * g.z, ez.w * g.w));
         gp += M; vp += M; sp += 2 * M; ovp += M; otp += 2 * M;
     }
-    if (gridDim.y == 1) {
+    if (S > 1) {
+        // 0 + p0 + p1 + ... in chunk order, as coupling_bwd_finalize adds the workspace partials
+        __shared__ float4 part[2][kThreads];
+        part[0][threadIdx.x] = A;
+        part[1][threadIdx.x] = C;
+        __syncthreads();
+        if (chunk != 0 || !live) return;
+        A = make_float4(0.f, 0.f, 0.f, 0.f); C = A;
+        for (int c = 0; c < S; ++c) {
+            const float4 a = part[0][(c * wpc + warp) * 32 + lane], cc = part[1][(c * wpc + warp) * 32 + lane];
+            A.x += a.x; A.y += a.y; A.z += a.z; A.w += a.w;
+            C.x += cc.x; C.y += cc.y; C.z += cc.z; C.w += cc.w;
+        }
+    } else if (gridDim.y > 1) {
+        const size_t BM = (size_t)B * M;
+        float* w = ws + (size_t)blockIdx.y * 2 * BM + (size_t)b * M + j;
+        *reinterpret_cast<float4*>(w) = A;
+        *reinterpret_cast<float4*>(w + BM) = C;
+        return;
+    }
+    {
         float4 gx = make_float4(0.f, 0.f, 0.f, 0.f);
         if (g_x) gx = ldg4(g_x + (size_t)b * M + j);
         float4 gz, gt, gs;
@@ -207,11 +270,6 @@ coupling_bwd_vec4(int B, int d, int M, int kchunk,
         *reinterpret_cast<float4*>(g_z + (size_t)b * M + j) = gz;
         *reinterpret_cast<float4*>(g_st + (size_t)b * 2 * M + j) = gt;
         *reinterpret_cast<float4*>(g_st + (size_t)b * 2 * M + M + j) = gs;
-    } else {
-        const size_t BM = (size_t)B * M;
-        float* w = ws + (size_t)blockIdx.y * 2 * BM + (size_t)b * M + j;
-        *reinterpret_cast<float4*>(w) = A;
-        *reinterpret_cast<float4*>(w + BM) = C;
     }
 }
 
@@ -396,17 +454,35 @@ extern "C" int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
                     "coupling_bwd: workspace too small (%zu bytes, need %zu)", workspace_bytes,
                     (size_t)ny * 2 * (size_t)B * M * sizeof(float));
     float* ws = static_cast<float*>(workspace);
+    // 128-bit path, 2..8 tangent chunks: the chunks go to the warps of one CTA and meet in shared memory (one launch, no
+    // workspace); CMF_CPL_BWD_WARPSPLIT=0 restores the blockIdx.y chunks + finalize launch
+    static const bool warpsplit_off = [] { const char* e = getenv("CMF_CPL_BWD_WARPSPLIT"); return e && e[0] == '0'; }();
+    static const bool skip_fin = [] { const char* e = getenv("CMF_CPL_BWD_SKIPFIN"); return e && e[0] == '1'; }();   // timing probe only
+    // more than 8 chunks wanted (small batches): 8 warp chunks still win (B = 50, M = 392: 15.1 -> 10.8 us; B = 8: 10.6 -> 8.1)
+    // unless the grid is far from filling the machine AND the per-thread loop is long (B = 1, d = 512, M = 1536: 19.2 -> 22.8)
+    static const long long warpsplit_minfill = [] { const char* e = getenv("CMF_CPL_BWD_WARPSPLIT_MINFILL"); return e ? atoll(e) : 148LL * 128; }();
+    const bool few_long = (long long)B * (M >> 2) * 8 < warpsplit_minfill && d > 256;
+    if (vec && KC > 1 && !warpsplit_off && (KC <= 8 || !few_long)) {
+        int S = 2;
+        while (S < KC && S < 8) S <<= 1;
+        const int kchunk_s = (int)ceil_div(ceil_div(d, S), kUnroll) * kUnroll;
+        const unsigned nx = (unsigned)ceil_div((long long)B * (M >> 2), (kThreads / S));
+        coupling_bwd_vec4<<<dim3(nx, 1), kThreads, 0, stream>>>(B, d, M, kchunk_s, z_m, V_m, st, ST, g_x, g_V,
+                                                               g_z, g_Vin, g_st, g_ST, nullptr, S);
+        CMF_CHECK_LAUNCH();
+        return 0;
+    }
     if (vec) {
         dim3 grid((unsigned)ceil_div((long long)B * (M >> 2), kThreads), (unsigned)ny);
         coupling_bwd_vec4<<<grid, kThreads, 0, stream>>>(B, d, M, kchunk, z_m, V_m, st, ST, g_x, g_V,
-                                                         g_z, g_Vin, g_st, g_ST, ws);
+                                                         g_z, g_Vin, g_st, g_ST, ws, 1);
     } else {
         dim3 grid((unsigned)ceil_div((long long)B * Q, kThreads), (unsigned)ny);
         coupling_bwd_map<<<grid, kThreads, 0, stream>>>(B, d, M, Q, kchunk, z_m, V_m, st, ST, inv, g_x, g_V,
                                                         g_z, g_Vin, g_st, g_ST, ws);
     }
     CMF_CHECK_LAUNCH();
-    if (ny > 1) {
+    if (ny > 1 && !skip_fin) {
         coupling_bwd_finalize<<<(unsigned)ceil_div((long long)B * M, kThreads), kThreads, 0, stream>>>(
             B, M, Q, ny, z_m, st, map, g_x, ws, g_z, g_st);
         CMF_CHECK_LAUNCH();

@@ -58,7 +58,10 @@ int cmf_coupling_jvp_fwd(int B, int d, int M, int Q,
 /* Adjoint of cmf_coupling_jvp_fwd (what autograd derives from the ~10 ATen ops per layer per
  * column of acl.py:53-66 / :125-146).  g_x may be NULL (treated as zero).  g_st (B,2Q) and
  * g_ST (B,d,2Q) are written densely (zeros where inv[q] < 0).  workspace must hold
- * cmf_coupling_jvp_bwd_workspace(B,d,M,Q) bytes (may be 0). */
+ * cmf_coupling_jvp_bwd_workspace(B,d,M,Q) bytes (may be 0).  The query is conservative: the mapped
+ * (32-bit) path keeps its tangent-chunk partials there for a second, reducing launch; the identity-map
+ * 128-bit path reduces the chunks inside the CTA (one launch) and leaves the workspace untouched
+ * except for tiny grids with d > 256. */
 size_t cmf_coupling_jvp_bwd_workspace(int B, int d, int M, int Q);
 int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
                          const float* z_m, const float* V_m,

@@ -32,6 +32,9 @@ def _checker_maps(M, Q, seed=0):
 COUPLING_SHAPES = [  # B, d, M, Q (Q == M -> identity map; else mapped)
     (3, 5, 8, 8), (50, 64, 392, 392), (7, 64, 196, 392), (2, 3, 1, 1), (5, 0, 12, 12),
     (4, 6, 3, 3), (9, 10, 11, 21), (2, 130, 64, 64), (1, 1, 4, 4), (6, 2, 2, 5),
+    # 128-bit path with the tangent chunks on the warps of a CTA (8 and 4 chunks, some of them empty; a last block with
+    # idle lanes), and its workspace + finalize form (tiny grid, d > 256)
+    (130, 24, 100, 100), (40, 12, 36, 36), (1, 260, 8, 8),
 ]
 
 

@@ -78,6 +78,8 @@ def test_static_scratch_matches_workspace_entry_point_two_calls_in_a_row():
     lib = _lib.load()
     # two calls in a row on different shapes (the second, smaller and mapped, finds the first call's
     # partials in the shared array and must not be affected by them), then the first shape again
+    # (the 128-bit path has since learnt to reduce its tangent chunks inside the CTA and leaves the scratch alone at this
+    # shape; the mapped call below is the one that writes and reads it)
     first = _run_pair(lib, 50, 64, 392, 392, seed=10)       # the MNIST-shape layer, 128-bit path
     second = _run_pair(lib, 7, 64, 196, 392, seed=20)       # checkerboard map, 32-bit path
     third = _run_pair(lib, 50, 64, 392, 392, seed=30)
