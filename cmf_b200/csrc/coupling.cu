@@ -140,7 +140,7 @@ __device__ __forceinline__ void finalize_store(float z, float e, float gx, float
 #ifndef CMF_CPL_BWD_UNROLL
 #define CMF_CPL_BWD_UNROLL 4
 #endif
-constexpr int kUnrollB = CMF_CPL_BWD_UNROLL;
+[[maybe_unused]] constexpr int kUnrollB = CMF_CPL_BWD_UNROLL;
 // cache policy of the adjoint's streams (probe switches; scripts/cpl_probe.cu): loads 0 = ld.cs, 1 = ld.nc, 2 = ld.cg, 3 = ld.lu;
 // stores 0 = st.cs, 1 = st (write-back, normal eviction), 2 = st.cg, 3 = st.wt
 #ifndef CMF_CPL_BWD_LD
@@ -175,6 +175,31 @@ __device__ __forceinline__ void bwd_st4(float* p, float4 v) {
     __stwt(q, v);
 #endif
 }
+// The adjoint's three input streams go through a per-thread ring in shared memory filled by 16-byte cp.async copies
+// (LDGSTS: no registers held while a load is in flight): every thread copies only what it will read itself, so the ring
+// needs cp.async.wait_group and no barrier.  kRingStages stages of kRingU tangent rows x 3 streams x 16 bytes x 256 threads;
+// CMF_CPL_BWD_RING=0 (compile time) restores the register form (12 loads in flight per thread, then compute, then stores).
+#ifndef CMF_CPL_BWD_RING
+#define CMF_CPL_BWD_RING 1
+#endif
+#ifndef CMF_CPL_BWD_STAGES
+#define CMF_CPL_BWD_STAGES 4
+#endif
+#ifndef CMF_CPL_BWD_U
+#define CMF_CPL_BWD_U 2
+#endif
+constexpr int kRingStages = CMF_CPL_BWD_STAGES, kRingU = CMF_CPL_BWD_U;
+constexpr int kRingStageVecs = 3 * kRingU * kThreads;                       // float4 per stage
+constexpr size_t kBwdRingBytes = CMF_CPL_BWD_RING ? (size_t)kRingStages * kRingStageVecs * sizeof(float4) : 0;
+static_assert((kRingStages & (kRingStages - 1)) == 0, "ring stages: a power of two");
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 __global__ void __launch_bounds__(kThreads, CMF_CPL_BWD_MINB)
 coupling_bwd_vec4(int B, int d, int M, int kchunk,
                   const float* __restrict__ z_m, const float* __restrict__ V_m,
@@ -211,6 +236,49 @@ coupling_bwd_vec4(int B, int d, int M, int kchunk,
     float* ovp = g_Vin + ((size_t)b * d + k0) * M + j;
     float* otp = g_ST + ((size_t)b * d + k0) * 2 * M + j;
     int k = k0;
+#if CMF_CPL_BWD_RING
+    {
+        extern __shared__ __align__(16) float4 ring[];
+        const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring) + threadIdx.x * 16u;
+        const int n_it = k1 > k0 ? (k1 - k0) / kRingU : 0;
+        auto issue = [&](int it) {
+            const uint32_t dst = ring_s + (uint32_t)(it & (kRingStages - 1)) * (uint32_t)(kRingStageVecs * 16);
+            const size_t row = (size_t)it * kRingU;
+#pragma unroll
+            for (int u = 0; u < kRingU; ++u) {
+                cp_async16(dst + (uint32_t)((0 * kRingU + u) * kThreads * 16), gp + (row + u) * M);
+                cp_async16(dst + (uint32_t)((1 * kRingU + u) * kThreads * 16), vp + (row + u) * M);
+                cp_async16(dst + (uint32_t)((2 * kRingU + u) * kThreads * 16), sp + (row + u) * 2 * M);
+            }
+        };
+#pragma unroll
+        for (int it = 0; it < kRingStages - 1; ++it) {
+            if (it < n_it) issue(it);
+            cp_async_commit();
+        }
+#pragma unroll 1
+        for (int it = 0; it < n_it; ++it) {
+            if (it + kRingStages - 1 < n_it) issue(it + kRingStages - 1);
+            cp_async_commit();
+            cp_async_wait<kRingStages - 1>();          // stage `it` has landed (this thread's own copies: no barrier)
+            const float4* src = ring + (size_t)(it & (kRingStages - 1)) * kRingStageVecs + threadIdx.x;
+#pragma unroll
+            for (int u = 0; u < kRingU; ++u) {
+                const float4 g = src[(0 * kRingU + u) * kThreads], v = src[(1 * kRingU + u) * kThreads],
+                             sd = src[(2 * kRingU + u) * kThreads];
+                A.x += sd.x * g.x; A.y += sd.y * g.y; A.z += sd.z * g.z; A.w += sd.w * g.w;
+                C.x += v.x * g.x;  C.y += v.y * g.y;  C.z += v.z * g.z;  C.w += v.w * g.w;
+                bwd_st4(ovp + (size_t)u * M, make_float4(e.x * g.x, e.y * g.y, e.z * g.z, e.w * g.w));
+                bwd_st4(otp + (size_t)u * 2 * M, make_float4(-g.x, -g.y, -g.z, -g.w));
+                bwd_st4(otp + (size_t)u * 2 * M + M, make_float4(ez.x * g.x, ez.y * g.y, ez.z * g.z, ez.w * g.w));
+            }
+            ovp += (size_t)kRingU * M; otp += (size_t)kRingU * 2 * M;
+        }
+        cp_async_wait<0>();
+        k = k0 + n_it * kRingU;
+        gp += (size_t)n_it * kRingU * M; vp += (size_t)n_it * kRingU * M; sp += (size_t)n_it * kRingU * 2 * M;
+    }
+#else
     for (; k + kUnrollB <= k1; k += kUnrollB) {
         float4 g[kUnrollB], v[kUnrollB], sd[kUnrollB];
 #pragma unroll
@@ -230,6 +298,8 @@ coupling_bwd_vec4(int B, int d, int M, int kchunk,
         gp += (size_t)kUnrollB * M; vp += (size_t)kUnrollB * M; sp += (size_t)kUnrollB * 2 * M;
         ovp += (size_t)kUnrollB * M; otp += (size_t)kUnrollB * 2 * M;
     }
+#endif
+#pragma unroll 1
     for (; k < k1; ++k) {
         const float4 g = bwd_ld4(gp), v = bwd_ld4(vp), sd = bwd_ld4(sp);
         A.x += sd.x * g.x; A.y += sd.y * g.y; A.z += sd.z * g.z; A.w += sd.w * g.w;
@@ -454,6 +524,14 @@ extern "C" int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
                     "coupling_bwd: workspace too small (%zu bytes, need %zu)", workspace_bytes,
                     (size_t)ny * 2 * (size_t)B * M * sizeof(float));
     float* ws = static_cast<float*>(workspace);
+    if (vec && kBwdRingBytes + 8192 > 48 * 1024) {   // opt-in to the ring's dynamic shared memory (+ 8 KB static), once per device
+        static DeviceOnce ring_attr;
+        if (!ring_attr.done()) {
+            cudaError_t e = cudaFuncSetAttribute(coupling_bwd_vec4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdRingBytes);
+            if (e != cudaSuccess) { set_error("coupling_bwd attr: %s", cudaGetErrorString(e)); return (int)e; }
+            ring_attr.mark();
+        }
+    }
     // 128-bit path, 2..8 tangent chunks: the chunks go to the warps of one CTA and meet in shared memory (one launch, no
     // workspace); CMF_CPL_BWD_WARPSPLIT=0 restores the blockIdx.y chunks + finalize launch
     static const bool warpsplit_off = [] { const char* e = getenv("CMF_CPL_BWD_WARPSPLIT"); return e && e[0] == '0'; }();
@@ -467,14 +545,14 @@ extern "C" int cmf_coupling_jvp_bwd(int B, int d, int M, int Q,
         while (S < KC && S < 8) S <<= 1;
         const int kchunk_s = (int)ceil_div(ceil_div(d, S), kUnroll) * kUnroll;
         const unsigned nx = (unsigned)ceil_div((long long)B * (M >> 2), (kThreads / S));
-        coupling_bwd_vec4<<<dim3(nx, 1), kThreads, 0, stream>>>(B, d, M, kchunk_s, z_m, V_m, st, ST, g_x, g_V,
+        coupling_bwd_vec4<<<dim3(nx, 1), kThreads, kBwdRingBytes, stream>>>(B, d, M, kchunk_s, z_m, V_m, st, ST, g_x, g_V,
                                                                g_z, g_Vin, g_st, g_ST, nullptr, S);
         CMF_CHECK_LAUNCH();
         return 0;
     }
     if (vec) {
         dim3 grid((unsigned)ceil_div((long long)B * (M >> 2), kThreads), (unsigned)ny);
-        coupling_bwd_vec4<<<grid, kThreads, 0, stream>>>(B, d, M, kchunk, z_m, V_m, st, ST, g_x, g_V,
+        coupling_bwd_vec4<<<grid, kThreads, kBwdRingBytes, stream>>>(B, d, M, kchunk, z_m, V_m, st, ST, g_x, g_V,
                                                          g_z, g_Vin, g_st, g_ST, ws, 1);
     } else {
         dim3 grid((unsigned)ceil_div((long long)B * Q, kThreads), (unsigned)ny);
